@@ -1,0 +1,89 @@
+"""Layer modules used by the model zoo.
+
+Every class subclasses the matching ``torch.nn`` module (so ``isinstance`` checks,
+``state_dict`` keys and initialisers behave as usual) and routes ``forward`` to the
+hand-written sm_100a kernels when (a) the tensors live on a CUDA device, (b) the
+native library is loaded and (c) the native backend is enabled for that op (see
+``set_backend``).  On CPU, or for shapes a kernel does not cover, the stock
+PyTorch implementation runs -- that path is also the numerical oracle in tests.
+"""
+from __future__ import annotations
+
+import torch
+import torch.nn as nn
+import torch.nn.functional as F
+
+_BACKEND = {"name": "auto"}
+
+
+def set_backend(name: str):
+    """``'auto'`` (native kernels where available), ``'torch'`` (stock ops only)."""
+    if name not in ("auto", "torch", "native"):
+        raise ValueError(name)
+    _BACKEND["name"] = name
+
+
+def get_backend() -> str:
+    return _BACKEND["name"]
+
+
+def _native_ok(x: torch.Tensor) -> bool:
+    if _BACKEND["name"] == "torch" or not x.is_cuda:
+        return False
+    from .. import _native
+    return _native.available()
+
+
+class Conv2d(nn.Conv2d):
+    def forward(self, x):
+        if _native_ok(x):
+            from . import conv as _conv
+            y = _conv.maybe_conv2d(self, x)
+            if y is not None:
+                return y
+        return super().forward(x)
+
+
+class Linear(nn.Linear):
+    def forward(self, x):
+        if _native_ok(x):
+            from . import gemm as _gemm
+            y = _gemm.maybe_linear(self, x)
+            if y is not None:
+                return y
+        return super().forward(x)
+
+
+class BatchNorm2d(nn.BatchNorm2d):
+    """Batch norm; ``fuse_relu`` lets a following ReLU be folded into the kernel."""
+
+    def forward(self, x):
+        if _native_ok(x):
+            from . import bn as _bn
+            y = _bn.maybe_batch_norm(self, x)
+            if y is not None:
+                return y
+        return super().forward(x)
+
+
+class ReLU(nn.ReLU):
+    pass
+
+
+class MaxPool2d(nn.MaxPool2d):
+    pass
+
+
+class CrossEntropyLoss(nn.CrossEntropyLoss):
+    def forward(self, logits, target):
+        if _native_ok(logits):
+            from . import loss as _loss
+            y = _loss.maybe_cross_entropy(self, logits, target)
+            if y is not None:
+                return y
+        return super().forward(logits.float() if logits.dtype != torch.float32 else logits, target)
+
+
+def add_relu(x: torch.Tensor, y: torch.Tensor) -> torch.Tensor:
+    """``relu(x + y)`` -- the residual join (reference resnet.py:89-90)."""
+    return F.relu(x + y)
