@@ -1,0 +1,301 @@
+#!/usr/bin/env python
+"""Headline benchmark: ResNet-50 training img/s with layer-wise Top-k 1 % gradient exchange.
+
+    python bench.py --gpus N --steps K --warmup W            # this framework (fused engine)
+    python bench.py --impl reference --gpus N ...            # unmodified reference code path
+
+For N > 1 launch under ``python -m torch.distributed.run --nproc-per-node N`` (one rank per
+GPU, NCCL for the plumbing).  Synthetic ImageNet-shaped data (224x224 uint8), random-init
+weights, per-GPU batch 224 (the reference recipe's batch at 224 px,
+IMAGENET/training/train_imagenet_nv.py:211).  One step = normalise -> forward -> loss ->
+backward -> compress/exchange/decompress -> SGD(momentum, nesterov, wd) incl. the fp32-master
+update.  Timed with CUDA events between barriers, max over ranks; clocks sampled with
+nvidia-smi during the timed region.  Rank 0 prints ONE JSON line.
+
+The reference arm imports the reference's own ``resnet50``, ``fp16util`` and
+``layerwise_compressed_comm`` from ``baseline/_ref`` (a verbatim copy of the reference tree;
+it has no setup.py, so ``pip install`` is impossible -- see DESIGN.md) and drives them exactly
+like its ``train()`` does in ``--fp16`` mode (train_imagenet_nv.py:404-441).
+"""
+import argparse
+import json
+import os
+import statistics
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+import torch  # noqa: E402
+import torch.distributed as dist  # noqa: E402
+
+BASELINE_PUBLISHED = None      # BASELINE.json "published": {} -> vs_baseline is null
+
+
+def parse():
+    p = argparse.ArgumentParser()
+    p.add_argument("--gpus", type=int, default=1)
+    p.add_argument("--steps", type=int, default=20)
+    p.add_argument("--warmup", type=int, default=5)
+    p.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    p.add_argument("--batch", type=int, default=224, help="per-GPU batch")
+    p.add_argument("--size", type=int, default=224)
+    p.add_argument("--arch", default="resnet50")
+    p.add_argument("--method", default="Topk")
+    p.add_argument("--ratio", type=float, default=0.01)
+    p.add_argument("--compress", default="layerwise")
+    p.add_argument("--no-ef", action="store_true")
+    p.add_argument("--no-overlap", action="store_true")
+    p.add_argument("--engine", default="auto")
+    p.add_argument("--ref-dtype", default="fp16", choices=["fp16", "fp32"])
+    p.add_argument("--skip-e2e", action="store_true")
+    p.add_argument("--phase-times", action="store_true", help="also report compress+comm ms/step")
+    return p.parse_args()
+
+
+class ClockSampler:
+    """Samples SM clocks / throttle reasons with nvidia-smi while the timed region runs."""
+    Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index: int):
+        self.index, self.proc, self.lines = index, None, []
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
+                                          "-i", str(self.index), "-lms", "100"], stdout=subprocess.PIPE,
+                                         stderr=subprocess.DEVNULL, text=True)
+            self.thread = threading.Thread(target=self._read, daemon=True)
+            self.thread.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.lines.append(line.strip())
+
+    def stop(self):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=2)
+        except Exception:
+            self.proc.kill()
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for ln in self.lines:
+            f = [x.strip() for x in ln.split(",")]
+            if len(f) < 6:
+                continue
+            try:
+                sm.append(float(f[0]))
+                mx.append(float(f[1]))
+            except ValueError:
+                continue
+            for n, v in zip(names, f[2:6]):
+                if v.lower().startswith("active"):
+                    reasons.add(n)
+        return {"sm_mhz": statistics.median(sm) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+def setup_dist(args):
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local)
+    if world > 1 or args.impl == "reference":
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        os.environ.setdefault("MASTER_PORT", "29512")
+        dist.init_process_group("nccl", rank=rank, world_size=world, device_id=torch.device("cuda", local))
+    return world, rank, local
+
+
+def barrier():
+    if dist.is_initialized():
+        dist.barrier(device_ids=[torch.cuda.current_device()])
+    torch.cuda.synchronize()
+
+
+def max_over_ranks(ms: float) -> float:
+    if not dist.is_initialized() or dist.get_world_size() == 1:
+        return ms
+    t = torch.tensor([ms], device="cuda", dtype=torch.float64)
+    dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    return float(t.item())
+
+
+def timed(step_fn, steps, sampler=None):
+    barrier()
+    if sampler:
+        sampler.start()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for i in range(steps):
+        step_fn(i)
+    e1.record()
+    torch.cuda.synchronize()
+    clocks = sampler.stop() if sampler else None
+    barrier()
+    return max_over_ranks(e0.elapsed_time(e1)), clocks
+
+
+# ---------------------------------------------------------------------------------------------------------
+def build_ours(args, world, rank):
+    import layerwise_b200  # noqa: F401
+    from layerwise_b200 import _native
+    from layerwise_b200.parallel.exchange import CompressionConfig
+    from layerwise_b200.train.imagenet import Trainer
+    _native.require()
+    cfg = CompressionConfig(compress=args.compress, method=args.method, ratio=args.ratio,
+                            error_feedback=not args.no_ef)
+    tr = Trainer(arch=args.arch, dtype="bf16", cfg=cfg, lr=0.1, momentum=0.9, weight_decay=1e-4,
+                 overlap=not args.no_overlap, engine=args.engine, device=torch.device("cuda", torch.cuda.current_device()))
+    return tr
+
+
+def build_reference(args, world, rank):
+    ref = os.path.join(ROOT, "baseline", "_ref")
+    if not os.path.isdir(os.path.join(ref, "IMAGENET", "training")):
+        raise FileNotFoundError("baseline/_ref missing (cp -r /root/reference/. baseline/_ref)")
+    sys.path.insert(0, ref)
+    sys.path.insert(0, os.path.join(ref, "IMAGENET", "training"))
+    import resnet as ref_resnet                       # IMAGENET/training/resnet.py (unmodified)
+    import fp16util as ref_fp16                        # IMAGENET/training/fp16util.py (unmodified)
+    from CIFAR10.core import layerwise_compressed_comm, entiremodel_compressed_comm  # noqa: F401
+    torch.backends.cudnn.benchmark = True             # train_imagenet_nv.py:95
+    torch.manual_seed(2147483647)                     # :117-118
+    model = ref_resnet.resnet50(bn0=True).cuda()
+    fp16 = args.ref_dtype == "fp16"
+    if fp16:
+        model = ref_fp16.network_to_half(model)
+        model_params, master_params = ref_fp16.prep_param_lists(model)
+    else:
+        model_params = master_params = list(model.parameters())
+    criterion = torch.nn.CrossEntropyLoss().cuda()
+    opt = torch.optim.SGD(master_params, 0.1, momentum=0.9, weight_decay=1e-4, nesterov=True)
+    loss_scale = 1024.0
+    mean = torch.tensor([0.485 * 255, 0.456 * 255, 0.406 * 255]).cuda().view(1, 3, 1, 1)
+    std = torch.tensor([0.229 * 255, 0.224 * 255, 0.225 * 255]).cuda().view(1, 3, 1, 1)
+    if fp16:
+        mean, std = mean.half(), std.half()
+    wsize = float(world)
+
+    def step(images_u8, target):
+        # BatchTransformDataLoader.process_tensors (dataloader.py:88-93)
+        x = images_u8.cuda(non_blocking=True)
+        x = x.half() if fp16 else x.float()
+        x = x.sub_(mean).div_(std)
+        t = target.cuda(non_blocking=True)
+        output = model(x)
+        loss = criterion(output, t)
+        if fp16:                                       # train_imagenet_nv.py:411-428
+            loss = loss * loss_scale
+            model.zero_grad()
+            loss.backward()
+            layerwise_compressed_comm(model, wsize, args.method, args.ratio, 0.001, 255)
+            ref_fp16.model_grads_to_master_grads(model_params, master_params)
+            for p in master_params:
+                p.grad.data = p.grad.data / loss_scale
+            opt.step()
+            ref_fp16.master_params_to_model_params(model_params, master_params)
+            loss = loss / loss_scale
+        else:                                          # :429-441
+            opt.zero_grad()
+            loss.backward()
+            layerwise_compressed_comm(model, wsize, args.method, args.ratio, 0.001, 255)
+            opt.step()
+        return loss
+    return step
+
+
+def main():
+    args = parse()
+    if not torch.cuda.is_available():
+        print(json.dumps({"impl": args.impl, "unavailable": "no CUDA device"}))
+        return 0
+    world, rank, local = setup_dist(args)
+    B, S = args.batch, args.size
+    g = torch.Generator().manual_seed(1234 + rank)
+    nbuf = 4
+    host_x = [torch.randint(0, 256, (B, 3, S, S), dtype=torch.uint8, generator=g).pin_memory() for _ in range(nbuf)]
+    host_y = [torch.randint(0, 1000, (B,), generator=g).pin_memory() for _ in range(nbuf)]
+    dev_x = [t.cuda() for t in host_x]
+    dev_y = [t.cuda() for t in host_y]
+
+    launches = {"n": 0}
+    if args.impl == "reference":
+        try:
+            ref_step = build_reference(args, world, rank)
+        except Exception as e:      # noqa: BLE001
+            if rank == 0:
+                print(json.dumps({"impl": "reference", "unavailable": f"{type(e).__name__}: {e}"[:300]}))
+            return 0
+        step_dev = lambda i: ref_step(dev_x[i % nbuf], dev_y[i % nbuf])      # noqa: E731
+        step_e2e = lambda i: ref_step(host_x[i % nbuf], host_y[i % nbuf])    # noqa: E731
+        dtype, par = args.ref_dtype, f"dp{world}"
+    else:
+        tr = build_ours(args, world, rank)
+        step_dev = lambda i: tr.train_step(dev_x[i % nbuf], dev_y[i % nbuf])[1]     # noqa: E731
+        step_e2e = lambda i: tr.train_step(host_x[i % nbuf], host_y[i % nbuf])[1]   # noqa: E731
+        dtype, par = "bf16", f"dp{world}"
+
+    for i in range(args.warmup):
+        step_dev(i)
+    torch.cuda.synchronize()
+    if args.impl == "ours":
+        from layerwise_b200 import _native
+        _native.counters.reset()
+    ms, clocks = timed(step_dev, args.steps, ClockSampler(local))
+    if args.impl == "ours":
+        launches["n"] = _native.counters.kernels
+    imgs = B * world * args.steps
+    value = imgs / (ms / 1e3)
+
+    e2e = None
+    if not args.skip_e2e:
+        sink = []
+
+        def e2e_step(i):
+            loss = step_e2e(i)
+            sink.append(float(loss))             # device -> host read of the step's result
+        for i in range(2):
+            e2e_step(i)
+        ms2, _ = timed(e2e_step, args.steps)
+        e2e = {"value": imgs / (ms2 / 1e3), "unit": "img/s",
+               "h2d_bytes_per_step": host_x[0].numel() + host_y[0].numel() * 8, "d2h_bytes_per_step": 4,
+               "ms_per_step": ms2 / args.steps}
+
+    extra = {}
+    if args.impl == "ours" and args.phase_times:
+        extra["exchange"] = tr.exchanger.engine.stats() if hasattr(tr.exchanger.engine, "stats") else None
+    if rank == 0:
+        out = {
+            "metric": "ResNet-50 img/s, layerwise Top-k 1% (train step incl. compress+exchange+SGD)",
+            "value": value, "unit": "img/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+            "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": (value / BASELINE_PUBLISHED) if BASELINE_PUBLISHED else None,
+            "dtype": dtype, "data": "synthetic (uint8 224x224 images, random-init weights)",
+            "impl": args.impl,
+            "config": {"model": args.arch, "global_batch": B * world, "per_gpu_batch": B, "seq_len": None,
+                       "image_size": S, "parallelism": par, "compress": args.compress, "method": args.method,
+                       "ratio": args.ratio, "error_feedback": (not args.no_ef) if args.impl == "ours" else False,
+                       "l2_policy": "inputs+activations per step (>1 GB) exceed the 126 MB L2; 4 rotating input buffers",
+                       "optimizer": "SGD momentum 0.9 nesterov wd 1e-4, fp32 masters"},
+            "clocks": clocks, "e2e": e2e, "gpu_launches": launches["n"],
+        }
+        out.update(extra)
+        print(json.dumps(out))
+    if dist.is_initialized():
+        dist.destroy_process_group()
+    return 0
+
+
+if __name__ == "__main__":
+    sys.exit(main())

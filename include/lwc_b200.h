@@ -1,0 +1,154 @@
+/*
+ * lwc_b200.h -- C ABI of the layerwise_b200 native library (sm_100a).
+ *
+ * All entry points return 0 on success, a positive cudaError_t on a CUDA failure and a
+ * negative LWC_E* code on an argument error.  Pointers named *_dev are device pointers.
+ * Streams are passed as void* (cudaStream_t).  Nothing here synchronises the device
+ * unless stated.
+ *
+ * Reference citations name the file:line of aritra-dutta/layer-wise-aaai20 whose
+ * behaviour the entry point covers.
+ */
+#ifndef LWC_B200_H_
+#define LWC_B200_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define LWC_MAX_WORLD 8
+#define LWC_CHUNK 8192            /* elements handled by one CTA */
+
+/* error codes */
+#define LWC_EINVAL   (-1)
+#define LWC_ENOMEM   (-2)
+#define LWC_ETOOBIG  (-3)
+#define LWC_ESTATE   (-4)
+
+/* dtypes */
+#define LWC_F32  0
+#define LWC_BF16 1
+#define LWC_F16  2
+
+/* methods (CIFAR10/core.py:178-215) */
+#define LWC_NONE       0
+#define LWC_TOPK       1   /* core.py:178-183 */
+#define LWC_RANDOMK    2   /* core.py:184-188, sparsified_ddp.py:409-413 */
+#define LWC_THRESHOLDV 3   /* core.py:189-193 */
+#define LWC_ADAPTIVE   4   /* core.py:194-199 */
+#define LWC_TERNGRAD   5   /* core.py:200-206 */
+#define LWC_DITHERING  6   /* core.py:207-213 (QSGD) */
+
+/* ------------------------------------------------------------------------------------------
+ * Device memory that can be shared between processes (peer receive slots, gradient arenas).
+ * cudaMalloc-backed so that cudaIpc handles can be taken (torch's caching allocator cannot
+ * promise that).  Stand-in for the c10d-internal buffers behind dist._queue_reduction
+ * (IMAGENET/training/sparsified_ddp.py:460).
+ * ---------------------------------------------------------------------------------------- */
+int lwc_malloc(void** out_dev, size_t bytes);
+int lwc_free(void* dev);
+int lwc_memset_async(void* dev, int value, size_t bytes, void* stream);
+int lwc_ipc_get_handle(void* dev, void* handle_out_64B);
+int lwc_ipc_open_handle(const void* handle_64B, void** out_dev);
+int lwc_ipc_close_handle(void* dev);
+int lwc_enable_peer_access(int peer_device);           /* idempotent */
+const char* lwc_error_string(int code);
+
+/* ------------------------------------------------------------------------------------------
+ * Exchange plan: one bucket of gradient tensors that is compressed, exchanged and
+ * decompressed together.  "Layer-wise" = one selection group per tensor; "entire-model" =
+ * one group spanning all tensors (CIFAR10/core.py:175-225 vs :227-301).
+ * ---------------------------------------------------------------------------------------- */
+typedef struct LwcPlan LwcPlan;
+
+typedef struct {
+    int32_t  num_tensors;
+    int32_t  num_groups;
+    int32_t  method;          /* LWC_* */
+    int32_t  grad_dtype;      /* dtype of grad_dev[] */
+    int32_t  out_dtype;       /* dtype of out_dev[]  */
+    int32_t  world;           /* ranks in the exchange (1..LWC_MAX_WORLD) */
+    int32_t  rank;
+    int32_t  qstates;         /* LWC_DITHERING levels (1..255) */
+    float    threshold;       /* LWC_THRESHOLDV */
+    uint64_t seed;            /* RNG key; same on all ranks for shared masks */
+    /* per tensor */
+    const void* const* grad_dev;
+    void* const*       out_dev;
+    float* const*      resid_dev;   /* error-feedback residuals, or NULL entries / NULL array */
+    const int64_t*     numel;
+    const int32_t*     group_of;    /* group id of each tensor, non-decreasing */
+    const int32_t*     uid;         /* stable id per tensor for RNG keying */
+    /* per group */
+    const int64_t*     keep;        /* Top-k / Random-k: number of elements to keep */
+    const int64_t*     cap;         /* payload capacity (entries) */
+} LwcPlanDesc;
+
+int lwc_plan_create(LwcPlan** out, const LwcPlanDesc* desc);
+int lwc_plan_destroy(LwcPlan* plan);
+/* bytes of one receive slot (one source rank, one parity) and of the whole region
+ * (2 parities x world slots) a rank must provide for this plan */
+size_t lwc_plan_slot_bytes(const LwcPlan* plan);
+size_t lwc_plan_region_bytes(const LwcPlan* plan);
+/* region_dev[d] = base of rank d's receive region for this plan, flags_dev[d] = rank d's
+ * flag array (LWC_MAX_WORLD uint64 per plan, zero-initialised).  For rank==d these are
+ * local allocations; for the others peer-mapped pointers. */
+int lwc_plan_bind(LwcPlan* plan, void* const* region_dev, void* const* flags_dev);
+/* optional: uniforms in [0,1) (quantisers) or integer keys (Random-k) injected per tensor
+ * for bit-exact tests; NULL restores the counter-based generator */
+int lwc_plan_set_random(LwcPlan* plan, const void* const* rand_dev);
+/* Sender side: error-feedback accumulate, select / quantise, residual update, pack,
+ * store into every rank's slot, release flags.  step must increase by 1 per call. */
+int lwc_plan_send(LwcPlan* plan, uint64_t step, void* stream);
+/* Receiver side: acquire the flags of step, scatter-add / dequantise all sources in rank
+ * order, scale by 1/world, write out_dev[].  With sgd != NULL the averaged gradient is
+ * consumed by a fused SGD update instead (see LwcSgdArgs). */
+typedef struct {
+    float lr, momentum, dampening, weight_decay, grad_scale;
+    int32_t nesterov, first_step;
+    void* const*  param_dev;      /* fp32 master weights per tensor */
+    void* const*  mom_dev;        /* fp32 momentum buffers per tensor (or NULL when momentum==0) */
+    void* const*  model_dev;      /* optional low-precision copies (out_dtype), NULL entries allowed */
+} LwcSgdArgs;
+int lwc_plan_recv(LwcPlan* plan, uint64_t step, void* stream);
+/* counters: [0]=entries sent last step, [1]=entries dropped by capacity clamp,
+ * [2]=flag wait timeouts, [3]=payload bytes stored per destination */
+int lwc_plan_stats(LwcPlan* plan, uint64_t out[4], void* stream);
+
+/* ------------------------------------------------------------------------------------------
+ * Stand-alone exact Top-k selection of one fp32 vector (the K1 kernel family without the
+ * exchange): threshold = keep-th largest |x|, every |x| >= threshold and != 0 is emitted in
+ * index order, at most cap entries.  workspace_dev must hold lwc_topk_workspace_bytes(n)
+ * bytes of scratch.  (CIFAR10/core.py:178-183)
+ * ---------------------------------------------------------------------------------------- */
+size_t lwc_topk_workspace_bytes(int64_t n);
+int lwc_topk_select_f32(const float* x_dev, int64_t n, int64_t keep, int64_t cap,
+                        uint32_t* idx_out_dev, float* val_out_dev, int64_t* count_out_dev,
+                        void* workspace_dev, void* stream);
+
+/* ------------------------------------------------------------------------------------------
+ * Fused multi-tensor SGD (torch.optim.SGD semantics: CIFAR10/torch_backend.py:132-143,
+ * IMAGENET/training/train_imagenet_nv.py:188-191,:441; fp16 master copies
+ * IMAGENET/training/fp16util.py:103-139 folded in).
+ * ---------------------------------------------------------------------------------------- */
+typedef struct {
+    int32_t num_tensors;
+    int32_t grad_dtype;      /* dtype of grads */
+    int32_t model_dtype;     /* dtype of model copies (ignored when model_dev == NULL) */
+    float lr, momentum, dampening, weight_decay, grad_scale;
+    int32_t nesterov, first_step;
+} LwcSgdDesc;
+/* table_dev: device array of num_tensors LwcSgdTensor; chunk table built by lwc_sgd_plan */
+typedef struct { void* param; const void* grad; void* mom; void* model; int64_t n; } LwcSgdTensor;
+typedef struct LwcSgdPlan LwcSgdPlan;
+int lwc_sgd_plan_create(LwcSgdPlan** out, const LwcSgdTensor* tensors_host, int32_t num_tensors);
+int lwc_sgd_plan_destroy(LwcSgdPlan* plan);
+int lwc_sgd_step(LwcSgdPlan* plan, const LwcSgdDesc* desc, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif  /* LWC_B200_H_ */

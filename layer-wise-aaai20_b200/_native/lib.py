@@ -28,9 +28,25 @@ _load_error: Optional[str] = None
 
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-std=c++17", "-lineinfo",
-    "--use_fast_math", "-Xcompiler", "-fPIC", "-Xcompiler", "-O3",
+    "-Xcompiler", "-fPIC", "-Xcompiler", "-O3",
     "--expt-relaxed-constexpr", "-Xptxas", "-v",
 ]
+
+
+class _Counters:
+    """Host-side count of kernels this library launched (bench.py reports it as gpu_launches)."""
+
+    def __init__(self):
+        self.kernels = 0
+
+    def reset(self):
+        self.kernels = 0
+
+    def add(self, n: int):
+        self.kernels += n
+
+
+counters = _Counters()
 
 
 def _nvcc() -> str:

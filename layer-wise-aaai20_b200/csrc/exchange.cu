@@ -1,0 +1,1155 @@
+// Fused gradient compress -> exchange -> decompress for sm_100a (B200), NVLink peer stores.
+//
+// One "plan" = one bucket of gradient tensors.  Work is cut into chunks of LWC_CHUNK elements
+// (one CTA each) listed in a device chunk table, so a bucket with hundreds of tiny tensors and
+// a bucket with one 100M-element tensor both run as a handful of launches ("multi-tensor").
+//
+// Sparse methods (Top-k, Random-k, Threshold-v, adaptive threshold):
+//   k_pre      : acc = grad + residual (error feedback), residual <- acc, first radix histogram
+//                of the 31-bit selection key (|acc| bit pattern, or a counter-based hash for
+//                Random-k) or a max-reduction (adaptive)
+//   k_group    : per selection group: find the histogram bin holding the keep-th largest key
+//   k_hist     : second / third radix level restricted to the current prefix
+//   k_count    : per chunk number of keys > T and == T
+//   k_group    : exclusive scan of the chunk counts (ordered, deterministic payload layout)
+//   k_compact_send : ordered compaction of (index, value), residual <- 0 at sent entries,
+//                coalesced stores of the packed run into the receive slot of EVERY rank
+//                (local + peer-mapped pointers over NVLink), release flag by the last CTA
+//   k_recv_sparse : acquire W-1 flags, each CTA owns one chunk of the dense output: binary-search
+//                every source's sorted payload for its index range, accumulate in shared memory in
+//                rank order (deterministic, no atomics), scale by 1/W, write the gradient
+// Quantisers (TernGrad 2-bit, QSGD/dithering 8-bit + sign) and the dense path reuse k_pre for the
+// scale (max / L2 norm) and then k_quant_send / k_recv_dense.
+//
+// Reference behaviour covered: CIFAR10/core.py:175-301 (compress + all_reduce + /W + copy back),
+// IMAGENET/training/sparsified_ddp.py:403-414,:468-483 (error feedback, pack, expand).
+#include <math.h>
+#include <stdio.h>
+#include <string.h>
+
+#include <vector>
+
+#include "common.cuh"
+
+namespace lwc {
+
+constexpr int kHist1 = 2048;     // key bits 30..20
+constexpr int kHist2 = 1024;     // key bits 19..10
+constexpr int kHist3 = 1024;     // key bits  9..0
+constexpr int kStage = 2048;     // staged payload entries per CTA
+constexpr uint32_t kNoKey = 0x80000000u;   // larger than every 31-bit key
+constexpr unsigned long long kNoQuota = ~0ULL;
+
+struct TensorRec {
+    const void* grad;
+    void* out;
+    float* resid;
+    const void* rnd;
+    long long n;
+    long long goff;     // offset of element 0 inside the group's index space
+    int group;
+    int uid;
+};
+struct ChunkRec {
+    int tensor;
+    int len;
+    long long start;
+};
+struct GroupCfg {
+    long long n;
+    long long keep;
+    long long cap;
+    long long pay_off;
+    int chunk_begin;
+    int chunk_end;
+    int uid;
+    int pad;
+};
+struct GroupState {
+    unsigned hist1[kHist1];
+    unsigned hist2[kHist2];
+    unsigned hist3[kHist3];
+    unsigned prefix;
+    unsigned thresh;
+    unsigned maxbits;
+    float scale;
+    unsigned long long remaining;
+    unsigned long long count_gt;
+    unsigned long long eq_quota;
+    unsigned long long gt_total;
+    unsigned long long eq_total;
+    unsigned long long kept;
+};
+struct Counters {
+    unsigned long long sent;
+    unsigned long long dropped;
+    unsigned long long timeouts;
+    unsigned long long bytes;
+    unsigned int done;      // CTA completion ticket of the send kernel
+    unsigned int pad;
+};
+
+struct DevPlan {     // passed by value to kernels
+    const TensorRec* tensors;
+    const ChunkRec* chunks;
+    const GroupCfg* gcfg;
+    GroupState* gstate;
+    unsigned* chunk_cnt;       // packed gt | eq<<16 per chunk
+    unsigned long long* chunk_off;   // packed exclusive offsets gt | eq<<32
+    float* chunk_part;         // per chunk partial (sum of squares)
+    Counters* counters;
+    int num_chunks;
+    int num_groups;
+    int method;
+    int world;
+    int rank;
+    int qstates;
+    float threshold;
+    unsigned long long seed;
+    unsigned long long step;
+    // slot geometry
+    unsigned long long slot_bytes;
+    unsigned long long hdr_bytes;
+    unsigned long long idx_off;     // byte offset of idx array inside a slot
+    unsigned long long val_off;     // byte offset of val array
+    unsigned long long code_off;    // byte offset of code area (dense / quantised)
+    unsigned long long code_stride; // bytes per chunk in the code area
+    char* region[LWC_MAX_WORLD];
+    uint64_t* flags[LWC_MAX_WORLD];
+    // stand-alone selection: write (idx, val, count) here instead of into exchange slots
+    uint32_t* direct_idx;
+    float* direct_val;
+    long long* direct_count;
+};
+
+__device__ __forceinline__ char* slot_ptr(const DevPlan& p, int dst, int src) {
+    const unsigned long long parity = p.step & 1ULL;
+    return p.region[dst] + (parity * p.world + src) * p.slot_bytes;
+}
+
+// ---- selection key -----------------------------------------------------------------------------
+__device__ __forceinline__ uint64_t group_salt(const DevPlan& p, int uid) {
+    return mix64(p.seed + p.step * 0xD6E8FEB86659FD93ULL + (unsigned long long)uid * 0xA24BAED4963EE407ULL);
+}
+__device__ __forceinline__ uint32_t make_key(int method, float acc, const void* rnd, long long i,
+                                             long long gidx, uint64_t salt) {
+    if (method == LWC_RANDOMK) {
+        if (rnd) return reinterpret_cast<const uint32_t*>(rnd)[i] & 0x7fffffffu;
+        return (uint32_t)(mix64((uint64_t)gidx * 0x9E3779B97F4A7C15ULL + salt) >> 33);
+    }
+    if (method == LWC_ADAPTIVE) return __float_as_uint(fabsf(acc * 2.0f));
+    return __float_as_uint(fabsf(acc));
+}
+
+// Source of the accumulated gradient for the passes after k_pre.
+template <typename GradT>
+__device__ __forceinline__ void load_acc(const TensorRec& t, long long start, int j, int len, float v[4]) {
+    if (t.resid) {
+        const float* b = t.resid + start;
+        load_quad<float>(b, j, len, vec_ok(b), v);
+    } else {
+        const GradT* b = reinterpret_cast<const GradT*>(t.grad) + start;
+        load_quad<GradT>(b, j, len, vec_ok(b), v);
+    }
+}
+
+enum { STAT_NONE = 0, STAT_HIST = 1, STAT_MAX = 2, STAT_SUMSQ = 3 };
+
+// ---- pass 1: error-feedback accumulate + first statistic -----------------------------------------------
+template <typename GradT, int STAT>
+__global__ void __launch_bounds__(kThreads) k_pre(DevPlan p) {
+    __shared__ unsigned sh_hist[STAT == STAT_HIST ? kHist1 : 1];
+    __shared__ float sh_red[kThreads / 32];
+    const ChunkRec c = p.chunks[blockIdx.x];
+    const TensorRec t = p.tensors[c.tensor];
+    const int tid = threadIdx.x;
+    if (STAT == STAT_HIST) {
+        for (int b = tid; b < kHist1; b += kThreads) sh_hist[b] = 0;
+        __syncthreads();
+    }
+    const GradT* g = reinterpret_cast<const GradT*>(t.grad) + c.start;
+    float* r = t.resid ? t.resid + c.start : nullptr;
+    const bool gv = vec_ok(g), rv = r && vec_ok(r);
+    const uint64_t salt = group_salt(p, p.gcfg[t.group].uid);
+    float red = 0.0f;
+#pragma unroll 2
+    for (int it = 0; it < kQuadsPerThread; ++it) {
+        const int j = (it * kThreads + tid) * 4;
+        if (j >= c.len) break;
+        float v[4];
+        load_quad<GradT>(g, j, c.len, gv, v);
+        if (r) {
+            float e[4];
+            load_quad<float>(r, j, c.len, rv, e);
+#pragma unroll
+            for (int k = 0; k < 4; ++k) v[k] += e[k];
+            store_quad<float>(r, j, c.len, rv, v);
+        }
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+            if (j + k >= c.len) break;
+            if (STAT == STAT_HIST) {
+                const long long i = c.start + j + k;
+                const uint32_t key = make_key(p.method, v[k], t.rnd, i, t.goff + i, salt);
+                atomicAdd(&sh_hist[key >> 20], 1u);
+            } else if (STAT == STAT_MAX) {
+                red = fmaxf(red, fabsf(v[k]));
+            } else if (STAT == STAT_SUMSQ) {
+                red = fmaf(v[k], v[k], red);
+            }
+        }
+    }
+    if (STAT == STAT_HIST) {
+        __syncthreads();
+        GroupState& gs = p.gstate[t.group];
+        for (int b = tid; b < kHist1; b += kThreads) {
+            const unsigned h = sh_hist[b];
+            if (h) atomicAdd(&gs.hist1[b], h);
+        }
+    } else if (STAT == STAT_MAX || STAT == STAT_SUMSQ) {
+        red = (STAT == STAT_MAX) ? warp_max(red) : warp_sum(red);
+        if ((tid & 31) == 0) sh_red[tid >> 5] = red;
+        __syncthreads();
+        if (tid < 32) {
+            float x = tid < kThreads / 32 ? sh_red[tid] : 0.0f;
+            x = (STAT == STAT_MAX) ? warp_max(x) : warp_sum(x);
+            if (tid == 0) {
+                if (STAT == STAT_MAX) atomicMax(&p.gstate[t.group].maxbits, __float_as_uint(x));
+                else p.chunk_part[blockIdx.x] = x;
+            }
+        }
+    }
+}
+
+// ---- radix levels 2 and 3 -----------------------------------------------------------------------------
+template <typename GradT, int LEVEL>
+__global__ void __launch_bounds__(kThreads) k_hist(DevPlan p) {
+    __shared__ unsigned sh_hist[kHist2];
+    const ChunkRec c = p.chunks[blockIdx.x];
+    const TensorRec t = p.tensors[c.tensor];
+    GroupState& gs = p.gstate[t.group];
+    const unsigned prefix = gs.prefix;
+    const int tid = threadIdx.x;
+    for (int b = tid; b < kHist2; b += kThreads) sh_hist[b] = 0;
+    __syncthreads();
+    const uint64_t salt = group_salt(p, p.gcfg[t.group].uid);
+    bool any = false;
+#pragma unroll 2
+    for (int it = 0; it < kQuadsPerThread; ++it) {
+        const int j = (it * kThreads + tid) * 4;
+        if (j >= c.len) break;
+        float v[4];
+        load_acc<GradT>(t, c.start, j, c.len, v);
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+            if (j + k >= c.len) break;
+            const long long i = c.start + j + k;
+            const uint32_t key = make_key(p.method, v[k], t.rnd, i, t.goff + i, salt);
+            if (LEVEL == 2) {
+                if ((key >> 20) == prefix) { atomicAdd(&sh_hist[(key >> 10) & 1023u], 1u); any = true; }
+            } else {
+                if ((key >> 10) == prefix) { atomicAdd(&sh_hist[key & 1023u], 1u); any = true; }
+            }
+        }
+    }
+    if (!__syncthreads_or(any)) return;
+    unsigned* dst = (LEVEL == 2) ? gs.hist2 : gs.hist3;
+    for (int b = tid; b < kHist2; b += kThreads) {
+        const unsigned h = sh_hist[b];
+        if (h) atomicAdd(&dst[b], h);
+    }
+}
+
+// ---- per-group bookkeeping (one CTA per group) -----------------------------------------------------
+enum { G_SCAN1 = 1, G_SCAN2, G_SCAN3, G_SET_THRESH, G_SET_ADAPT, G_FIN_MAX, G_FIN_NORM, G_SCAN_COUNTS };
+
+__device__ __forceinline__ unsigned long long block_excl_scan_u64(unsigned long long v, unsigned long long* sh,
+                                                                  unsigned long long* total) {
+    // sh: kThreads/32 + 1 entries
+    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+    unsigned long long x = v;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        unsigned long long y = __shfl_up_sync(0xffffffffu, x, o);
+        if (lane >= o) x += y;
+    }
+    if (lane == 31) sh[w] = x;
+    __syncthreads();
+    if (w == 0) {
+        unsigned long long s = lane < kThreads / 32 ? sh[lane] : 0ULL;
+        unsigned long long xs = s;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            unsigned long long y = __shfl_up_sync(0xffffffffu, xs, o);
+            if (lane >= o) xs += y;
+        }
+        if (lane < kThreads / 32) sh[lane] = xs - s;           // exclusive warp offsets
+        if (lane == kThreads / 32 - 1) sh[kThreads / 32] = xs;  // grand total
+    }
+    __syncthreads();
+    const unsigned long long res = x - v + sh[w];
+    if (total) *total = sh[kThreads / 32];
+    __syncthreads();
+    return res;
+}
+
+// Find the bin b (scanning from the top) with S(b+1) < target <= S(b); returns via shared result.
+template <int BINS>
+__device__ void select_bin(const unsigned* hist, unsigned long long target, unsigned long long* sh_scan,
+                           unsigned* out_bin, unsigned long long* out_above, unsigned* out_cnt) {
+    constexpr int PER = BINS / kThreads;
+    const int tid = threadIdx.x;
+    // thread tid owns bins [BINS-(tid+1)*PER, BINS-tid*PER), visited from the top down
+    unsigned local[PER];
+    unsigned long long sum = 0;
+#pragma unroll
+    for (int k = 0; k < PER; ++k) {
+        local[k] = hist[BINS - 1 - (tid * PER + k)];
+        sum += local[k];
+    }
+    unsigned long long total;
+    unsigned long long above = block_excl_scan_u64(sum, sh_scan, &total);
+    __shared__ unsigned s_bin;
+    __shared__ unsigned long long s_above;
+    __shared__ unsigned s_cnt;
+    if (tid == 0) { s_bin = 0; s_above = total - hist[0]; s_cnt = hist[0]; }   // default: lowest bin
+    __syncthreads();
+    if (target > above && target <= above + sum) {
+        unsigned long long a = above;
+#pragma unroll
+        for (int k = 0; k < PER; ++k) {
+            if (target <= a + local[k]) {
+                s_bin = BINS - 1 - (tid * PER + k);
+                s_above = a;
+                s_cnt = local[k];
+                break;
+            }
+            a += local[k];
+        }
+    }
+    __syncthreads();
+    *out_bin = s_bin;
+    *out_above = s_above;
+    *out_cnt = s_cnt;
+}
+
+__global__ void __launch_bounds__(kThreads) k_group(DevPlan p, int mode) {
+    __shared__ unsigned long long sh_scan[kThreads / 32 + 1];
+    const int g = blockIdx.x;
+    const GroupCfg cfg = p.gcfg[g];
+    GroupState& gs = p.gstate[g];
+    const int tid = threadIdx.x;
+    if (mode == G_SCAN1 || mode == G_SCAN2 || mode == G_SCAN3) {
+        if (cfg.keep <= 0) {
+            if (tid == 0 && mode == G_SCAN3) { gs.thresh = kNoKey; gs.count_gt = 0; gs.eq_quota = 0; }
+            return;
+        }
+        unsigned bin, cnt;
+        unsigned long long above;
+        const unsigned long long target = (mode == G_SCAN1) ? (unsigned long long)cfg.keep : gs.remaining;
+        if (mode == G_SCAN1) select_bin<kHist1>(gs.hist1, target, sh_scan, &bin, &above, &cnt);
+        else if (mode == G_SCAN2) select_bin<kHist2>(gs.hist2, target, sh_scan, &bin, &above, &cnt);
+        else select_bin<kHist3>(gs.hist3, target, sh_scan, &bin, &above, &cnt);
+        if (tid == 0) {
+            const unsigned long long cg = (mode == G_SCAN1 ? 0ULL : gs.count_gt) + above;
+            gs.count_gt = cg;
+            gs.remaining = target > above ? target - above : 1ULL;
+            if (mode == G_SCAN1) gs.prefix = bin;
+            else if (mode == G_SCAN2) gs.prefix = (gs.prefix << 10) | bin;
+            else {
+                gs.thresh = (gs.prefix << 10) | bin;
+                // Top-k keeps every tie (reference: |g| >= thres); Random-k keeps exactly `keep`
+                const unsigned long long k = (unsigned long long)cfg.keep;
+                gs.eq_quota = (p.method == LWC_RANDOMK) ? (k > cg ? k - cg : 0ULL) : kNoQuota;
+            }
+        }
+    } else if (mode == G_SET_THRESH) {
+        if (tid == 0) { gs.thresh = __float_as_uint(fabsf(p.threshold)); gs.eq_quota = kNoQuota; }
+    } else if (mode == G_SET_ADAPT) {
+        if (tid == 0) { gs.thresh = gs.maxbits; gs.eq_quota = kNoQuota; }
+    } else if (mode == G_FIN_MAX) {
+        if (tid == 0) gs.scale = __uint_as_float(gs.maxbits);
+    } else if (mode == G_FIN_NORM) {
+        // fixed-order double accumulation of the chunk partials: run-to-run deterministic
+        double acc = 0.0;
+        for (int c = cfg.chunk_begin + tid; c < cfg.chunk_end; c += kThreads) acc += (double)p.chunk_part[c];
+        __shared__ double sh_d[kThreads];
+        sh_d[tid] = acc;
+        __syncthreads();
+        for (int o = kThreads / 2; o > 0; o >>= 1) {
+            if (tid < o) sh_d[tid] += sh_d[tid + o];
+            __syncthreads();
+        }
+        if (tid == 0) gs.scale = (float)sqrt(sh_d[0]);
+    } else if (mode == G_SCAN_COUNTS) {
+        unsigned long long run_gt = 0, run_eq = 0;
+        for (int base = cfg.chunk_begin; base < cfg.chunk_end; base += kThreads) {
+            const int c = base + tid;
+            const unsigned packed = c < cfg.chunk_end ? p.chunk_cnt[c] : 0u;
+            const unsigned long long v = (unsigned long long)(packed & 0xffffu) | ((unsigned long long)(packed >> 16) << 32);
+            unsigned long long tot;
+            const unsigned long long ex = block_excl_scan_u64(v, sh_scan, &tot);
+            if (c < cfg.chunk_end) {
+                const unsigned long long gt = run_gt + (ex & 0xffffffffULL);
+                const unsigned long long eq = run_eq + (ex >> 32);
+                p.chunk_off[c] = gt | (eq << 32);
+            }
+            run_gt += tot & 0xffffffffULL;
+            run_eq += tot >> 32;
+        }
+        if (tid == 0) {
+            const unsigned long long quota = gs.eq_quota;
+            unsigned long long want = run_gt + (run_eq < quota ? run_eq : quota);
+            unsigned long long kept = want < (unsigned long long)cfg.cap ? want : (unsigned long long)cfg.cap;
+            gs.gt_total = run_gt;
+            gs.eq_total = run_eq;
+            gs.kept = kept;
+            atomicAdd(&p.counters->sent, kept);
+            atomicAdd(&p.counters->dropped, want - kept);
+        }
+    }
+}
+
+// ---- per chunk counts of keys > T and == T -----------------------------------------------------------
+template <typename GradT>
+__global__ void __launch_bounds__(kThreads) k_count(DevPlan p) {
+    __shared__ unsigned sh[kThreads / 32];
+    const ChunkRec c = p.chunks[blockIdx.x];
+    const TensorRec t = p.tensors[c.tensor];
+    const unsigned T = p.gstate[t.group].thresh;
+    const uint64_t salt = group_salt(p, p.gcfg[t.group].uid);
+    const int tid = threadIdx.x;
+    unsigned cnt = 0;   // gt in low 16 bits, eq in high 16 bits (a thread sees at most 32 elements)
+#pragma unroll 2
+    for (int it = 0; it < kQuadsPerThread; ++it) {
+        const int j = (it * kThreads + tid) * 4;
+        if (j >= c.len) break;
+        float v[4];
+        load_acc<GradT>(t, c.start, j, c.len, v);
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+            if (j + k >= c.len) break;
+            if (v[k] == 0.0f) continue;
+            const long long i = c.start + j + k;
+            const uint32_t key = make_key(p.method, v[k], t.rnd, i, t.goff + i, salt);
+            cnt += (key > T) ? 1u : (key == T ? 0x10000u : 0u);
+        }
+    }
+    cnt = warp_sum_u(cnt);
+    if ((tid & 31) == 0) sh[tid >> 5] = cnt;
+    __syncthreads();
+    if (tid == 0) {
+        unsigned s = 0;
+#pragma unroll
+        for (int w = 0; w < kThreads / 32; ++w) s += sh[w];
+        p.chunk_cnt[blockIdx.x] = s;
+    }
+}
+
+// Publish "this rank's payload for `step` is complete" to every destination.  Called by all
+// threads of every CTA of the sending kernel after their payload stores.
+__device__ __forceinline__ void publish_when_last(const DevPlan& p) {
+    if (p.direct_idx) return;
+    __threadfence_system();
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        const unsigned ticket = atomicAdd(&p.counters->done, 1u);
+        if (ticket == gridDim.x - 1) {
+            __threadfence_system();
+            p.counters->done = 0;
+            for (int d = 0; d < p.world; ++d) st_release_sys(p.flags[d] + p.rank, p.step + 1);
+        }
+    }
+}
+
+// ---- ordered compaction + residual update + stores to every rank ---------------------------------------
+template <typename GradT>
+__global__ void __launch_bounds__(kThreads) k_compact_send(DevPlan p) {
+    __shared__ uint32_t st_idx[kStage];
+    __shared__ float st_val[kStage];
+    __shared__ unsigned sh_warp[kThreads / 32];
+    __shared__ unsigned sh_base;
+    const ChunkRec c = p.chunks[blockIdx.x];
+    const TensorRec t = p.tensors[c.tensor];
+    const GroupCfg cfg = p.gcfg[t.group];
+    const GroupState& gs = p.gstate[t.group];
+    const unsigned T = gs.thresh;
+    const unsigned long long quota = gs.eq_quota;
+    const unsigned long long cap = (unsigned long long)cfg.cap;
+    const uint64_t salt = group_salt(p, cfg.uid);
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+
+    const unsigned long long off = p.chunk_off[blockIdx.x];
+    const unsigned long long gt_off = off & 0xffffffffULL, eq_off = off >> 32;
+    const unsigned packed = p.chunk_cnt[blockIdx.x];
+    const unsigned long long cgt = packed & 0xffffu, ceq = packed >> 16;
+    auto pos_of = [&](unsigned long long g, unsigned long long e) {
+        return g + (e < quota ? e : quota);
+    };
+    unsigned long long pos_begin = pos_of(gt_off, eq_off);
+    unsigned long long pos_end = pos_of(gt_off + cgt, eq_off + ceq);
+    if (pos_begin > cap) pos_begin = cap;
+    if (pos_end > cap) pos_end = cap;
+    const unsigned n_out = (unsigned)(pos_end - pos_begin);
+    const bool staged = n_out <= (unsigned)kStage;
+
+    // header: the CTA owning the group's first chunk publishes the entry count to every rank
+    if (p.direct_idx) {
+        if ((int)blockIdx.x == cfg.chunk_begin && tid == 0) p.direct_count[t.group] = (long long)gs.kept;
+    } else if ((int)blockIdx.x == cfg.chunk_begin && tid < p.world) {
+        long long* hdr = reinterpret_cast<long long*>(slot_ptr(p, tid, p.rank));
+        hdr[t.group] = (long long)gs.kept;
+    }
+    if (tid == 0) sh_base = 0;
+    __syncthreads();
+
+    if (n_out > 0) {
+        for (int it = 0; it < kQuadsPerThread; ++it) {
+            const int j = (it * kThreads + tid) * 4;
+            float v[4] = {0.f, 0.f, 0.f, 0.f};
+            unsigned fl = 0;      // bit k: gt, bit 4+k: eq
+            if (j < c.len) {
+                load_acc<GradT>(t, c.start, j, c.len, v);
+#pragma unroll
+                for (int k = 0; k < 4; ++k) {
+                    if (j + k >= c.len || v[k] == 0.0f) continue;
+                    const long long i = c.start + j + k;
+                    const uint32_t key = make_key(p.method, v[k], t.rnd, i, t.goff + i, salt);
+                    fl |= (key > T) ? (1u << k) : (key == T ? (16u << k) : 0u);
+                }
+            }
+            const unsigned mine = __popc(fl & 0xfu) | (__popc(fl >> 4) << 16);
+            const unsigned incl = warp_incl_scan(mine);
+            if (lane == 31) sh_warp[warp] = incl;
+            __syncthreads();
+            unsigned wbase = sh_base;
+#pragma unroll
+            for (int w = 0; w < kThreads / 32; ++w)
+                if (w < warp) wbase += sh_warp[w];
+            unsigned run = wbase + incl - mine;     // exclusive (gt | eq<<16) before this thread
+            if (fl) {
+#pragma unroll
+                for (int k = 0; k < 4; ++k) {
+                    const bool is_gt = (fl >> k) & 1u, is_eq = (fl >> (4 + k)) & 1u;
+                    if (!(is_gt || is_eq)) continue;
+                    const unsigned long long g_before = gt_off + (run & 0xffffu);
+                    const unsigned long long e_before = eq_off + (run >> 16);
+                    const unsigned long long pos = pos_of(g_before, e_before);
+                    const bool keep = pos < cap && (is_gt || e_before < quota);
+                    run += is_gt ? 1u : 0x10000u;
+                    if (!keep) continue;
+                    const long long i = c.start + j + k;
+                    const uint32_t gidx = (uint32_t)(t.goff + i);
+                    if (staged) {
+                        st_idx[pos - pos_begin] = gidx;
+                        st_val[pos - pos_begin] = v[k];
+                    } else if (p.direct_idx) {
+                        p.direct_idx[cfg.pay_off + pos] = gidx;
+                        p.direct_val[cfg.pay_off + pos] = v[k];
+                    } else {
+                        for (int d = 0; d < p.world; ++d) {
+                            char* s = slot_ptr(p, d, p.rank);
+                            reinterpret_cast<uint32_t*>(s + p.idx_off)[cfg.pay_off + pos] = gidx;
+                            reinterpret_cast<float*>(s + p.val_off)[cfg.pay_off + pos] = v[k];
+                        }
+                    }
+                    if (t.resid) t.resid[i] = 0.0f;     // sent exactly: nothing left behind
+                }
+            }
+            __syncthreads();
+            if (tid == kThreads - 1) sh_base = wbase + incl;   // last thread holds the block total
+            __syncthreads();
+        }
+        if (staged) {
+            const int ndst = p.direct_idx ? 1 : p.world;
+            for (int d = 0; d < ndst; ++d) {
+                char* s = p.direct_idx ? nullptr : slot_ptr(p, d, p.rank);
+                uint32_t* di = (p.direct_idx ? p.direct_idx : reinterpret_cast<uint32_t*>(s + p.idx_off)) + cfg.pay_off + pos_begin;
+                float* dv = (p.direct_val ? p.direct_val : reinterpret_cast<float*>(s + p.val_off)) + cfg.pay_off + pos_begin;
+                for (unsigned e = tid; e < n_out; e += kThreads) {
+                    di[e] = st_idx[e];
+                    dv[e] = st_val[e];
+                }
+            }
+        }
+    }
+    publish_when_last(p);
+}
+
+// ---- wait for every source's flag (bounded spin) -------------------------------------------------------
+__device__ __forceinline__ void wait_sources(const DevPlan& p) {
+    if (threadIdx.x < p.world && (int)threadIdx.x != p.rank) {
+        const uint64_t* f = p.flags[p.rank] + threadIdx.x;
+        const uint64_t want = p.step + 1;
+        const uint64_t t0 = global_timer_ns();
+        unsigned spins = 0;
+        while (ld_acquire_sys(f) < want) {
+            if ((++spins & 1023u) == 0 && global_timer_ns() - t0 > 10000000000ULL) {   // 10 s
+                atomicAdd(&p.counters->timeouts, 1ULL);
+                break;
+            }
+            __nanosleep(64);
+        }
+    }
+    __syncthreads();
+}
+
+// ---- receiver, sparse: every CTA owns one chunk of the dense output --------------------------------------
+template <typename OutT>
+__global__ void __launch_bounds__(kThreads) k_recv_sparse(DevPlan p) {
+    __shared__ float acc[kChunk];
+    __shared__ int sh_rng[2];
+    const ChunkRec c = p.chunks[blockIdx.x];
+    const TensorRec t = p.tensors[c.tensor];
+    const GroupCfg cfg = p.gcfg[t.group];
+    const int tid = threadIdx.x;
+    for (int j = tid; j < kChunk; j += kThreads) acc[j] = 0.0f;
+    wait_sources(p);
+    const unsigned long long lo = (unsigned long long)(t.goff + c.start), hi = lo + c.len;
+    for (int src = 0; src < p.world; ++src) {
+        const char* s = slot_ptr(p, p.rank, src);
+        long long kept = reinterpret_cast<const long long*>(s)[t.group];
+        if (kept > cfg.cap) kept = cfg.cap;
+        const uint32_t* idx = reinterpret_cast<const uint32_t*>(s + p.idx_off) + cfg.pay_off;
+        const float* val = reinterpret_cast<const float*>(s + p.val_off) + cfg.pay_off;
+        if (tid < 2) {     // lower_bound(lo) and lower_bound(hi)
+            const unsigned long long key = tid == 0 ? lo : hi;
+            long long a = 0, b = kept;
+            while (a < b) {
+                const long long m = (a + b) >> 1;
+                if ((unsigned long long)idx[m] < key) a = m + 1; else b = m;
+            }
+            sh_rng[tid] = (int)a;
+        }
+        __syncthreads();
+        const int e0 = sh_rng[0], e1 = sh_rng[1];
+        for (int e = e0 + tid; e < e1; e += kThreads) acc[idx[e] - (uint32_t)lo] += val[e];
+        __syncthreads();
+    }
+    const float inv = 1.0f / (float)p.world;
+    OutT* o = reinterpret_cast<OutT*>(t.out) + c.start;
+    const bool ov = vec_ok(o);
+    for (int it = 0; it < kQuadsPerThread; ++it) {
+        const int j = (it * kThreads + tid) * 4;
+        if (j >= c.len) break;
+        float v[4];
+#pragma unroll
+        for (int k = 0; k < 4; ++k) v[k] = (j + k < c.len) ? acc[j + k] * inv : 0.0f;
+        store_quad<OutT>(o, j, c.len, ov, v);
+    }
+}
+
+// ---- quantisers and the dense path -------------------------------------------------------------------
+// Code area of chunk ci inside a slot: code_off + ci * code_stride.
+//   dense    : raw GradT values
+//   TernGrad : 2 bits per element (0 = zero, 1 = +s, 2 = -s), 4 elements per byte
+//   dithering: one level byte per element followed by one sign bit per element
+__device__ __forceinline__ void quad_uniforms(const DevPlan& p, const TensorRec& t, long long i, long long gidx,
+                                              uint64_t salt, float u[4]) {
+    if (t.rnd) {
+        const float* r = reinterpret_cast<const float*>(t.rnd);
+#pragma unroll
+        for (int k = 0; k < 4; ++k) u[k] = (i + k < t.n) ? r[i + k] : 0.0f;
+        return;
+    }
+    const uint64_t q = (uint64_t)gidx >> 2;
+    const uint4 w = philox4x32_10(make_uint4((uint32_t)q, (uint32_t)(q >> 32), (uint32_t)p.step, (uint32_t)(p.step >> 32)),
+                                  make_uint2((uint32_t)salt, (uint32_t)(salt >> 32)));
+    u[0] = u32_to_unit(w.x); u[1] = u32_to_unit(w.y); u[2] = u32_to_unit(w.z); u[3] = u32_to_unit(w.w);
+}
+
+template <typename GradT>
+__global__ void __launch_bounds__(kThreads) k_quant_send(DevPlan p) {
+    const ChunkRec c = p.chunks[blockIdx.x];
+    const TensorRec t = p.tensors[c.tensor];
+    const GroupCfg cfg = p.gcfg[t.group];
+    const GroupState& gs = p.gstate[t.group];
+    const int tid = threadIdx.x, lane = tid & 31;
+    const float scale = gs.scale;
+    const float qf = (float)p.qstates;
+    const uint64_t salt = group_salt(p, cfg.uid);
+    const unsigned long long coff = p.code_off + (unsigned long long)blockIdx.x * p.code_stride;
+
+    if ((int)blockIdx.x == cfg.chunk_begin && tid < p.world) {
+        float* hdr = reinterpret_cast<float*>(slot_ptr(p, tid, p.rank));
+        hdr[t.group] = scale;
+    }
+    for (int it = 0; it < kQuadsPerThread; ++it) {
+        const int q = it * kThreads + tid;
+        const int j = q * 4;
+        if (it * kThreads * 4 >= c.len) break;      // whole warp-row beyond the chunk (uniform)
+        float v[4] = {0.f, 0.f, 0.f, 0.f};
+        if (j < c.len) load_acc<GradT>(t, c.start, j, c.len, v);
+        if (p.method == LWC_NONE) {
+            if (j < c.len) {
+                for (int d = 0; d < p.world; ++d) {
+                    GradT* dst = reinterpret_cast<GradT*>(slot_ptr(p, d, p.rank) + coff);
+                    store_quad<GradT>(dst, j, c.len, true, v);
+                }
+            }
+            continue;
+        }
+        float u[4] = {1.f, 1.f, 1.f, 1.f};
+        if (j < c.len) quad_uniforms(p, t, c.start + j, t.goff + c.start + j, salt, u);
+        float deq[4];
+        unsigned code = 0, sign = 0;
+        if (p.method == LWC_TERNGRAD) {
+#pragma unroll
+            for (int k = 0; k < 4; ++k) {
+                const float a = fabsf(v[k]);
+                const bool b = (scale > 0.0f) && (u[k] < __fdiv_rn(a, scale)) && (j + k < c.len);
+                const unsigned cde = b ? (v[k] < 0.0f ? 2u : 1u) : 0u;
+                code |= cde << (2 * k);
+                deq[k] = b ? (v[k] < 0.0f ? -scale : scale) : 0.0f;
+            }
+            // four lanes -> one 32-bit word (16 elements)
+            unsigned word = code << (8 * (lane & 3));
+            word |= __shfl_xor_sync(0xffffffffu, word, 1);
+            word |= __shfl_xor_sync(0xffffffffu, word, 2);
+            if ((lane & 3) == 0 && j < c.len) {
+                for (int d = 0; d < p.world; ++d)
+                    reinterpret_cast<uint32_t*>(slot_ptr(p, d, p.rank) + coff)[q >> 2] = word;
+            }
+        } else {   // LWC_DITHERING
+#pragma unroll
+            for (int k = 0; k < 4; ++k) {
+                float level = 0.0f;
+                if (scale > 0.0f && j + k < c.len)
+                    level = floorf(__fadd_rn(__fmul_rn(__fdiv_rn(fabsf(v[k]), scale), qf), u[k]));
+                level = fminf(level, 255.0f);
+                code |= ((unsigned)level) << (8 * k);
+                sign |= (v[k] < 0.0f ? 1u : 0u) << k;
+                const float mag = __fmul_rn(scale, __fdiv_rn(level, qf));
+                deq[k] = v[k] < 0.0f ? -mag : (v[k] > 0.0f ? mag : 0.0f);
+            }
+            // eight lanes -> one 32-bit word of sign bits (32 elements)
+            unsigned sw = sign << (4 * (lane & 7));
+            sw |= __shfl_xor_sync(0xffffffffu, sw, 1);
+            sw |= __shfl_xor_sync(0xffffffffu, sw, 2);
+            sw |= __shfl_xor_sync(0xffffffffu, sw, 4);
+            if (j < c.len) {
+                for (int d = 0; d < p.world; ++d) {
+                    char* base = slot_ptr(p, d, p.rank) + coff;
+                    reinterpret_cast<uint32_t*>(base)[q] = code;
+                    if ((lane & 7) == 0) reinterpret_cast<uint32_t*>(base + kChunk)[q >> 3] = sw;
+                }
+            }
+        }
+        if (t.resid && j < c.len) {
+            float e[4];
+#pragma unroll
+            for (int k = 0; k < 4; ++k) e[k] = v[k] - deq[k];
+            float* r = t.resid + c.start;
+            store_quad<float>(r, j, c.len, vec_ok(r), e);
+        }
+    }
+    publish_when_last(p);
+}
+
+template <typename GradT, typename OutT>
+__global__ void __launch_bounds__(kThreads) k_recv_dense(DevPlan p) {
+    const ChunkRec c = p.chunks[blockIdx.x];
+    const TensorRec t = p.tensors[c.tensor];
+    const int tid = threadIdx.x;
+    const float qf = (float)p.qstates;
+    const unsigned long long coff = p.code_off + (unsigned long long)blockIdx.x * p.code_stride;
+    wait_sources(p);
+    const float inv = 1.0f / (float)p.world;
+    OutT* o = reinterpret_cast<OutT*>(t.out) + c.start;
+    const bool ov = vec_ok(o);
+    for (int it = 0; it < kQuadsPerThread; ++it) {
+        const int q = it * kThreads + tid;
+        const int j = q * 4;
+        if (j >= c.len) break;
+        float sum[4] = {0.f, 0.f, 0.f, 0.f};
+        for (int src = 0; src < p.world; ++src) {
+            const char* s = slot_ptr(p, p.rank, src);
+            const char* base = s + coff;
+            if (p.method == LWC_NONE) {
+                float v[4];
+                load_quad<GradT>(reinterpret_cast<const GradT*>(base), j, c.len, true, v);
+#pragma unroll
+                for (int k = 0; k < 4; ++k) sum[k] += v[k];
+            } else {
+                const float scale = reinterpret_cast<const float*>(s)[t.group];
+                if (p.method == LWC_TERNGRAD) {
+                    const unsigned code = reinterpret_cast<const uint8_t*>(base)[q];
+#pragma unroll
+                    for (int k = 0; k < 4; ++k) {
+                        const unsigned cde = (code >> (2 * k)) & 3u;
+                        sum[k] += cde == 1u ? scale : (cde == 2u ? -scale : 0.0f);
+                    }
+                } else {
+                    const unsigned code = reinterpret_cast<const uint32_t*>(base)[q];
+                    const unsigned sb = (reinterpret_cast<const uint8_t*>(base + kChunk)[q >> 1] >> (4 * (q & 1))) & 0xfu;
+#pragma unroll
+                    for (int k = 0; k < 4; ++k) {
+                        const float level = (float)((code >> (8 * k)) & 0xffu);
+                        const float mag = __fmul_rn(scale, __fdiv_rn(level, qf));
+                        sum[k] += ((sb >> k) & 1u) ? -mag : mag;
+                    }
+                }
+            }
+        }
+#pragma unroll
+        for (int k = 0; k < 4; ++k) sum[k] *= inv;
+        store_quad<OutT>(o, j, c.len, ov, sum);
+    }
+}
+
+}  // namespace lwc
+
+// =====================================================================================================
+// Host side
+// =====================================================================================================
+using namespace lwc;
+
+struct LwcPlan {
+    DevPlan dev;
+    int num_tensors;
+    int grad_dtype, out_dtype;
+    bool any_resid;
+    bool bound;
+    size_t state_bytes;
+    std::vector<TensorRec> h_tensors;
+    void* d_tensors = nullptr;
+    void* d_chunks = nullptr;
+    void* d_gcfg = nullptr;
+    void* d_gstate = nullptr;
+    void* d_chunk_cnt = nullptr;
+    void* d_chunk_off = nullptr;
+    void* d_chunk_part = nullptr;
+    void* d_counters = nullptr;
+};
+
+static size_t align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
+static size_t dtype_size(int dt) { return dt == LWC_F32 ? 4 : 2; }
+
+extern "C" int lwc_plan_create(LwcPlan** out, const LwcPlanDesc* d) {
+    if (!out || !d || d->num_tensors <= 0 || d->num_groups <= 0) return LWC_EINVAL;
+    if (d->world < 1 || d->world > LWC_MAX_WORLD || d->rank < 0 || d->rank >= d->world) return LWC_EINVAL;
+    if (d->method < LWC_NONE || d->method > LWC_DITHERING) return LWC_EINVAL;
+    if (d->method == LWC_DITHERING && (d->qstates < 1 || d->qstates > 255)) return LWC_EINVAL;
+    LwcPlan* P = new LwcPlan();
+    P->num_tensors = d->num_tensors;
+    P->grad_dtype = d->grad_dtype;
+    P->out_dtype = d->out_dtype;
+    P->bound = false;
+    P->any_resid = false;
+    const int G = d->num_groups;
+    std::vector<GroupCfg> gcfg(G);
+    for (int g = 0; g < G; ++g) {
+        gcfg[g] = GroupCfg{0, d->keep ? d->keep[g] : 0, d->cap ? d->cap[g] : 0, 0, 0, 0, 0, 0};
+    }
+    std::vector<ChunkRec> chunks;
+    P->h_tensors.resize(d->num_tensors);
+    int prev_group = -1;
+    for (int t = 0; t < d->num_tensors; ++t) {
+        const int g = d->group_of[t];
+        if (g < prev_group || g >= G || g > prev_group + 1) { delete P; return LWC_EINVAL; }
+        TensorRec& r = P->h_tensors[t];
+        r.grad = d->grad_dev[t];
+        r.out = d->out_dev[t];
+        r.resid = (d->resid_dev && d->method != LWC_NONE) ? d->resid_dev[t] : nullptr;
+        r.rnd = nullptr;
+        r.n = d->numel[t];
+        r.goff = gcfg[g].n;
+        r.group = g;
+        r.uid = d->uid ? d->uid[t] : t;
+        if (r.resid) P->any_resid = true;
+        if (g != prev_group) {
+            gcfg[g].chunk_begin = (int)chunks.size();
+            gcfg[g].uid = r.uid;
+            prev_group = g;
+        }
+        for (long long s = 0; s < r.n; s += kChunk) {
+            ChunkRec c;
+            c.tensor = t;
+            c.start = s;
+            c.len = (int)((r.n - s) < kChunk ? (r.n - s) : kChunk);
+            chunks.push_back(c);
+        }
+        gcfg[g].n += r.n;
+        gcfg[g].chunk_end = (int)chunks.size();
+        if (gcfg[g].n > 0xffffffffLL) { delete P; return LWC_ETOOBIG; }
+    }
+    if (prev_group != G - 1 || chunks.empty()) { delete P; return LWC_EINVAL; }
+    long long pay = 0;
+    for (int g = 0; g < G; ++g) {
+        gcfg[g].pay_off = pay;
+        if (gcfg[g].cap > gcfg[g].n) gcfg[g].cap = gcfg[g].n;
+        pay += (gcfg[g].cap + 3) / 4 * 4;
+    }
+    DevPlan& D = P->dev;
+    memset(&D, 0, sizeof(D));
+    D.num_chunks = (int)chunks.size();
+    D.num_groups = G;
+    D.method = d->method;
+    D.world = d->world;
+    D.rank = d->rank;
+    D.qstates = d->qstates;
+    D.threshold = d->threshold;
+    D.seed = d->seed;
+    const bool sparse = d->method >= LWC_TOPK && d->method <= LWC_ADAPTIVE;
+    D.hdr_bytes = align_up((size_t)G * 8, 256);
+    if (sparse) {
+        D.idx_off = D.hdr_bytes;
+        D.val_off = D.idx_off + align_up((size_t)pay * 4, 256);
+        D.slot_bytes = D.val_off + align_up((size_t)pay * 4, 256);
+    } else {
+        D.code_off = D.hdr_bytes;
+        D.code_stride = d->method == LWC_NONE ? (size_t)kChunk * dtype_size(d->grad_dtype)
+                        : d->method == LWC_TERNGRAD ? kChunk / 4 : kChunk + kChunk / 8;
+        D.slot_bytes = D.code_off + (size_t)D.num_chunks * D.code_stride;
+    }
+    P->state_bytes = sizeof(GroupState) * (size_t)G;
+    cudaError_t e = cudaSuccess;
+    auto alloc = [&](void** p, size_t bytes) { if (e == cudaSuccess) e = cudaMalloc(p, bytes ? bytes : 16); };
+    alloc(&P->d_tensors, sizeof(TensorRec) * P->h_tensors.size());
+    alloc(&P->d_chunks, sizeof(ChunkRec) * chunks.size());
+    alloc(&P->d_gcfg, sizeof(GroupCfg) * G);
+    alloc(&P->d_gstate, P->state_bytes);
+    alloc(&P->d_chunk_cnt, sizeof(unsigned) * chunks.size());
+    alloc(&P->d_chunk_off, sizeof(unsigned long long) * chunks.size());
+    alloc(&P->d_chunk_part, sizeof(float) * chunks.size());
+    alloc(&P->d_counters, sizeof(Counters));
+    if (e == cudaSuccess) e = cudaMemcpy(P->d_tensors, P->h_tensors.data(), sizeof(TensorRec) * P->h_tensors.size(), cudaMemcpyHostToDevice);
+    if (e == cudaSuccess) e = cudaMemcpy(P->d_chunks, chunks.data(), sizeof(ChunkRec) * chunks.size(), cudaMemcpyHostToDevice);
+    if (e == cudaSuccess) e = cudaMemcpy(P->d_gcfg, gcfg.data(), sizeof(GroupCfg) * G, cudaMemcpyHostToDevice);
+    if (e == cudaSuccess) e = cudaMemset(P->d_gstate, 0, P->state_bytes);
+    if (e == cudaSuccess) e = cudaMemset(P->d_counters, 0, sizeof(Counters));
+    if (e != cudaSuccess) { lwc_plan_destroy(P); return (int)e; }
+    D.tensors = (const TensorRec*)P->d_tensors;
+    D.chunks = (const ChunkRec*)P->d_chunks;
+    D.gcfg = (const GroupCfg*)P->d_gcfg;
+    D.gstate = (GroupState*)P->d_gstate;
+    D.chunk_cnt = (unsigned*)P->d_chunk_cnt;
+    D.chunk_off = (unsigned long long*)P->d_chunk_off;
+    D.chunk_part = (float*)P->d_chunk_part;
+    D.counters = (Counters*)P->d_counters;
+    *out = P;
+    return 0;
+}
+
+extern "C" int lwc_plan_destroy(LwcPlan* P) {
+    if (!P) return 0;
+    cudaFree(P->d_tensors); cudaFree(P->d_chunks); cudaFree(P->d_gcfg); cudaFree(P->d_gstate);
+    cudaFree(P->d_chunk_cnt); cudaFree(P->d_chunk_off); cudaFree(P->d_chunk_part); cudaFree(P->d_counters);
+    delete P;
+    return 0;
+}
+
+extern "C" size_t lwc_plan_slot_bytes(const LwcPlan* P) { return P ? (size_t)P->dev.slot_bytes : 0; }
+extern "C" size_t lwc_plan_region_bytes(const LwcPlan* P) {
+    return P ? (size_t)P->dev.slot_bytes * 2 * P->dev.world : 0;
+}
+
+extern "C" int lwc_plan_bind(LwcPlan* P, void* const* region_dev, void* const* flags_dev) {
+    if (!P || !region_dev || !flags_dev) return LWC_EINVAL;
+    for (int d = 0; d < P->dev.world; ++d) {
+        if (!region_dev[d] || !flags_dev[d]) return LWC_EINVAL;
+        P->dev.region[d] = (char*)region_dev[d];
+        P->dev.flags[d] = (uint64_t*)flags_dev[d];
+    }
+    P->bound = true;
+    return 0;
+}
+
+extern "C" int lwc_plan_set_random(LwcPlan* P, const void* const* rand_dev) {
+    if (!P) return LWC_EINVAL;
+    for (int t = 0; t < P->num_tensors; ++t) P->h_tensors[t].rnd = rand_dev ? rand_dev[t] : nullptr;
+    LWC_CUDA_CHECK(cudaMemcpy(P->d_tensors, P->h_tensors.data(), sizeof(TensorRec) * P->h_tensors.size(),
+                              cudaMemcpyHostToDevice));
+    return 0;
+}
+
+#define LWC_DISPATCH_GRAD(dt, ...)                                            \
+    switch (dt) {                                                             \
+        case LWC_F32: { using GradT = float; __VA_ARGS__; } break;            \
+        case LWC_BF16: { using GradT = __nv_bfloat16; __VA_ARGS__; } break;   \
+        case LWC_F16: { using GradT = __half; __VA_ARGS__; } break;           \
+        default: return LWC_EINVAL;                                           \
+    }
+
+extern "C" int lwc_plan_send(LwcPlan* P, uint64_t step, void* stream_) {
+    if (!P || !P->bound) return LWC_ESTATE;
+    cudaStream_t st = (cudaStream_t)stream_;
+    DevPlan D = P->dev;
+    D.step = step;
+    const int NC = D.num_chunks, G = D.num_groups, m = D.method;
+    LWC_CUDA_CHECK(cudaMemsetAsync(P->d_gstate, 0, P->state_bytes, st));
+    switch (m) {
+        case LWC_TOPK:
+        case LWC_RANDOMK:
+            LWC_DISPATCH_GRAD(P->grad_dtype, k_pre<GradT, STAT_HIST><<<NC, kThreads, 0, st>>>(D));
+            k_group<<<G, kThreads, 0, st>>>(D, G_SCAN1);
+            LWC_DISPATCH_GRAD(P->grad_dtype, k_hist<GradT, 2><<<NC, kThreads, 0, st>>>(D));
+            k_group<<<G, kThreads, 0, st>>>(D, G_SCAN2);
+            LWC_DISPATCH_GRAD(P->grad_dtype, k_hist<GradT, 3><<<NC, kThreads, 0, st>>>(D));
+            k_group<<<G, kThreads, 0, st>>>(D, G_SCAN3);
+            break;
+        case LWC_THRESHOLDV:
+            if (P->any_resid) { LWC_DISPATCH_GRAD(P->grad_dtype, k_pre<GradT, STAT_NONE><<<NC, kThreads, 0, st>>>(D)); }
+            k_group<<<G, kThreads, 0, st>>>(D, G_SET_THRESH);
+            break;
+        case LWC_ADAPTIVE:
+            LWC_DISPATCH_GRAD(P->grad_dtype, k_pre<GradT, STAT_MAX><<<NC, kThreads, 0, st>>>(D));
+            k_group<<<G, kThreads, 0, st>>>(D, G_SET_ADAPT);
+            break;
+        case LWC_TERNGRAD:
+            LWC_DISPATCH_GRAD(P->grad_dtype, k_pre<GradT, STAT_MAX><<<NC, kThreads, 0, st>>>(D));
+            k_group<<<G, kThreads, 0, st>>>(D, G_FIN_MAX);
+            break;
+        case LWC_DITHERING:
+            LWC_DISPATCH_GRAD(P->grad_dtype, k_pre<GradT, STAT_SUMSQ><<<NC, kThreads, 0, st>>>(D));
+            k_group<<<G, kThreads, 0, st>>>(D, G_FIN_NORM);
+            break;
+        default: break;
+    }
+    if (m >= LWC_TOPK && m <= LWC_ADAPTIVE) {
+        LWC_DISPATCH_GRAD(P->grad_dtype, k_count<GradT><<<NC, kThreads, 0, st>>>(D));
+        k_group<<<G, kThreads, 0, st>>>(D, G_SCAN_COUNTS);
+        LWC_DISPATCH_GRAD(P->grad_dtype, k_compact_send<GradT><<<NC, kThreads, 0, st>>>(D));
+    } else {
+        LWC_DISPATCH_GRAD(P->grad_dtype, k_quant_send<GradT><<<NC, kThreads, 0, st>>>(D));
+    }
+    return (int)cudaGetLastError();
+}
+
+template <typename GradT>
+static int launch_recv_dense(const DevPlan& D, int out_dtype, cudaStream_t st) {
+    switch (out_dtype) {
+        case LWC_F32: k_recv_dense<GradT, float><<<D.num_chunks, kThreads, 0, st>>>(D); break;
+        case LWC_BF16: k_recv_dense<GradT, __nv_bfloat16><<<D.num_chunks, kThreads, 0, st>>>(D); break;
+        case LWC_F16: k_recv_dense<GradT, __half><<<D.num_chunks, kThreads, 0, st>>>(D); break;
+        default: return LWC_EINVAL;
+    }
+    return 0;
+}
+
+extern "C" int lwc_plan_recv(LwcPlan* P, uint64_t step, void* stream_) {
+    if (!P || !P->bound) return LWC_ESTATE;
+    cudaStream_t st = (cudaStream_t)stream_;
+    DevPlan D = P->dev;
+    D.step = step;
+    const int m = D.method;
+    if (m >= LWC_TOPK && m <= LWC_ADAPTIVE) {
+        switch (P->out_dtype) {
+            case LWC_F32: k_recv_sparse<float><<<D.num_chunks, kThreads, 0, st>>>(D); break;
+            case LWC_BF16: k_recv_sparse<__nv_bfloat16><<<D.num_chunks, kThreads, 0, st>>>(D); break;
+            case LWC_F16: k_recv_sparse<__half><<<D.num_chunks, kThreads, 0, st>>>(D); break;
+            default: return LWC_EINVAL;
+        }
+    } else {
+        int rc = 0;
+        LWC_DISPATCH_GRAD(P->grad_dtype, rc = launch_recv_dense<GradT>(D, P->out_dtype, st));
+        if (rc) return rc;
+    }
+    return (int)cudaGetLastError();
+}
+
+extern "C" int lwc_plan_stats(LwcPlan* P, uint64_t out[4], void* stream_) {
+    if (!P || !out) return LWC_EINVAL;
+    Counters c;
+    cudaStream_t st = (cudaStream_t)stream_;
+    LWC_CUDA_CHECK(cudaMemcpyAsync(&c, P->d_counters, sizeof(c), cudaMemcpyDeviceToHost, st));
+    LWC_CUDA_CHECK(cudaStreamSynchronize(st));
+    out[0] = c.sent; out[1] = c.dropped; out[2] = c.timeouts;
+    const bool sparse = P->dev.method >= LWC_TOPK && P->dev.method <= LWC_ADAPTIVE;
+    out[3] = sparse ? c.sent * 8 : (uint64_t)(P->dev.slot_bytes - P->dev.hdr_bytes);
+    return 0;
+}
+
+
+// =====================================================================================================
+// Stand-alone exact Top-k selection of one fp32 vector, scratch supplied by the caller.
+// =====================================================================================================
+namespace lwc {
+struct TopkHeader {
+    TensorRec t;
+    GroupCfg g;
+    Counters c;
+    GroupState gs;
+};
+__host__ __device__ inline size_t topk_align(size_t x) { return (x + 255) / 256 * 256; }
+struct TopkLayout {
+    size_t chunks, cnt, off, total;
+    __host__ __device__ explicit TopkLayout(long long n) {
+        const size_t nc = (size_t)((n + kChunk - 1) / kChunk);
+        chunks = topk_align(sizeof(TopkHeader));
+        cnt = chunks + topk_align(nc * sizeof(ChunkRec));
+        off = cnt + topk_align(nc * sizeof(unsigned));
+        total = off + topk_align(nc * sizeof(unsigned long long));
+    }
+};
+__global__ void k_topk_init(char* ws, const float* x, long long n, long long keep, long long cap) {
+    const TopkLayout L(n);
+    const int nc = (int)((n + kChunk - 1) / kChunk);
+    TopkHeader* H = reinterpret_cast<TopkHeader*>(ws);
+    ChunkRec* ch = reinterpret_cast<ChunkRec*>(ws + L.chunks);
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < nc) {
+        const long long s = (long long)i * kChunk;
+        ch[i].tensor = 0;
+        ch[i].start = s;
+        ch[i].len = (int)((n - s) < kChunk ? (n - s) : kChunk);
+    }
+    if (i == 0) {
+        H->t = TensorRec{x, nullptr, nullptr, nullptr, n, 0, 0, 0};
+        H->g = GroupCfg{n, keep, cap < n ? cap : n, 0, 0, nc, 0, 0};
+        H->c = Counters{0, 0, 0, 0, 0, 0};
+    }
+}
+}  // namespace lwc
+
+extern "C" size_t lwc_topk_workspace_bytes(int64_t n) {
+    if (n <= 0) return 0;
+    return TopkLayout(n).total;
+}
+
+// Shared by the public entry point (caller-provided scratch) and any variant that brings its own.
+int lwc_topk_select_impl(const float* x, int64_t n, int64_t keep, int64_t cap, uint32_t* idx_out, float* val_out,
+                         int64_t* count_out, void* ws_, cudaStream_t st) {
+    if (!x || !idx_out || !val_out || !count_out || !ws_ || n <= 0 || keep < 0 || cap <= 0) return LWC_EINVAL;
+    if (n > 0xffffffffLL) return LWC_ETOOBIG;
+    char* ws = (char*)ws_;
+    const TopkLayout L(n);
+    const int nc = (int)((n + kChunk - 1) / kChunk);
+    TopkHeader* H = reinterpret_cast<TopkHeader*>(ws);
+    LWC_CUDA_CHECK(cudaMemsetAsync(&H->gs, 0, sizeof(GroupState), st));
+    k_topk_init<<<(nc + 255) / 256, 256, 0, st>>>(ws, x, n, keep, cap);
+    DevPlan D;
+    memset(&D, 0, sizeof(D));
+    D.tensors = &H->t;
+    D.chunks = reinterpret_cast<const ChunkRec*>(ws + L.chunks);
+    D.gcfg = &H->g;
+    D.gstate = &H->gs;
+    D.chunk_cnt = reinterpret_cast<unsigned*>(ws + L.cnt);
+    D.chunk_off = reinterpret_cast<unsigned long long*>(ws + L.off);
+    D.chunk_part = nullptr;
+    D.counters = &H->c;
+    D.num_chunks = nc;
+    D.num_groups = 1;
+    D.method = LWC_TOPK;
+    D.world = 1;
+    D.rank = 0;
+    D.direct_idx = idx_out;
+    D.direct_val = val_out;
+    D.direct_count = reinterpret_cast<long long*>(count_out);
+    k_pre<float, STAT_HIST><<<nc, kThreads, 0, st>>>(D);
+    k_group<<<1, kThreads, 0, st>>>(D, G_SCAN1);
+    k_hist<float, 2><<<nc, kThreads, 0, st>>>(D);
+    k_group<<<1, kThreads, 0, st>>>(D, G_SCAN2);
+    k_hist<float, 3><<<nc, kThreads, 0, st>>>(D);
+    k_group<<<1, kThreads, 0, st>>>(D, G_SCAN3);
+    k_count<float><<<nc, kThreads, 0, st>>>(D);
+    k_group<<<1, kThreads, 0, st>>>(D, G_SCAN_COUNTS);
+    k_compact_send<float><<<nc, kThreads, 0, st>>>(D);
+    return (int)cudaGetLastError();
+}
+
+extern "C" int lwc_topk_select_f32(const float* x_dev, int64_t n, int64_t keep, int64_t cap, uint32_t* idx_out_dev,
+                                   float* val_out_dev, int64_t* count_out_dev, void* workspace_dev, void* stream) {
+    return lwc_topk_select_impl(x_dev, n, keep, cap, idx_out_dev, val_out_dev, count_out_dev, workspace_dev,
+                                (cudaStream_t)stream);
+}

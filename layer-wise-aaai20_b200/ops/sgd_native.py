@@ -1,0 +1,82 @@
+"""Launch glue for the fused multi-tensor SGD kernel (``csrc/sgd.cu``)."""
+from __future__ import annotations
+
+import ctypes as C
+
+import torch
+
+from .. import _native
+from .._native import abi
+
+
+class _Plan:
+    def __init__(self, key, handle, grad_dtype, model_dtype):
+        self.key, self.handle, self.grad_dtype, self.model_dtype = key, handle, grad_dtype, model_dtype
+
+
+def _build(opt, params, bufs):
+    lib = _native.lib()
+    n = len(params)
+    arr = (abi.LwcSgdTensor * n)()
+    model_dtype = None
+    for i, p in enumerate(params):
+        model = opt._model_copy.get(id(p))
+        arr[i].param = p.data_ptr()
+        arr[i].grad = p.grad.data_ptr()
+        arr[i].mom = 0 if bufs is None else bufs[i].data_ptr()
+        arr[i].model = 0 if model is None else model.data_ptr()
+        arr[i].n = p.numel()
+        if model is not None:
+            model_dtype = model.dtype
+    handle = C.c_void_p()
+    abi.check(lib.lwc_sgd_plan_create(C.byref(handle), arr, n), "lwc_sgd_plan_create")
+    return handle, model_dtype
+
+
+def _same_dense_layout(p, g) -> bool:
+    if p.stride() != g.stride() or p.size() != g.size():
+        return False
+    return p.is_contiguous() or (p.dim() == 4 and p.is_contiguous(memory_format=torch.channels_last))
+
+
+def step_group(opt, gi, group, params):
+    """One fused launch per (dtype) subset of a param group."""
+    lib = _native.lib()
+    mu = group["momentum"]
+    # split by (param dtype must be fp32), grad dtype
+    subsets = {}
+    for p in params:
+        if p.dtype != torch.float32 or not _same_dense_layout(p, p.grad):
+            opt._step_reference(group, [p])
+            continue
+        subsets.setdefault(p.grad.dtype, []).append(p)
+    for gdt, ps in subsets.items():
+        first = False
+        bufs = None
+        if mu != 0:
+            bufs = []
+            for p in ps:
+                st = opt.state[p]
+                if "momentum_buffer" not in st or st["momentum_buffer"] is None:
+                    st["momentum_buffer"] = torch.zeros_like(p, memory_format=torch.preserve_format)
+                    first = True
+                bufs.append(st["momentum_buffer"])
+        key = (gi, gdt) + tuple(p.data_ptr() for p in ps) + tuple(p.grad.data_ptr() for p in ps) + \
+            (tuple(b.data_ptr() for b in bufs) if bufs else ())
+        plan = opt._plans.get((gi, gdt))
+        if plan is None or plan.key != key:
+            if plan is not None:
+                lib.lwc_sgd_plan_destroy(plan.handle)
+            handle, mdt = _build(opt, ps, bufs)
+            plan = _Plan(key, handle, gdt, mdt)
+            opt._plans[(gi, gdt)] = plan
+        d = abi.LwcSgdDesc()
+        d.num_tensors = len(ps)
+        d.grad_dtype = abi.dtype_code(gdt)
+        d.model_dtype = abi.dtype_code(plan.model_dtype) if plan.model_dtype is not None else abi.LWC_F32
+        d.lr, d.momentum, d.dampening = float(group["lr"]), float(mu), float(group["dampening"])
+        d.weight_decay, d.grad_scale = float(group["weight_decay"]), float(opt.grad_scale)
+        d.nesterov, d.first_step = int(bool(group["nesterov"])), int(first)
+        st = torch.cuda.current_stream().cuda_stream
+        abi.check(lib.lwc_sgd_step(plan.handle, C.byref(d), C.c_void_p(st)), "lwc_sgd_step")
+        _native.counters.add(1)

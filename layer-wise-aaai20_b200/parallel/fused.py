@@ -1,0 +1,377 @@
+"""Fused CUDA exchange engine (B200): plans, buckets, streams, hooks.
+
+``ExchangePlan`` wraps one native plan (``csrc/exchange.cu``): a bucket of gradient tensors
+whose compress -> pack -> peer-store -> flag -> receive -> scatter-add/dequantise pipeline
+runs as a fixed, short launch sequence with no host synchronisation.
+
+``FusedEngine`` owns the gradient arena (every ``p.grad`` is a view into one flat buffer
+per dtype, so "flattening" the model gradient costs nothing -- the reference concatenates
+and re-slices every step, CIFAR10/core.py:229-236,:292-301), the fp32 error-feedback
+arena, the peer heap with receive slots, and the bucket schedule.  With ``overlap=True`` it
+registers post-accumulate-grad hooks and launches each bucket's send on a side stream the
+moment its last gradient is produced, in reverse parameter order -- the role of the
+reference's hook-driven DDP wrappers (IMAGENET/training/sparsified_ddp.py:383-450) for
+every compressor, not only Random-k.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import math
+from typing import Dict, List, Optional, Sequence
+
+import torch
+import torch.distributed as dist
+
+from .. import _native
+from .._native import abi
+from ..ops import compress_ref as cref
+from . import comm
+from .peer import DeviceBuffer, LocalWorld, PeerHeap
+
+FLAG_BYTES = abi.LWC_MAX_WORLD * 8
+
+
+def _ptr_array(ptrs: Sequence[int]):
+    arr = (C.c_void_p * len(ptrs))()
+    for i, p in enumerate(ptrs):
+        arr[i] = p
+    return arr
+
+
+def keep_and_cap(method: str, n: int, cfg) -> (int, int):
+    """Per-group keep count and payload capacity (entries)."""
+    if method == cref.TOPK:
+        keep = cref.topk_keep_count(n, cfg.ratio)
+        cap = min(n, int(math.ceil(keep * cfg.capacity_factor)) + 64)
+    elif method == cref.RANDOMK:
+        keep = cref.randomk_keep_count(n, cfg.ratio)
+        cap = keep
+    elif method in (cref.THRESHOLDV, cref.ADAPTIVE):
+        keep = 0
+        cap = min(n, max(int(math.ceil(n * cfg.dense_capacity)), 1024))
+    else:
+        keep, cap = 0, 0
+    return max(keep, 0), max(cap, 1)
+
+
+class ExchangePlan:
+    """One native plan.  ``grads/outs/resids`` are flat tensors with stable addresses."""
+
+    def __init__(self, grads: List[torch.Tensor], outs: List[torch.Tensor],
+                 resids: Optional[List[Optional[torch.Tensor]]], cfg, world: int, rank: int,
+                 entire: bool, uids: Optional[List[int]] = None):
+        self.lib = _native.lib()
+        self.cfg, self.world, self.rank = cfg, world, rank
+        self.method = cfg.method_name
+        T = len(grads)
+        self.keepalive = (grads, outs, resids)
+        numel = [int(g.numel()) for g in grads]
+        if entire:
+            group_of = [0] * T
+            gsize = [sum(numel)]
+        else:
+            group_of = list(range(T))
+            gsize = numel
+        kc = [keep_and_cap(self.method, n, cfg) for n in gsize]
+        self.keep = [k for k, _ in kc]
+        self.cap = [c for _, c in kc]
+        d = abi.LwcPlanDesc()
+        d.num_tensors, d.num_groups = T, len(gsize)
+        d.method = abi.METHOD_CODES[self.method]
+        d.grad_dtype = abi.dtype_code(grads[0].dtype)
+        d.out_dtype = abi.dtype_code(outs[0].dtype)
+        d.world, d.rank = world, rank
+        d.qstates = int(cfg.qstates or 0) if self.method == cref.DITHERING else 0
+        d.threshold = float(cfg.threshold or 0.0)
+        d.seed = int(cfg.seed) & 0xFFFFFFFFFFFFFFFF
+        self._arrs = dict(
+            grad=_ptr_array([g.data_ptr() for g in grads]),
+            out=_ptr_array([o.data_ptr() for o in outs]),
+            resid=_ptr_array([0 if (resids is None or r is None) else r.data_ptr()
+                              for r in (resids or [None] * T)]),
+            numel=(C.c_int64 * T)(*numel),
+            group_of=(C.c_int32 * T)(*group_of),
+            uid=(C.c_int32 * T)(*(uids or list(range(T)))),
+            keep=(C.c_int64 * len(gsize))(*self.keep),
+            cap=(C.c_int64 * len(gsize))(*self.cap),
+        )
+        a = self._arrs
+        d.grad_dev, d.out_dev, d.resid_dev = a["grad"], a["out"], a["resid"]
+        d.numel, d.group_of, d.uid, d.keep, d.cap = a["numel"], a["group_of"], a["uid"], a["keep"], a["cap"]
+        self.handle = C.c_void_p()
+        abi.check(self.lib.lwc_plan_create(C.byref(self.handle), C.byref(d)), "lwc_plan_create")
+        self.slot_bytes = int(self.lib.lwc_plan_slot_bytes(self.handle))
+        self.region_bytes = int(self.lib.lwc_plan_region_bytes(self.handle))
+        self.numel = sum(numel)
+        # kernels per send (the memset is not one of ours) and per receive
+        self.kernels_per_send = {cref.TOPK: 9, cref.RANDOMK: 9, cref.THRESHOLDV: 4 + int(resids is not None),
+                                 cref.ADAPTIVE: 5, cref.TERNGRAD: 3, cref.DITHERING: 3}.get(self.method, 1)
+
+    def bind(self, region_ptrs: Sequence[int], flag_ptrs: Sequence[int]):
+        abi.check(self.lib.lwc_plan_bind(self.handle, _ptr_array(region_ptrs), _ptr_array(flag_ptrs)),
+                  "lwc_plan_bind")
+
+    def set_random(self, rand: Optional[List[Optional[torch.Tensor]]]):
+        self._rand_keep = rand
+        if rand is None:
+            abi.check(self.lib.lwc_plan_set_random(self.handle, None), "lwc_plan_set_random")
+        else:
+            arr = _ptr_array([0 if r is None else r.data_ptr() for r in rand])
+            abi.check(self.lib.lwc_plan_set_random(self.handle, arr), "lwc_plan_set_random")
+
+    def send(self, step: int, stream=None):
+        st = (stream or torch.cuda.current_stream()).cuda_stream
+        abi.check(self.lib.lwc_plan_send(self.handle, C.c_uint64(step), C.c_void_p(st)), "lwc_plan_send")
+        _native.counters.add(self.kernels_per_send)
+
+    def recv(self, step: int, stream=None):
+        st = (stream or torch.cuda.current_stream()).cuda_stream
+        abi.check(self.lib.lwc_plan_recv(self.handle, C.c_uint64(step), C.c_void_p(st)), "lwc_plan_recv")
+        _native.counters.add(1)
+
+    def stats(self) -> Dict[str, int]:
+        out = (C.c_uint64 * 4)()
+        st = torch.cuda.current_stream().cuda_stream
+        abi.check(self.lib.lwc_plan_stats(self.handle, out, C.c_void_p(st)), "lwc_plan_stats")
+        return {"sent": int(out[0]), "dropped": int(out[1]), "timeouts": int(out[2]), "bytes": int(out[3])}
+
+    def close(self):
+        if self.handle:
+            self.lib.lwc_plan_destroy(self.handle)
+            self.handle = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+def bind_local_world(plans: List[ExchangePlan]) -> LocalWorld:
+    """Wire W plans (virtual ranks of one process) to each other; returns the backing heaps."""
+    W = len(plans)
+    region = max(p.region_bytes for p in plans)
+    region = (region + 255) // 256 * 256
+    lw = LocalWorld(W, region + FLAG_BYTES)
+    regions = [ptr for ptr in lw.ptrs]
+    flags = [ptr + region for ptr in lw.ptrs]
+    for p in plans:
+        p.bind(regions, flags)
+    return lw
+
+
+# --------------------------------------------------------------------------------------------------------
+class _Bucket:
+    def __init__(self, idxs: List[int]):
+        self.idxs = idxs
+        self.plan: Optional[ExchangePlan] = None
+        self.pending = 0
+        self.launched = False
+
+
+class FusedEngine:
+    name = "fused"
+
+    def __init__(self, params: List[torch.nn.Parameter], cfg, group=None, overlap: bool = False,
+                 out_dtype: Optional[torch.dtype] = None, num_buckets: Optional[int] = None):
+        _native.require()
+        self.params, self.cfg, self.group = params, cfg, group
+        self.world = comm.world_size(group)
+        self.rank = comm.rank(group)
+        if self.world > abi.LWC_MAX_WORLD:
+            raise ValueError(f"fused engine supports up to {abi.LWC_MAX_WORLD} ranks per node")
+        self.device = params[0].device
+        self.step = 0
+        self.overlap = overlap
+        dts = {p.dtype for p in params}
+        self.entire = cfg.compress == "entiremodel"
+        if self.entire and len(dts) > 1:
+            raise ValueError("entire-model mode needs all parameters in one dtype")
+        # ---- arenas: grads (per dtype) and fp32 error-feedback residuals ----------------------------
+        self._grad_arena: Dict[torch.dtype, torch.Tensor] = {}
+        self.grad_views: List[torch.Tensor] = [None] * len(params)
+        for dt in dts:
+            idx = [i for i, p in enumerate(params) if p.dtype == dt]
+            offs, total = [], 0
+            for i in idx:
+                offs.append(total)
+                total += (params[i].numel() + 63) // 64 * 64      # 256-byte aligned views (fp32)
+            arena = torch.zeros(total, dtype=dt, device=self.device)
+            self._grad_arena[dt] = arena
+            for i, o in zip(idx, offs):
+                self.grad_views[i] = arena[o:o + params[i].numel()]
+        use_ef = cfg.error_feedback and cfg.method_name != cref.NONE
+        self.resid_views: Optional[List[torch.Tensor]] = None
+        if use_ef:
+            total = sum((p.numel() + 63) // 64 * 64 for p in params)
+            self._resid_arena = torch.zeros(total, dtype=torch.float32, device=self.device)
+            self.resid_views, o = [], 0
+            for p in params:
+                self.resid_views.append(self._resid_arena[o:o + p.numel()])
+                o += (p.numel() + 63) // 64 * 64
+        self._adopt_grads()
+        # ---- buckets -----------------------------------------------------------------------------------------
+        order = list(range(len(params)))[::-1] if overlap else list(range(len(params)))
+        if self.entire:
+            buckets = [list(range(len(params)))]
+        else:
+            buckets = self._make_buckets(order, num_buckets)
+        self.buckets = [_Bucket(b) for b in buckets]
+        for b in self.buckets:
+            b.idxs = sorted(b.idxs)
+            grads = [self.grad_views[i] for i in b.idxs]
+            resids = None if self.resid_views is None else [self.resid_views[i] for i in b.idxs]
+            b.plan = ExchangePlan(grads, grads, resids, cfg, self.world, self.rank, self.entire,
+                                  uids=list(b.idxs))
+        # ---- peer heap: regions of every bucket + flag words ---------------------------------------------
+        offs, total = [], 0
+        for b in self.buckets:
+            offs.append(total)
+            total += (b.plan.region_bytes + 255) // 256 * 256
+        flag_off = total
+        total += FLAG_BYTES * len(self.buckets)
+        self.heap = PeerHeap(total, group=group, device=self.device)
+        for bi, b in enumerate(self.buckets):
+            b.plan.bind([ptr + offs[bi] for ptr in self.heap.ptrs],
+                        [ptr + flag_off + bi * FLAG_BYTES for ptr in self.heap.ptrs])
+        self.comm_stream = torch.cuda.Stream(device=self.device) if overlap else None
+        self._hooks = []
+        self._param_bucket = {}
+        if overlap:
+            for bi, b in enumerate(self.buckets):
+                for i in b.idxs:
+                    self._param_bucket[i] = bi
+            for i, p in enumerate(params):
+                self._hooks.append(p.register_post_accumulate_grad_hook(self._make_hook(i)))
+            self._reset_pending()
+
+    # ---- helpers ---------------------------------------------------------------------------------------------
+    def _make_buckets(self, order: List[int], num_buckets: Optional[int]) -> List[List[int]]:
+        by_dtype: Dict[torch.dtype, List[int]] = {}
+        for i in order:
+            by_dtype.setdefault(self.params[i].dtype, []).append(i)
+        out = []
+        for dt, idx in by_dtype.items():
+            if not self.overlap and num_buckets is None:
+                out.append(idx)
+                continue
+            total_bytes = sum(self.params[i].numel() * self.params[i].element_size() for i in idx)
+            cap = self.cfg.bucket_cap_mb * (1 << 20) if num_buckets is None else total_bytes / num_buckets
+            cur, size = [], 0
+            for i in idx:
+                nbytes = self.params[i].numel() * self.params[i].element_size()
+                if cur and size + nbytes > cap:
+                    out.append(cur)
+                    cur, size = [], 0
+                cur.append(i)
+                size += nbytes
+            if cur:
+                out.append(cur)
+        return out
+
+    def _shaped(self, i: int) -> torch.Tensor:
+        """Arena view with the parameter's own shape *and strides* (e.g. channels_last weights),
+        so that flat element k of the gradient matches flat element k of the parameter."""
+        p, v = self.params[i], self.grad_views[i]
+        dense = p.is_contiguous() or (p.dim() == 4 and p.is_contiguous(memory_format=torch.channels_last))
+        if not dense:
+            raise ValueError("fused engine needs dense parameters (contiguous or channels_last)")
+        return torch.as_strided(v, p.size(), p.stride())
+
+    def _adopt_grads(self):
+        """Make every ``p.grad`` a view of the arena (copying an existing gradient once)."""
+        for i, (p, v) in enumerate(zip(self.params, self.grad_views)):
+            g = p.grad
+            if g is not None and g.data_ptr() == v.data_ptr():
+                continue
+            shaped = self._shaped(i)
+            if g is not None:
+                shaped.copy_(g)
+            p.grad = shaped
+
+    def zero_grad(self):
+        """One memset per dtype arena instead of one launch per parameter."""
+        for arena in self._grad_arena.values():
+            arena.zero_()
+
+    # ---- after-backward mode -----------------------------------------------------------------------------
+    @torch.no_grad()
+    def exchange(self):
+        if self.overlap:
+            return self.finish()
+        self._adopt_grads()
+        for b in self.buckets:
+            b.plan.send(self.step)
+        for b in self.buckets:
+            b.plan.recv(self.step)
+        self.step += 1
+
+    # ---- hook-driven mode ----------------------------------------------------------------------------------
+    def _reset_pending(self):
+        for b in self.buckets:
+            b.pending = len(b.idxs)
+            b.launched = False
+
+    def _make_hook(self, i: int):
+        def hook(param):
+            bi = self._param_bucket[i]
+            b = self.buckets[bi]
+            if param.grad is not None and param.grad.data_ptr() != self.grad_views[i].data_ptr():
+                shaped = self._shaped(i)
+                shaped.copy_(param.grad)
+                param.grad = shaped
+            b.pending -= 1
+            if b.pending == 0 and not b.launched:
+                b.launched = True
+                self.comm_stream.wait_stream(torch.cuda.current_stream())
+                b.plan.send(self.step, self.comm_stream)
+        return hook
+
+    @torch.no_grad()
+    def finish(self):
+        """Join: launch any bucket whose hooks did not all fire, run the receivers."""
+        if not self.overlap:
+            return
+        cur = torch.cuda.current_stream()
+        self.comm_stream.wait_stream(cur)
+        for b in self.buckets:
+            if not b.launched:
+                b.plan.send(self.step, self.comm_stream)
+        for b in self.buckets:
+            b.plan.recv(self.step, self.comm_stream)
+        cur.wait_stream(self.comm_stream)
+        self.step += 1
+        self._reset_pending()
+
+    # ---- state -------------------------------------------------------------------------------------------------
+    def state_dict(self):
+        res = None if self.resid_views is None else [r.detach().cpu().clone() for r in self.resid_views]
+        return {"residual": res, "step": self.step}
+
+    def load_state_dict(self, sd):
+        # the step counter also keys the peer flags: never move it backwards on a live engine
+        self.step = max(self.step, int(sd.get("step", 0)))
+        res = sd.get("residual")
+        if res is not None and self.resid_views is not None:
+            if isinstance(res, torch.Tensor):      # entire-model flat residual from the torch engine
+                off = 0
+                for v in self.resid_views:
+                    v.copy_(res[off:off + v.numel()])
+                    off += v.numel()
+            else:
+                for v, r in zip(self.resid_views, res):
+                    v.copy_(r)
+
+    def stats(self):
+        tot = {"sent": 0, "dropped": 0, "timeouts": 0, "bytes": 0}
+        for b in self.buckets:
+            for k, v in b.plan.stats().items():
+                tot[k] += v
+        return tot
+
+    def close(self):
+        for h in self._hooks:
+            h.remove()
+        for b in self.buckets:
+            b.plan.close()
+        self.heap.close()

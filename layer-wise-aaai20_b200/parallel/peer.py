@@ -1,0 +1,121 @@
+"""Peer-memory runtime: device buffers every rank of the node can address.
+
+Each rank allocates one *heap* with ``cudaMalloc`` (through the native library, so a
+``cudaIpcMemHandle`` can be taken), publishes the handle through the process group
+(setup only -- never on the hot path), and maps the other ranks' heaps.  NVSwitch gives every
+pair of GPUs full NVLink 5 bandwidth, so there is no ring order or topology table to
+build -- contrast the reference launcher's hand-made ``NCCL_RINGS`` for V100 hybrid
+cube-mesh (IMAGENET/train.py:159-203).
+
+The heap stands in for the c10d-internal staging buffers behind
+``dist._queue_reduction`` / ``_dist_broadcast_coalesced`` that the reference's DDP
+wrappers rely on (IMAGENET/training/sparsified_ddp.py:251-254,:460).
+
+``LocalWorld`` builds the same pointer tables for W *virtual* ranks inside one process
+on one GPU; tests use it to run the multi-rank kernels without W GPUs (all sends are
+launched before any receive, so nothing ever waits on an unlaunched kernel).
+"""
+from __future__ import annotations
+
+import ctypes as C
+from typing import List, Optional
+
+import torch
+import torch.distributed as dist
+
+from .. import _native
+from .._native import abi
+
+
+class DeviceBuffer:
+    """A raw device allocation that can be viewed as torch tensors without copying."""
+
+    def __init__(self, ptr: int, nbytes: int, device: torch.device, owner: bool):
+        self.ptr, self.nbytes, self.device, self.owner = int(ptr), int(nbytes), device, owner
+
+    @classmethod
+    def allocate(cls, nbytes: int, device=None, zero: bool = True) -> "DeviceBuffer":
+        device = torch.device("cuda", torch.cuda.current_device()) if device is None else torch.device(device)
+        lib = _native.lib()
+        out = C.c_void_p()
+        with torch.cuda.device(device):
+            abi.check(lib.lwc_malloc(C.byref(out), nbytes), "lwc_malloc")
+            if zero:
+                st = torch.cuda.current_stream().cuda_stream
+                abi.check(lib.lwc_memset_async(out, 0, nbytes, C.c_void_p(st)), "lwc_memset_async")
+                torch.cuda.current_stream().synchronize()
+        return cls(out.value, nbytes, device, True)
+
+    def view(self, dtype: torch.dtype, numel: int, offset_bytes: int = 0) -> torch.Tensor:
+        esz = torch.empty((), dtype=dtype).element_size()
+        assert offset_bytes % esz == 0 and offset_bytes + numel * esz <= self.nbytes
+        typestr = {torch.float32: "<f4", torch.float16: "<f2", torch.bfloat16: "<u2", torch.uint8: "|u1",
+                   torch.int32: "<i4", torch.int64: "<i8"}[dtype]
+
+        class _Iface:
+            pass
+        obj = _Iface()
+        obj.__cuda_array_interface__ = {"shape": (numel,), "typestr": typestr,
+                                        "data": (self.ptr + offset_bytes, False), "version": 3}
+        obj._keepalive = self
+        t = torch.as_tensor(obj, device=self.device)
+        if dtype == torch.bfloat16:
+            t = t.view(torch.bfloat16)
+        return t
+
+    def ipc_handle(self) -> bytes:
+        buf = C.create_string_buffer(64)
+        abi.check(_native.lib().lwc_ipc_get_handle(C.c_void_p(self.ptr), buf), "lwc_ipc_get_handle")
+        return bytes(buf.raw)
+
+    def free(self):
+        if self.owner and self.ptr:
+            _native.lib().lwc_free(C.c_void_p(self.ptr))
+            self.ptr = 0
+
+
+class PeerHeap:
+    """One symmetric heap per rank; ``ptrs[r]`` is rank r's heap base as seen from here."""
+
+    def __init__(self, nbytes: int, group=None, device=None):
+        self.group = group
+        self.world = dist.get_world_size(group) if dist.is_initialized() else 1
+        self.rank = dist.get_rank(group) if dist.is_initialized() else 0
+        self.nbytes = int(nbytes)
+        self.local = DeviceBuffer.allocate(self.nbytes, device)
+        self.ptrs: List[int] = [0] * self.world
+        self.ptrs[self.rank] = self.local.ptr
+        self._opened: List[int] = []
+        if self.world > 1:
+            handles: List[Optional[bytes]] = [None] * self.world
+            dist.all_gather_object(handles, (self.local.ipc_handle(), self.local.device.index), group=group)
+            lib = _native.lib()
+            for r, (h, dev_index) in enumerate(handles):
+                if r == self.rank:
+                    continue
+                out = C.c_void_p()
+                abi.check(lib.lwc_ipc_open_handle(C.create_string_buffer(h, 64), C.byref(out)),
+                          f"lwc_ipc_open_handle(rank {r})")
+                self.ptrs[r] = out.value
+                self._opened.append(out.value)
+            dist.barrier(group=group)
+
+    def close(self):
+        lib = _native.lib()
+        for p in self._opened:
+            lib.lwc_ipc_close_handle(C.c_void_p(p))
+        self._opened = []
+        self.local.free()
+
+
+class LocalWorld:
+    """W virtual ranks in one process: W heaps on the current device, full pointer tables."""
+
+    def __init__(self, world: int, nbytes: int, device=None):
+        self.world = world
+        self.heaps = [DeviceBuffer.allocate(nbytes, device) for _ in range(world)]
+        self.ptrs = [h.ptr for h in self.heaps]
+
+    def close(self):
+        for h in self.heaps:
+            h.free()

@@ -1,0 +1,223 @@
+"""Fused CUDA exchange kernels vs the fp32 PyTorch oracle (single GPU, W virtual ranks)."""
+import math
+
+import pytest
+import torch
+
+import layerwise_b200  # noqa: F401
+from layerwise_b200.ops import compress_ref as cr
+from layerwise_b200.parallel.exchange import CompressionConfig
+
+pytestmark = pytest.mark.gpu
+
+SIZES = [64, 1000, 8192, 8193, 50000, 300001]
+
+
+def _world(W, sizes, cfg, entire, dtype=torch.float32, ef=False, seed=0):
+    from layerwise_b200.parallel.fused import ExchangePlan, bind_local_world
+    g = torch.Generator(device="cuda").manual_seed(seed)
+    grads = [[torch.randn(n, device="cuda", generator=g).to(dtype) for n in sizes] for _ in range(W)]
+    outs = [[torch.empty(n, device="cuda", dtype=dtype) for n in sizes] for _ in range(W)]
+    resids = [[torch.zeros(n, device="cuda") for n in sizes] if ef else None for _ in range(W)]
+    plans = [ExchangePlan(grads[r], outs[r], resids[r], cfg, W, r, entire) for r in range(W)]
+    lw = bind_local_world(plans)
+    return grads, outs, resids, plans, lw
+
+
+def _run(plans, step):
+    for p in plans:
+        p.send(step)
+    for p in plans:
+        p.recv(step)
+    torch.cuda.synchronize()
+
+
+def _oracle(grads, cfg, entire, rand=None, resids=None):
+    W = len(grads)
+    T = len(grads[0])
+    if entire:
+        flat = []
+        for r in range(W):
+            f = torch.cat([t.float() for t in grads[r]])
+            rr = None if resids is None else resids[r]
+            rd = None if rand is None else torch.cat([x for x in rand[r]])
+            flat.append(cr.compress_with_feedback(f, rr, cfg.method_name, cfg.ratio, cfg.threshold, cfg.qstates, rand=rd))
+        s = sum(flat) / W
+        out, off = [], 0
+        for t in grads[0]:
+            out.append(s[off:off + t.numel()])
+            off += t.numel()
+        return out
+    out = []
+    for i in range(T):
+        acc = 0
+        for r in range(W):
+            rr = None if resids is None else resids[r][i]
+            rd = None if rand is None else rand[r][i]
+            acc = acc + cr.compress_with_feedback(grads[r][i].float(), rr, cfg.method_name, cfg.ratio,
+                                                  cfg.threshold, cfg.qstates, rand=rd)
+        out.append(acc / W)
+    return out
+
+
+@pytest.mark.parametrize("W", [1, 2, 4])
+@pytest.mark.parametrize("entire", [False, True])
+@pytest.mark.parametrize("method,kw", [("Topk", dict(ratio=0.01)), ("Topk", dict(ratio=0.3)),
+                                       ("Thresholdv", dict(threshold=1.5)),
+                                       ("AdaptiveThreshold", {}), ("none", {})])
+def test_deterministic_methods_match_oracle(W, entire, method, kw):
+    cfg = CompressionConfig(compress="entiremodel" if entire else "layerwise", method=method,
+                            capacity_factor=1.5, dense_capacity=1.0, **kw)
+    grads, outs, _, plans, lw = _world(W, SIZES, cfg, entire)
+    _run(plans, 0)
+    exp = _oracle(grads, cfg, entire)
+    for r in range(W):
+        for e, o in zip(exp, outs[r]):
+            assert torch.allclose(e, o, atol=1e-6, rtol=1e-6)
+        for o0, o in zip(outs[0], outs[r]):
+            assert torch.equal(o0, o)        # bitwise-identical replicas
+    st = plans[0].stats()
+    assert st["dropped"] == 0 and st["timeouts"] == 0
+
+
+@pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float16])
+def test_topk_low_precision_grads_with_ties(dtype):
+    cfg = CompressionConfig(compress="layerwise", method="Topk", ratio=0.05, capacity_factor=4.0)
+    grads, outs, _, plans, lw = _world(2, [4096, 70000], cfg, False, dtype=dtype)
+    _run(plans, 0)
+    exp = _oracle(grads, cfg, False)
+    for e, o in zip(exp, outs[0]):
+        assert torch.allclose(e, o.float(), atol=2e-2, rtol=1e-2)
+    assert plans[0].stats()["dropped"] == 0
+
+
+def test_topk_zero_gradient_sends_nothing():
+    cfg = CompressionConfig(compress="layerwise", method="Topk", ratio=0.1)
+    grads, outs, _, plans, lw = _world(2, [5000], cfg, False)
+    for r in range(2):
+        grads[r][0].zero_()
+        grads[r][0][:7] = torch.arange(1.0, 8.0, device="cuda")
+    _run(plans, 0)
+    assert torch.allclose(outs[0][0], grads[0][0])     # threshold 0: everything non-zero survives
+    assert plans[0].stats()["sent"] == 7
+
+
+def test_error_feedback_multi_step_matches_oracle():
+    cfg = CompressionConfig(compress="layerwise", method="Topk", ratio=0.02, error_feedback=True,
+                            capacity_factor=2.0)
+    W, sizes = 2, [1000, 20000]
+    grads, outs, resids, plans, lw = _world(W, sizes, cfg, False, ef=True)
+    ref_res = [[torch.zeros(n, device="cuda") for n in sizes] for _ in range(W)]
+    g = torch.Generator(device="cuda").manual_seed(5)
+    for step in range(4):
+        for r in range(W):
+            for t in grads[r]:
+                t.copy_(torch.randn(t.shape, device="cuda", generator=g))
+        exp = _oracle(grads, cfg, False, resids=ref_res)
+        _run(plans, step)
+        for e, o in zip(exp, outs[0]):
+            assert torch.allclose(e, o, atol=1e-6)
+        for r in range(W):
+            for a, b in zip(ref_res[r], resids[r]):
+                assert torch.allclose(a, b, atol=1e-6)
+
+
+@pytest.mark.parametrize("entire", [False, True])
+def test_randomk_injected_keys_exact(entire):
+    cfg = CompressionConfig(compress="entiremodel" if entire else "layerwise", method="Randomk", ratio=0.03)
+    W, sizes = 2, [1000, 30000]
+    grads, outs, _, plans, lw = _world(W, sizes, cfg, entire)
+    g = torch.Generator(device="cuda").manual_seed(9)
+    keys = [[torch.randint(0, 2**31 - 1, (n,), device="cuda", generator=g, dtype=torch.int64).to(torch.int32)
+             for n in sizes] for _ in range(W)]
+    for r in range(W):
+        plans[r].set_random(keys[r])
+    _run(plans, 0)
+    exp = _oracle(grads, cfg, entire, rand=[[k.to(torch.int64) for k in keys[r]] for r in range(W)])
+    for e, o in zip(exp, outs[0]):
+        assert torch.allclose(e, o, atol=1e-6)
+
+
+def test_randomk_counter_rng_exact_count_and_shared_mask():
+    cfg = CompressionConfig(compress="layerwise", method="Randomk", ratio=0.01)
+    W, sizes = 2, [1000, 123457]
+    grads, outs, _, plans, lw = _world(W, sizes, cfg, False)
+    for r in range(W):
+        for t in grads[r]:
+            t.abs_().add_(1.0)          # no zeros
+    _run(plans, 0)
+    for n, o in zip(sizes, outs[0]):
+        assert int((o != 0).sum()) == cr.randomk_keep_count(n, 0.01)    # same mask on both ranks
+    first = [o.clone() for o in outs[0]]
+    _run(plans, 1)
+    assert not torch.equal((first[1] != 0), (outs[0][1] != 0))          # new mask every step
+
+
+@pytest.mark.parametrize("method,q", [("TernGrad", 0), ("RandomDithering", 255), ("RandomDithering", 15)])
+@pytest.mark.parametrize("entire", [False, True])
+def test_quantisers_injected_uniforms(method, q, entire):
+    cfg = CompressionConfig(compress="entiremodel" if entire else "layerwise", method=method, qstates=q or 255,
+                            error_feedback=True)
+    W, sizes = 2, [777, 40000]
+    grads, outs, resids, plans, lw = _world(W, sizes, cfg, entire, ef=True)
+    g = torch.Generator(device="cuda").manual_seed(11)
+    us = [[torch.rand(n, device="cuda", generator=g) for n in sizes] for _ in range(W)]
+    for r in range(W):
+        plans[r].set_random(us[r])
+    _run(plans, 0)
+    if entire:
+        ref_res = [torch.zeros(sum(sizes), device="cuda") for _ in range(W)]
+    else:
+        ref_res = [[torch.zeros(n, device="cuda") for n in sizes] for _ in range(W)]
+    exp = _oracle(grads, cfg, entire, rand=us, resids=ref_res)
+    for e, o in zip(exp, outs[0]):
+        # the norm is reduced in a different order than torch.norm: allow one-level flips to be rare
+        bad = (~torch.isclose(e, o, atol=1e-5, rtol=1e-4)).float().mean()
+        assert bad < 2e-3
+    for o0, o1 in zip(outs[0], outs[1]):
+        assert torch.equal(o0, o1)
+
+
+def test_quantisers_counter_rng_unbiased():
+    cfg = CompressionConfig(compress="layerwise", method="RandomDithering", qstates=7)
+    grads, outs, _, plans, lw = _world(1, [20000], cfg, False)
+    acc = torch.zeros(20000, device="cuda")
+    reps = 200
+    for s in range(reps):
+        _run(plans, s)
+        acc += outs[0][0]
+    err = (acc / reps - grads[0][0]).abs().mean()
+    assert err < 0.5 * grads[0][0].norm() / 7 / math.sqrt(reps) * 3
+
+
+def test_capacity_clamp_keeps_residual():
+    cfg = CompressionConfig(compress="layerwise", method="Thresholdv", threshold=0.1, error_feedback=True,
+                            dense_capacity=0.05)
+    grads, outs, resids, plans, lw = _world(1, [40000], cfg, False, ef=True)
+    g0 = grads[0][0].clone()
+    _run(plans, 0)
+    st = plans[0].stats()
+    assert st["dropped"] > 0 and st["sent"] == plans[0].cap[0]
+    assert torch.allclose(outs[0][0] + resids[0][0], g0, atol=1e-6)     # nothing lost
+
+
+def test_standalone_topk_select():
+    import ctypes as C
+    from layerwise_b200 import _native
+    lib = _native.lib()
+    n, keep = 200000, 2001
+    x = torch.randn(n, device="cuda")
+    ws = torch.empty(lib.lwc_topk_workspace_bytes(n), dtype=torch.uint8, device="cuda")
+    idx = torch.empty(keep + 64, dtype=torch.int32, device="cuda")
+    val = torch.empty(keep + 64, dtype=torch.float32, device="cuda")
+    cnt = torch.zeros(1, dtype=torch.int64, device="cuda")
+    st = torch.cuda.current_stream().cuda_stream
+    rc = lib.lwc_topk_select_f32(x.data_ptr(), n, keep, keep + 64, idx.data_ptr(), val.data_ptr(), cnt.data_ptr(),
+                                 ws.data_ptr(), C.c_void_p(st))
+    assert rc == 0
+    torch.cuda.synchronize()
+    k = int(cnt.item())
+    assert k == keep
+    ref = x.abs().topk(keep).indices.sort().values
+    assert torch.equal(idx[:k].long(), ref)
+    assert torch.equal(val[:k], x[ref])
