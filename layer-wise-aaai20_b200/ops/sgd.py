@@ -18,6 +18,16 @@ from typing import Callable, Dict, Iterable, List, Optional
 import torch
 
 
+def allow_lowp_grad(param: torch.Tensor) -> torch.Tensor:
+    """Let an fp32 master weight carry a bf16/fp16 ``.grad`` (torch >= 2.9 checks ``grad_dtype``)."""
+    if hasattr(param, "grad_dtype"):
+        try:
+            param.grad_dtype = None
+        except Exception:
+            pass
+    return param
+
+
 class FusedSGD(torch.optim.SGD):
     def __init__(self, params, lr=0.0, momentum=0.0, dampening=0.0, weight_decay=0.0,
                  nesterov=False, grad_scale: float = 1.0, model_params: Optional[List] = None):

@@ -110,8 +110,9 @@ class Trainer:
             comm.broadcast_coalesced([t for t in net.state_dict().values() if torch.is_tensor(t)])
         # ---- fp32 masters ----------------------------------------------------------------------------------
         if self.dtype != torch.float32:
-            self.master_params = [p.detach().clone().float().requires_grad_(True) if p.dtype != torch.float32
-                                  else p for p in self.model_params]
+            from ..ops.sgd import allow_lowp_grad
+            self.master_params = [allow_lowp_grad(p.detach().clone().float().requires_grad_(True))
+                                  if p.dtype != torch.float32 else p for p in self.model_params]
         else:
             self.master_params = self.model_params
         # ---- gradient exchange -----------------------------------------------------------------------------

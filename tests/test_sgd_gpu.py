@@ -2,7 +2,7 @@ import pytest
 import torch
 
 import layerwise_b200  # noqa: F401
-from layerwise_b200.ops.sgd import FusedSGD
+from layerwise_b200.ops.sgd import FusedSGD, allow_lowp_grad
 
 pytestmark = pytest.mark.gpu
 
@@ -30,7 +30,7 @@ def test_fused_sgd_matches_torch(momentum, nesterov, wd, damp):
 
 def test_fused_sgd_bf16_model_copy_and_grads():
     torch.manual_seed(0)
-    master = [torch.randn(5000, device="cuda", requires_grad=True)]
+    master = [allow_lowp_grad(torch.randn(5000, device="cuda", requires_grad=True))]
     model = [master[0].detach().to(torch.bfloat16)]
     opt = FusedSGD(master, lr=0.05, momentum=0.9, nesterov=True, weight_decay=1e-4, model_params=model,
                    grad_scale=1.0 / 128)
