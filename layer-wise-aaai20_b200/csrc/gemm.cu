@@ -215,7 +215,9 @@ __global__ void __launch_bounds__(THREADS) k_gemm(const __grid_constant__ CUtens
                         *reinterpret_cast<float4*>(dst + j) = make_float4(__uint_as_float(r[j]), __uint_as_float(r[j + 1]),
                                                                           __uint_as_float(r[j + 2]), __uint_as_float(r[j + 3]));
                 } else {
-                    for (int j = 0; j < ncol; ++j) dst[j] = __uint_as_float(r[j]);
+#pragma unroll
+                    for (int j = 0; j < 32; ++j)
+                        if (j < ncol) dst[j] = __uint_as_float(r[j]);
                 }
                 continue;
             }
@@ -228,9 +230,12 @@ __global__ void __launch_bounds__(THREADS) k_gemm(const __grid_constant__ CUtens
             }
             if (p.out_dtype == LWC_F32) {
                 float* dst = reinterpret_cast<float*>(p.C) + (size_t)row * p.ldc + col0;
-                for (int j = 0; j < ncol; ++j) {
-                    float x = v[j] + (p.accumulate ? dst[j] : 0.0f);
-                    dst[j] = p.relu ? fmaxf(x, 0.0f) : x;
+#pragma unroll
+                for (int j = 0; j < 32; ++j) {
+                    if (j < ncol) {
+                        float x = v[j] + (p.accumulate ? dst[j] : 0.0f);
+                        dst[j] = p.relu ? fmaxf(x, 0.0f) : x;
+                    }
                 }
             } else {
                 __nv_bfloat16* dst = reinterpret_cast<__nv_bfloat16*>(p.C) + (size_t)row * p.ldc + col0;
@@ -259,9 +264,12 @@ __global__ void __launch_bounds__(THREADS) k_gemm(const __grid_constant__ CUtens
                         *reinterpret_cast<uint4*>(dst + j) = o;
                     }
                 } else {
-                    for (int j = 0; j < ncol; ++j) {
-                        float x = v[j] + (p.accumulate ? __bfloat162float(dst[j]) : 0.0f);
-                        dst[j] = __float2bfloat16_rn(p.relu ? fmaxf(x, 0.0f) : x);
+#pragma unroll
+                    for (int j = 0; j < 32; ++j) {
+                        if (j < ncol) {
+                            float x = v[j] + (p.accumulate ? __bfloat162float(dst[j]) : 0.0f);
+                            dst[j] = __float2bfloat16_rn(p.relu ? fmaxf(x, 0.0f) : x);
+                        }
                     }
                 }
             }
@@ -270,6 +278,7 @@ __global__ void __launch_bounds__(THREADS) k_gemm(const __grid_constant__ CUtens
     tcgen05_fence_before();
     __syncthreads();
     if (warp == 1) {
+        __syncwarp();
         asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "n"(BN));
     }
 }

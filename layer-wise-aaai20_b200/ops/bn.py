@@ -1,5 +1,135 @@
-"""Batch-norm dispatch (fused native kernels where available)."""
+"""Fused batch-norm (+ residual add) (+ ReLU) for channels-last activations.
+
+``batch_norm_act`` is an autograd function over ``csrc/bn.cu``: training forward = statistics
++ finalize + apply (3 launches), backward = reduce + finalize + apply (3 launches), with the
+ReLU and the residual join folded in.  The stock modules it replaces run separate statistics /
+transform / ReLU / add kernels (reference: nn.BatchNorm2d + nn.ReLU(True) + ``out += residual``,
+CIFAR10/dawn.py:23-28, IMAGENET/training/resnet.py:40-56,:75-95).
+"""
+from __future__ import annotations
+
+import ctypes as C
+from typing import Optional
+
+import torch
+
+from .. import _native
+from .._native import abi
+
+_WS = {}
 
 
-def maybe_batch_norm(module, x):
+def _workspace(nbytes: int, device) -> torch.Tensor:
+    key = (device.index, torch.cuda.current_stream(device).cuda_stream)
+    ws = _WS.get(key)
+    if ws is None or ws.numel() * 4 < nbytes:
+        ws = torch.empty(max(nbytes // 4 + 1, 1 << 18), dtype=torch.float32, device=device)
+        _WS[key] = ws
+    return ws
+
+
+def _rows_channels(x: torch.Tensor):
+    """(M, C) when ``x`` is a dense channels-last 4-D tensor or a contiguous 2-D one, else None."""
+    if x.dim() == 4 and x.is_contiguous(memory_format=torch.channels_last):
+        n, c, h, w = x.shape
+        return n * h * w, c
+    if x.dim() == 2 and x.is_contiguous():
+        return x.shape[0], x.shape[1]
     return None
+
+
+def supported(x: torch.Tensor, weight, bias, residual=None) -> bool:
+    if not x.is_cuda or x.dtype not in (torch.bfloat16, torch.float16, torch.float32):
+        return False
+    mc = _rows_channels(x)
+    if mc is None or mc[1] % 8 or mc[0] < 1:
+        return False
+    for t in (weight, bias):
+        if t is not None and (t.dtype != torch.float32 or not t.is_contiguous()):
+            return False
+    if residual is not None and (residual.dtype != x.dtype or residual.shape != x.shape
+                                 or _rows_channels(residual) is None):
+        return False
+    return True
+
+
+def _ptr(t):
+    return 0 if t is None else t.data_ptr()
+
+
+class _BatchNormAct(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x, weight, bias, running_mean, running_var, residual, training, momentum, eps, relu):
+        lib = _native.lib()
+        M, Cc = _rows_channels(x)
+        y = torch.empty_like(x)       # preserves the channels-last strides
+        st = torch.cuda.current_stream().cuda_stream
+        mean = invstd = None
+        ws_ptr = 0
+        if training:
+            mean = torch.empty(Cc, dtype=torch.float32, device=x.device)
+            invstd = torch.empty(Cc, dtype=torch.float32, device=x.device)
+            ws_ptr = _workspace(int(lib.lwc_bn_workspace_bytes(M, Cc)), x.device).data_ptr()
+        rc = lib.lwc_bn_forward(x.data_ptr(), y.data_ptr(), _ptr(residual), _ptr(weight), _ptr(bias), _ptr(mean),
+                                _ptr(invstd), _ptr(running_mean), _ptr(running_var), ws_ptr, M, Cc,
+                                abi.dtype_code(x.dtype), int(training), int(relu), float(eps), float(momentum),
+                                C.c_void_p(st))
+        abi.check(rc, "lwc_bn_forward")
+        _native.counters.add(3 if training else 1)
+        ctx.training, ctx.relu, ctx.has_res = training, relu, residual is not None
+        ctx.eps = eps
+        if training:
+            ctx.save_for_backward(x, y if relu else None, weight, mean, invstd)
+        else:
+            ctx.save_for_backward(x, y if relu else None, weight, running_mean, running_var)
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        lib = _native.lib()
+        x, y, weight, mean, invstd = ctx.saved_tensors
+        M, Cc = _rows_channels(x)
+        if _rows_channels(dy) is None or dy.stride() != x.stride():
+            dy = dy.contiguous(memory_format=torch.channels_last) if x.dim() == 4 else dy.contiguous()
+        if not ctx.training:
+            # eval-mode backward (rare): plain affine map, do it with tensor ops
+            a = (weight if weight is not None else 1.0) * torch.rsqrt(invstd + ctx.eps)   # invstd slot holds running_var
+            shape = (1, -1, 1, 1) if x.dim() == 4 else (1, -1)
+            g = dy if not ctx.relu else dy * (y > 0)
+            dx = (g.float() * a.view(shape)).to(x.dtype)
+            xhat = (x.float() - mean.view(shape)) * torch.rsqrt(invstd + ctx.eps).view(shape)
+            dims = (0, 2, 3) if x.dim() == 4 else (0,)
+            return (dx, (g.float() * xhat).sum(dims), g.float().sum(dims), None, None,
+                    g if ctx.has_res else None, None, None, None, None)
+        dx = torch.empty_like(x)
+        dres = torch.empty_like(x) if ctx.has_res else None
+        dgamma = torch.empty(Cc, dtype=torch.float32, device=x.device)
+        dbeta = torch.empty(Cc, dtype=torch.float32, device=x.device)
+        ws_ptr = _workspace(int(lib.lwc_bn_workspace_bytes(M, Cc)), x.device).data_ptr()
+        st = torch.cuda.current_stream().cuda_stream
+        rc = lib.lwc_bn_backward(dy.data_ptr(), x.data_ptr(), _ptr(y), dx.data_ptr(), _ptr(dres), _ptr(weight),
+                                 mean.data_ptr(), invstd.data_ptr(), dgamma.data_ptr(), dbeta.data_ptr(), ws_ptr,
+                                 M, Cc, abi.dtype_code(x.dtype), int(ctx.relu), C.c_void_p(st))
+        abi.check(rc, "lwc_bn_backward")
+        _native.counters.add(3)
+        return (dx, dgamma if weight is not None else None, dbeta if weight is not None else None, None, None,
+                dres, None, None, None, None)
+
+
+def batch_norm_act(x, weight, bias, running_mean, running_var, residual=None, training=True,
+                   momentum=0.1, eps=1e-5, relu=False):
+    """``relu?(batch_norm(x) + residual?)`` in one fused pass structure (see module docstring)."""
+    return _BatchNormAct.apply(x, weight, bias, running_mean, running_var, residual, training, momentum, eps, relu)
+
+
+def maybe_batch_norm(module, x, residual=None, relu=False):
+    """Module dispatch; returns ``None`` when the stock implementation must run."""
+    if module.momentum is None or (module.training and not module.track_running_stats and False):
+        return None
+    if not supported(x, module.weight, module.bias, residual):
+        return None
+    training = module.training or module.running_mean is None
+    if training and module.track_running_stats and module.num_batches_tracked is not None:
+        module.num_batches_tracked.add_(1)
+    return batch_norm_act(x, module.weight, module.bias, module.running_mean, module.running_var,
+                          residual, training, module.momentum, module.eps, relu)

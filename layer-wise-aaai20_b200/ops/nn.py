@@ -55,15 +55,24 @@ class Linear(nn.Linear):
 
 
 class BatchNorm2d(nn.BatchNorm2d):
-    """Batch norm; ``fuse_relu`` lets a following ReLU be folded into the kernel."""
+    """Batch norm with an optional fused epilogue: ``relu(bn(x) + residual)``.
 
-    def forward(self, x):
+    ``forward(x, residual=None, relu=False)`` -- callers that used to write
+    ``relu(bn(x))`` or ``relu(bn(x) + identity)`` pass the flags instead, and the fused
+    sm_100a kernels (``ops/bn.py``) do it in one pass structure; on CPU / unsupported
+    layouts the same math runs with stock ops.
+    """
+
+    def forward(self, x, residual=None, relu=False):
         if _native_ok(x):
             from . import bn as _bn
-            y = _bn.maybe_batch_norm(self, x)
+            y = _bn.maybe_batch_norm(self, x, residual, relu)
             if y is not None:
                 return y
-        return super().forward(x)
+        y = super().forward(x)
+        if residual is not None:
+            y = y + residual
+        return F.relu(y) if relu else y
 
 
 class ReLU(nn.ReLU):

@@ -1,0 +1,93 @@
+#!/usr/bin/env python
+"""Multi-GPU check of the fused exchange over real peer memory (run under torchrun).
+
+    python -m torch.distributed.run --nproc-per-node 2 --master-addr 127.0.0.1 tools/check_multigpu.py
+
+Every rank draws its own gradients; the fused engine's result must equal the oracle
+(compress locally with the reference math, NCCL all-reduce, divide by W) and be bitwise
+identical on all ranks.  Also times compress+exchange per step, max over ranks.
+"""
+import json
+import os
+import sys
+
+import torch
+import torch.distributed as dist
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import layerwise_b200  # noqa: E402,F401
+from layerwise_b200.ops import compress_ref as cr  # noqa: E402
+from layerwise_b200.parallel.exchange import CompressionConfig, GradientExchanger  # noqa: E402
+
+
+def main():
+    rank, world, local = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"]), int(os.environ["LOCAL_RANK"])
+    torch.cuda.set_device(local)
+    dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    sizes = [64, 1000, 8192, 70001, 2359296, 1000 * 2048]
+    results = {}
+    ok = True
+    for compress in ("layerwise", "entiremodel"):
+        for method, kw in (("Topk", dict(ratio=0.01)), ("Thresholdv", dict(threshold=2.0)),
+                           ("AdaptiveThreshold", {}), ("none", {}), ("Randomk", dict(ratio=0.01)),
+                           ("TernGrad", {}), ("RandomDithering", dict(qstates=255))):
+            cfg = CompressionConfig(compress=compress, method=method, error_feedback=False,
+                                    capacity_factor=1.5, dense_capacity=1.0, **kw)
+            g = torch.Generator(device="cuda").manual_seed(1000 + rank)
+            params = [torch.nn.Parameter(torch.zeros(n, device="cuda")) for n in sizes]
+            ex = GradientExchanger(params, cfg, engine="fused")
+            for p in params:
+                p.grad.copy_(torch.randn(p.shape, device="cuda", generator=g))
+            local_g = [p.grad.clone() for p in params]
+            ex.exchange()
+            torch.cuda.synchronize()
+            got = [p.grad.clone() for p in params]
+            name = f"{compress}/{method}"
+            if method in ("Topk", "Thresholdv", "AdaptiveThreshold", "none"):
+                if compress == "layerwise":
+                    exp = [cr.compress_dense(t, cfg.method_name, cfg.ratio, cfg.threshold, cfg.qstates) for t in local_g]
+                else:
+                    flat = cr.compress_dense(torch.cat(local_g), cfg.method_name, cfg.ratio, cfg.threshold, cfg.qstates)
+                    exp, off = [], 0
+                    for t in local_g:
+                        exp.append(flat[off:off + t.numel()])
+                        off += t.numel()
+                for e in exp:
+                    dist.all_reduce(e)
+                    e /= world
+                good = all(torch.allclose(a, b, atol=1e-6, rtol=1e-5) for a, b in zip(exp, got))
+            else:
+                good = all(torch.isfinite(t).all().item() for t in got)
+            # replicas must agree bit for bit
+            for t in got:
+                ref = t.clone()
+                dist.broadcast(ref, 0)
+                good = good and torch.equal(ref, t)
+            st = ex.engine.stats()
+            good = good and st["timeouts"] == 0
+            # timing: 20 exchanges
+            for _ in range(3):
+                ex.exchange()
+            torch.cuda.synchronize()
+            dist.barrier(device_ids=[local])
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            for _ in range(20):
+                ex.exchange()
+            e1.record()
+            torch.cuda.synchronize()
+            ms = torch.tensor([e0.elapsed_time(e1) / 20], device="cuda")
+            dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+            flag = torch.tensor([1.0 if good else 0.0], device="cuda")
+            dist.all_reduce(flag, op=dist.ReduceOp.MIN)
+            results[name] = {"ok": bool(flag.item()), "ms_per_exchange": round(float(ms.item()), 4), "stats": st}
+            ok = ok and bool(flag.item())
+            ex.engine.close()
+    if rank == 0:
+        print(json.dumps({"world": world, "ok": ok, "numel": sum(sizes), "results": results}, indent=1))
+    dist.destroy_process_group()
+    sys.exit(0 if ok else 1)
+
+
+if __name__ == "__main__":
+    main()
