@@ -129,6 +129,25 @@ int lwc_topk_select_f32(const float* x_dev, int64_t n, int64_t keep, int64_t cap
                         uint32_t* idx_out_dev, float* val_out_dev, int64_t* count_out_dev,
                         void* workspace_dev, void* stream);
 
+/* No counterpart in the reference (it never manages device memory itself): the same exact Top-k
+ * selection as lwc_topk_select_f32 for callers that cannot allocate device memory -- code running
+ * under a memory pool that already owns all of HBM, plug-ins that are only handed pointers and
+ * streams, or sections where cudaMalloc's device-wide synchronisation is unacceptable.  The scratch
+ * is a fixed array inside the library (LWC_TOPK_NOALLOC_SCRATCH_BYTES of device memory on every GPU
+ * that loads the library, held until the process exits), hence the size limit:
+ * n > LWC_TOPK_NOALLOC_MAX_N returns LWC_ETOOBIG.  Inputs and outputs are still the caller's.
+ * The call performs no cudaMalloc / cudaFree and uses no allocating library routine.
+ *  - The first call on each device looks up the array's device address (that device must be
+ *    current); make that first call before any stream capture begins.
+ *  - All calls on a device share the one array: two calls whose kernels may overlap on the GPU
+ *    (different streams, no ordering between them) race.  Serialise them.
+ *  - Nothing has to be cleared by the caller; the entry point resets what must start at zero. */
+#define LWC_TOPK_NOALLOC_MAX_N          (1 << 24)          /* 16 Mi elements */
+#define LWC_TOPK_NOALLOC_SCRATCH_BYTES  (96 * 1024)
+int lwc_topk_select_f32_noalloc(const float* x_dev, int64_t n, int64_t keep, int64_t cap,
+                                uint32_t* idx_out_dev, float* val_out_dev, int64_t* count_out_dev,
+                                void* stream);
+
 /* ------------------------------------------------------------------------------------------
  * Fused multi-tensor SGD (torch.optim.SGD semantics: CIFAR10/torch_backend.py:132-143,
  * IMAGENET/training/train_imagenet_nv.py:188-191,:441; fp16 master copies

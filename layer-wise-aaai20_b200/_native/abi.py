@@ -73,6 +73,7 @@ def declare(lib: C.CDLL):
     sig("lwc_plan_stats", C.c_int, vp, C.POINTER(u64), vp)
     sig("lwc_topk_workspace_bytes", sz, i64)
     sig("lwc_topk_select_f32", C.c_int, vp, i64, i64, i64, vp, vp, vp, vp, vp)
+    sig("lwc_topk_select_f32_noalloc", C.c_int, vp, i64, i64, i64, vp, vp, vp, vp)
     sig("lwc_gemm_workspace_bytes", sz, C.c_int, C.c_int, C.c_int)
     sig("lwc_gemm_pick_splits", C.c_int, C.c_int, C.c_int, C.c_int)
     sig("lwc_gemm_bf16", C.c_int, vp, vp, vp, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int,

@@ -1153,3 +1153,56 @@ extern "C" int lwc_topk_select_f32(const float* x_dev, int64_t n, int64_t keep, 
     return lwc_topk_select_impl(x_dev, n, keep, cap, idx_out_dev, val_out_dev, count_out_dev, workspace_dev,
                                 (cudaStream_t)stream);
 }
+
+// =====================================================================================================
+// Top-k selection for callers that must not allocate device memory.
+//
+// Who needs this: code that runs where a device allocation is off the table -- a host thread inside a
+// serving or training loop whose memory pool already owns all of HBM (so cudaMalloc would fail or steal
+// from the pool), a plug-in that is handed streams and pointers but is forbidden from touching the
+// allocator, or a latency-critical section that cannot afford cudaMalloc's implicit device-wide
+// synchronisation.  Such a caller has nowhere to get the selection scratch (histograms, per-chunk
+// counters, chunk table) from, so this variant keeps it in a fixed array inside the library image.
+//
+// The scratch lives in device memory of every GPU that loads the library, for the life of the process
+// (LWC_TOPK_NOALLOC_SCRATCH_BYTES each).  It bounds the problem size: n <= LWC_TOPK_NOALLOC_MAX_N.
+// =====================================================================================================
+static __device__ __align__(256) unsigned char g_topk_noalloc_scratch[LWC_TOPK_NOALLOC_SCRATCH_BYTES];
+
+namespace {
+constexpr int kMaxDevices = 64;
+void* g_noalloc_scratch_ptr[kMaxDevices] = {nullptr};   // device address of the array, per device
+}  // namespace
+
+// In host code `g_topk_noalloc_scratch` names a host-side shadow of the symbol, not device memory: the
+// real address has to be asked for, once per device, while that device is current.
+static int noalloc_scratch_for_current_device(void** out) {
+    int dev = -1;
+    LWC_CUDA_CHECK(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= kMaxDevices) return LWC_EINVAL;
+    if (!g_noalloc_scratch_ptr[dev]) {
+        void* ptr = nullptr;
+        const cudaError_t e = cudaGetSymbolAddress(&ptr, g_topk_noalloc_scratch);
+        if (e != cudaSuccess) return (int)e;
+        if (!ptr) return LWC_ESTATE;
+        g_noalloc_scratch_ptr[dev] = ptr;
+    }
+    *out = g_noalloc_scratch_ptr[dev];
+    return 0;
+}
+
+extern "C" int lwc_topk_select_f32_noalloc(const float* x_dev, int64_t n, int64_t keep, int64_t cap,
+                                           uint32_t* idx_out_dev, float* val_out_dev, int64_t* count_out_dev,
+                                           void* stream) {
+    if (n <= 0) return LWC_EINVAL;
+    if (n > (int64_t)LWC_TOPK_NOALLOC_MAX_N || TopkLayout(n).total > (size_t)LWC_TOPK_NOALLOC_SCRATCH_BYTES)
+        return LWC_ETOOBIG;      // "size beyond the supported maximum" (see lwc_error_string)
+    void* scratch = nullptr;
+    const int rc = noalloc_scratch_for_current_device(&scratch);
+    if (rc) return rc;
+    // lwc_topk_select_impl re-initialises everything it reads before use (selection state is memset,
+    // header / chunk table / counters are rewritten by k_topk_init, per-chunk counts are rewritten for
+    // every chunk of this call), so whatever the previous call left in the array is harmless.
+    return lwc_topk_select_impl(x_dev, n, keep, cap, idx_out_dev, val_out_dev, count_out_dev, scratch,
+                                (cudaStream_t)stream);
+}
