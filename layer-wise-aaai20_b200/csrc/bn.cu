@@ -112,6 +112,40 @@ __device__ __forceinline__ void st8<float>(float* p, const float v[8]) {
     *reinterpret_cast<float4*>(p + 4) = make_float4(v[4], v[5], v[6], v[7]);
 }
 
+// Packed 8-element vector kept in its storage format while loads are in flight (4 registers for
+// 16-bit types), unpacked to fp32 only when consumed: lets a thread keep 4 rows x several tensors
+// outstanding without blowing the register budget.
+template <typename T> struct Raw { uint4 v; };
+template <> struct Raw<float> { float4 a, b; };
+template <typename T>
+__device__ __forceinline__ void ldraw(const T* p, Raw<T>& r) { r.v = *reinterpret_cast<const uint4*>(p); }
+template <>
+__device__ __forceinline__ void ldraw<float>(const float* p, Raw<float>& r) {
+    r.a = *reinterpret_cast<const float4*>(p);
+    r.b = *reinterpret_cast<const float4*>(p + 4);
+}
+__device__ __forceinline__ void unpack(const Raw<__nv_bfloat16>& r, float v[8]) {
+    const uint32_t w[4] = {r.v.x, r.v.y, r.v.z, r.v.w};
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {     // bf16 -> fp32 is a 16-bit shift
+        v[2 * i] = __uint_as_float(w[i] << 16);
+        v[2 * i + 1] = __uint_as_float(w[i] & 0xffff0000u);
+    }
+}
+__device__ __forceinline__ void unpack(const Raw<__half>& r, float v[8]) {
+    const uint32_t w[4] = {r.v.x, r.v.y, r.v.z, r.v.w};
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+        const __half2 h = *reinterpret_cast<const __half2*>(&w[i]);
+        v[2 * i] = __low2float(h);
+        v[2 * i + 1] = __high2float(h);
+    }
+}
+__device__ __forceinline__ void unpack(const Raw<float>& r, float v[8]) {
+    v[0] = r.a.x; v[1] = r.a.y; v[2] = r.a.z; v[3] = r.a.w; v[4] = r.b.x; v[5] = r.b.y; v[6] = r.b.z; v[7] = r.b.w;
+}
+constexpr int ROWS = 4;      // rows in flight per thread
+
 struct Map {
     int tpr, rpp, tx, ry, cg;      // threads per row, rows per pass, my column / row lane, channel group
     bool active;
@@ -156,25 +190,25 @@ __global__ void __launch_bounds__(THREADS) k_bn_stats(Params p) {
     float s[8] = {0, 0, 0, 0, 0, 0, 0, 0}, q[8] = {0, 0, 0, 0, 0, 0, 0, 0};
     if (m.active) {
         const T* x = reinterpret_cast<const T*>(p.x) + (size_t)m.cg * VEC;
+        constexpr int U = 8;
         long long r = m.row0 + m.ry;
-        for (; r + 3LL * m.rpp < m.row1; r += 4LL * m.rpp) {
-            float v0[8], v1[8], v2[8], v3[8];
-            ld8<T>(x + (size_t)r * p.C, v0);
-            ld8<T>(x + (size_t)(r + m.rpp) * p.C, v1);
-            ld8<T>(x + (size_t)(r + 2 * m.rpp) * p.C, v2);
-            ld8<T>(x + (size_t)(r + 3 * m.rpp) * p.C, v3);
+        for (; r + (long long)(U - 1) * m.rpp < m.row1; r += (long long)U * m.rpp) {
+            Raw<T> raw[U];
 #pragma unroll
-            for (int k = 0; k < 8; ++k) {
-                s[k] += (v0[k] + v1[k]) + (v2[k] + v3[k]);
-                q[k] = fmaf(v0[k], v0[k], q[k]);
-                q[k] = fmaf(v1[k], v1[k], q[k]);
-                q[k] = fmaf(v2[k], v2[k], q[k]);
-                q[k] = fmaf(v3[k], v3[k], q[k]);
+            for (int u = 0; u < U; ++u) ldraw<T>(x + (size_t)(r + (long long)u * m.rpp) * p.C, raw[u]);
+#pragma unroll
+            for (int u = 0; u < U; ++u) {
+                float v[8];
+                unpack(raw[u], v);
+#pragma unroll
+                for (int k = 0; k < 8; ++k) { s[k] += v[k]; q[k] = fmaf(v[k], v[k], q[k]); }
             }
         }
         for (; r < m.row1; r += m.rpp) {
+            Raw<T> raw;
+            ldraw<T>(x + (size_t)r * p.C, raw);
             float v[8];
-            ld8<T>(x + (size_t)r * p.C, v);
+            unpack(raw, v);
 #pragma unroll
             for (int k = 0; k < 8; ++k) { s[k] += v[k]; q[k] = fmaf(v[k], v[k], q[k]); }
         }
@@ -187,45 +221,55 @@ __global__ void __launch_bounds__(THREADS) k_bn_stats(Params p) {
     }
 }
 
-// ---- forward: combine partials (one CTA = 32 channels x 8 lanes) --------------------------------------
+// ---- forward: combine partials (one warp per channel, fixed-order -> deterministic) -------------------
+__device__ __forceinline__ double warp_sum_d(double v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    return v;
+}
+
+constexpr int MAX_PART_PER_LANE = 20;     // plan_grid keeps nblk <= 32 * 20
+
+// All partials of a channel are fetched up front (<= 20 independent loads per lane), so the kernel pays
+// the memory latency once instead of once per loop iteration.
 __global__ void __launch_bounds__(256) k_bn_finalize(Params p) {
-    const int c = blockIdx.x * 32 + (threadIdx.x >> 3);
-    const int l = threadIdx.x & 7;
-    double n = 0.0, mean = 0.0, m2 = 0.0;
-    if (c < p.C) {
-        for (int b = l; b < p.nblk; b += 8) {
+    const int c = blockIdx.x * 8 + (threadIdx.x >> 5);
+    const int l = threadIdx.x & 31;
+    if (c >= p.C) return;
+    const float* part = p.partial + c;
+    const size_t stride = (size_t)2 * p.C;
+    float sv[MAX_PART_PER_LANE], qv[MAX_PART_PER_LANE];
+#pragma unroll
+    for (int i = 0; i < MAX_PART_PER_LANE; ++i) {
+        const int b = l + 32 * i;
+        sv[i] = b < p.nblk ? part[(size_t)b * stride] : 0.0f;
+        qv[i] = b < p.nblk ? part[(size_t)b * stride + p.C] : 0.0f;
+    }
+    double s = 0.0;
+#pragma unroll
+    for (int i = 0; i < MAX_PART_PER_LANE; ++i) s += (double)sv[i];
+    s = warp_sum_d(s);
+    const double n = (double)p.M;
+    const double mean = s / n;
+    // M2 = sum_b [ M2_b + n_b * (mean_b - mean)^2 ]   (Chan's combination against the global mean)
+    double m2 = 0.0;
+    const float fmean = (float)mean;
+#pragma unroll
+    for (int i = 0; i < MAX_PART_PER_LANE; ++i) {
+        const int b = l + 32 * i;
+        if (b < p.nblk) {
             long long r0 = (long long)b * p.rows_per_blk, r1 = r0 + p.rows_per_blk;
             if (r1 > p.M) r1 = p.M;
-            const double nb = (double)(r1 - r0);
-            if (nb <= 0) continue;
-            const float sb = p.partial[(size_t)b * 2 * p.C + c], qb = p.partial[(size_t)b * 2 * p.C + p.C + c];
-            const double mb = (double)sb / nb;
-            double m2b = (double)qb - (double)sb * mb;
-            if (m2b < 0) m2b = 0;
-            const double delta = mb - mean, tot = n + nb;
-            mean += delta * nb / tot;
-            m2 += m2b + delta * delta * n * nb / tot;
-            n = tot;
+            const float nb = (float)(r1 - r0);
+            const float mb = sv[i] / nb;
+            const float m2b = fmaxf(qv[i] - sv[i] * mb, 0.0f);
+            const float d = mb - fmean;
+            m2 += (double)(m2b + nb * d * d);
         }
     }
-    // fixed-order tree over the 8 lanes (deterministic)
-#pragma unroll
-    for (int o = 1; o < 8; o <<= 1) {
-        const double n2 = __shfl_xor_sync(0xffffffffu, n, o);
-        const double mean2 = __shfl_xor_sync(0xffffffffu, mean, o);
-        const double m22 = __shfl_xor_sync(0xffffffffu, m2, o);
-        // combine in a symmetric way so both partners compute the same value
-        const double tot = n + n2;
-        if (tot > 0) {
-            const double delta = mean2 - mean;
-            const double nm = (n * mean + n2 * mean2) / tot;
-            m2 = m2 + m22 + delta * delta * n * n2 / tot;
-            mean = nm;
-            n = tot;
-        }
-    }
-    if (c < p.C && l == 0) {
-        const double var = n > 0 ? m2 / n : 0.0;
+    m2 = warp_sum_d(m2);
+    if (l == 0) {
+        const double var = m2 / n;
         p.mean[c] = (float)mean;
         p.invstd[c] = (float)(1.0 / sqrt(var + (double)p.eps));
         if (p.running_mean) {
@@ -255,29 +299,38 @@ __global__ void __launch_bounds__(THREADS) k_bn_apply(Params p, int use_running)
     const T* x = reinterpret_cast<const T*>(p.x) + c0;
     const T* rs = p.res ? reinterpret_cast<const T*>(p.res) + c0 : nullptr;
     T* y = reinterpret_cast<T*>(p.y) + c0;
-    for (long long r = m.row0 + m.ry; r < m.row1; r += 2LL * m.rpp) {
-        const long long r2 = r + m.rpp;
-        const bool two = r2 < m.row1;
-        float v0[8], v1[8], w0[8], w1[8];
-        ld8<T>(x + (size_t)r * p.C, v0);
-        if (two) ld8<T>(x + (size_t)r2 * p.C, v1);
-        if (rs) {
-            ld8<T>(rs + (size_t)r * p.C, w0);
-            if (two) ld8<T>(rs + (size_t)r2 * p.C, w1);
+    for (long long r = m.row0 + m.ry; r < m.row1; r += (long long)ROWS * m.rpp) {
+        Raw<T> xr[ROWS], rr[ROWS];
+#pragma unroll
+        for (int u = 0; u < ROWS; ++u) {
+            const long long ru = r + (long long)u * m.rpp;
+            if (ru < m.row1) {
+                ldraw<T>(x + (size_t)ru * p.C, xr[u]);
+                if (rs) ldraw<T>(rs + (size_t)ru * p.C, rr[u]);
+            }
         }
 #pragma unroll
-        for (int k = 0; k < 8; ++k) {
-            float o0 = fmaf(v0[k], a[k], b[k]), o1 = fmaf(v1[k], a[k], b[k]);
-            if (rs) { o0 += w0[k]; o1 += w1[k]; }
-            if (p.relu) { o0 = fmaxf(o0, 0.0f); o1 = fmaxf(o1, 0.0f); }
-            v0[k] = o0; v1[k] = o1;
+        for (int u = 0; u < ROWS; ++u) {
+            const long long ru = r + (long long)u * m.rpp;
+            if (ru >= m.row1) break;
+            float v[8], w[8];
+            unpack(xr[u], v);
+            if (rs) unpack(rr[u], w);
+#pragma unroll
+            for (int k = 0; k < 8; ++k) {
+                float o = fmaf(v[k], a[k], b[k]);
+                if (rs) o += w[k];
+                v[k] = p.relu ? fmaxf(o, 0.0f) : o;
+            }
+            st8<T>(y + (size_t)ru * p.C, v);
         }
-        st8<T>(y + (size_t)r * p.C, v0);
-        if (two) st8<T>(y + (size_t)r2 * p.C, v1);
     }
 }
 
 // ---- backward: partial reductions -----------------------------------------------------------------------
+// Accumulates S1 = sum dy' and S2 = sum dy' * x per channel; the finalize kernel turns them into
+// dbeta = S1 and dgamma = invstd * (S2 - mean * S1).  dy' = dy * [y > 0] when ReLU is fused; y is either the
+// saved forward output (residual fused) or recomputed as fma(x, a, b) exactly like k_bn_apply.
 template <typename T>
 __global__ void __launch_bounds__(THREADS) k_bn_bwd_reduce(Params p) {
     __shared__ float sh[THREADS * 16];
@@ -285,35 +338,45 @@ __global__ void __launch_bounds__(THREADS) k_bn_bwd_reduce(Params p) {
     float sd[8] = {0, 0, 0, 0, 0, 0, 0, 0}, sx[8] = {0, 0, 0, 0, 0, 0, 0, 0};
     if (m.active) {
         const int c0 = m.cg * VEC;
-        float mu[8], is[8];
+        const bool have_y = p.y != nullptr;
+        const bool recompute = p.relu && !have_y;
+        float fa[8], fb[8];
 #pragma unroll
-        for (int k = 0; k < 8; ++k) { mu[k] = p.mean[c0 + k]; is[k] = p.invstd[c0 + k]; }
+        for (int k = 0; k < 8; ++k) {
+            fa[k] = (p.gamma ? p.gamma[c0 + k] : 1.0f) * p.invstd[c0 + k];
+            fb[k] = (p.beta ? p.beta[c0 + k] : 0.0f) - p.mean[c0 + k] * fa[k];
+        }
         const T* x = reinterpret_cast<const T*>(p.x) + c0;
         const T* dy = reinterpret_cast<const T*>(p.dy) + c0;
         const T* y = reinterpret_cast<const T*>(p.y) + c0;
-        for (long long r = m.row0 + m.ry; r < m.row1; r += 2LL * m.rpp) {
-            const long long r2 = r + m.rpp;
-            const bool two = r2 < m.row1;
-            float xv0[8], dv0[8], yv0[8], xv1[8], dv1[8], yv1[8];
-            ld8<T>(x + (size_t)r * p.C, xv0);
-            ld8<T>(dy + (size_t)r * p.C, dv0);
-            if (p.relu) ld8<T>(y + (size_t)r * p.C, yv0);
-            if (two) {
-                ld8<T>(x + (size_t)r2 * p.C, xv1);
-                ld8<T>(dy + (size_t)r2 * p.C, dv1);
-                if (p.relu) ld8<T>(y + (size_t)r2 * p.C, yv1);
+        for (long long r = m.row0 + m.ry; r < m.row1; r += (long long)ROWS * m.rpp) {
+            Raw<T> xr[ROWS], dr[ROWS], yr[ROWS];
+#pragma unroll
+            for (int u = 0; u < ROWS; ++u) {
+                const long long ru = r + (long long)u * m.rpp;
+                if (ru < m.row1) {
+                    ldraw<T>(x + (size_t)ru * p.C, xr[u]);
+                    ldraw<T>(dy + (size_t)ru * p.C, dr[u]);
+                    if (p.relu && have_y) ldraw<T>(y + (size_t)ru * p.C, yr[u]);
+                }
             }
 #pragma unroll
-            for (int k = 0; k < 8; ++k) {
-                float d0 = dv0[k];
-                if (p.relu && !(yv0[k] > 0.0f)) d0 = 0.0f;
-                sd[k] += d0;
-                sx[k] = fmaf(d0, (xv0[k] - mu[k]) * is[k], sx[k]);
-                if (two) {
-                    float d1 = dv1[k];
-                    if (p.relu && !(yv1[k] > 0.0f)) d1 = 0.0f;
-                    sd[k] += d1;
-                    sx[k] = fmaf(d1, (xv1[k] - mu[k]) * is[k], sx[k]);
+            for (int u = 0; u < ROWS; ++u) {
+                const long long ru = r + (long long)u * m.rpp;
+                if (ru >= m.row1) break;
+                float xv[8], dv[8], yv[8];
+                unpack(xr[u], xv);
+                unpack(dr[u], dv);
+                if (p.relu && have_y) unpack(yr[u], yv);
+#pragma unroll
+                for (int k = 0; k < 8; ++k) {
+                    float d = dv[k];
+                    if (p.relu) {
+                        const float yy = recompute ? fmaf(xv[k], fa[k], fb[k]) : yv[k];
+                        if (!(yy > 0.0f)) d = 0.0f;
+                    }
+                    sd[k] += d;
+                    sx[k] = fmaf(d, xv[k], sx[k]);
                 }
             }
         }
@@ -327,74 +390,83 @@ __global__ void __launch_bounds__(THREADS) k_bn_bwd_reduce(Params p) {
 }
 
 __global__ void __launch_bounds__(256) k_bn_bwd_finalize(Params p) {
-    const int c = blockIdx.x * 32 + (threadIdx.x >> 3);
-    const int l = threadIdx.x & 7;
-    double sd = 0.0, sx = 0.0;
-    if (c < p.C) {
-        for (int b = l; b < p.nblk; b += 8) {
-            sd += (double)p.partial[(size_t)b * 2 * p.C + c];
-            sx += (double)p.partial[(size_t)b * 2 * p.C + p.C + c];
-        }
-    }
+    const int c = blockIdx.x * 8 + (threadIdx.x >> 5);
+    const int l = threadIdx.x & 31;
+    if (c >= p.C) return;
+    const float* part = p.partial + c;
+    const size_t stride = (size_t)2 * p.C;
+    float sv[MAX_PART_PER_LANE], qv[MAX_PART_PER_LANE];
 #pragma unroll
-    for (int o = 1; o < 8; o <<= 1) {
-        sd += __shfl_xor_sync(0xffffffffu, sd, o);
-        sx += __shfl_xor_sync(0xffffffffu, sx, o);
+    for (int i = 0; i < MAX_PART_PER_LANE; ++i) {
+        const int b = l + 32 * i;
+        sv[i] = b < p.nblk ? part[(size_t)b * stride] : 0.0f;
+        qv[i] = b < p.nblk ? part[(size_t)b * stride + p.C] : 0.0f;
     }
-    if (c < p.C && l == 0) {
+    double sd = 0.0, sx = 0.0;
+#pragma unroll
+    for (int i = 0; i < MAX_PART_PER_LANE; ++i) { sd += (double)sv[i]; sx += (double)qv[i]; }
+    sd = warp_sum_d(sd);
+    sx = warp_sum_d(sx);
+    if (l == 0) {
         p.dbeta[c] = (float)sd;
-        p.dgamma[c] = (float)sx;
+        p.dgamma[c] = (float)((double)p.invstd[c] * (sx - (double)p.mean[c] * sd));
     }
 }
 
+// dx = A*dy' + B*x + C  with  A = gamma*invstd,  B = -A*invstd*mean(dy'*xhat),  C = -B*mean - A*mean(dy')
 template <typename T>
 __global__ void __launch_bounds__(THREADS) k_bn_bwd_apply(Params p) {
     const Map m = make_map(p);
     if (!m.active) return;
     const int c0 = m.cg * VEC;
-    float mu[8], is[8], a[8], md[8], mx[8];
+    const bool have_y = p.y != nullptr;
+    const bool recompute = p.relu && !have_y;
+    float A[8], B[8], Cc[8], fb[8];
     const float invM = 1.0f / (float)p.M;
 #pragma unroll
     for (int k = 0; k < 8; ++k) {
-        mu[k] = p.mean[c0 + k];
-        is[k] = p.invstd[c0 + k];
-        a[k] = (p.gamma ? p.gamma[c0 + k] : 1.0f) * is[k];
-        md[k] = p.dbeta[c0 + k] * invM;
-        mx[k] = p.dgamma[c0 + k] * invM;
+        const float mu = p.mean[c0 + k], is = p.invstd[c0 + k];
+        A[k] = (p.gamma ? p.gamma[c0 + k] : 1.0f) * is;
+        fb[k] = (p.beta ? p.beta[c0 + k] : 0.0f) - mu * A[k];
+        B[k] = -A[k] * is * (p.dgamma[c0 + k] * invM);
+        Cc[k] = -B[k] * mu - A[k] * (p.dbeta[c0 + k] * invM);
     }
     const T* x = reinterpret_cast<const T*>(p.x) + c0;
     const T* dy = reinterpret_cast<const T*>(p.dy) + c0;
     const T* y = reinterpret_cast<const T*>(p.y) + c0;
     T* dx = reinterpret_cast<T*>(p.dx) + c0;
     T* dr = p.dres ? reinterpret_cast<T*>(p.dres) + c0 : nullptr;
-    for (long long r = m.row0 + m.ry; r < m.row1; r += 2LL * m.rpp) {
-        const long long r2 = r + m.rpp;
-        const bool two = r2 < m.row1;
-        float xv0[8], dv0[8], yv0[8], xv1[8], dv1[8], yv1[8];
-        ld8<T>(x + (size_t)r * p.C, xv0);
-        ld8<T>(dy + (size_t)r * p.C, dv0);
-        if (p.relu) ld8<T>(y + (size_t)r * p.C, yv0);
-        if (two) {
-            ld8<T>(x + (size_t)r2 * p.C, xv1);
-            ld8<T>(dy + (size_t)r2 * p.C, dv1);
-            if (p.relu) ld8<T>(y + (size_t)r2 * p.C, yv1);
+    for (long long r = m.row0 + m.ry; r < m.row1; r += (long long)ROWS * m.rpp) {
+        Raw<T> xr[ROWS], gr[ROWS], yr[ROWS];
+#pragma unroll
+        for (int u = 0; u < ROWS; ++u) {
+            const long long ru = r + (long long)u * m.rpp;
+            if (ru < m.row1) {
+                ldraw<T>(x + (size_t)ru * p.C, xr[u]);
+                ldraw<T>(dy + (size_t)ru * p.C, gr[u]);
+                if (p.relu && have_y) ldraw<T>(y + (size_t)ru * p.C, yr[u]);
+            }
         }
 #pragma unroll
-        for (int k = 0; k < 8; ++k) {
-            float d0 = dv0[k], d1 = dv1[k];
-            if (p.relu) {
-                if (!(yv0[k] > 0.0f)) d0 = 0.0f;
-                if (!(yv1[k] > 0.0f)) d1 = 0.0f;
+        for (int u = 0; u < ROWS; ++u) {
+            const long long ru = r + (long long)u * m.rpp;
+            if (ru >= m.row1) break;
+            float xv[8], dv[8], yv[8];
+            unpack(xr[u], xv);
+            unpack(gr[u], dv);
+            if (p.relu && have_y) unpack(yr[u], yv);
+#pragma unroll
+            for (int k = 0; k < 8; ++k) {
+                float d = dv[k];
+                if (p.relu) {
+                    const float yy = recompute ? fmaf(xv[k], A[k], fb[k]) : yv[k];
+                    if (!(yy > 0.0f)) d = 0.0f;
+                }
+                dv[k] = d;
+                xv[k] = fmaf(A[k], d, fmaf(B[k], xv[k], Cc[k]));
             }
-            dv0[k] = d0; dv1[k] = d1;
-            xv0[k] = a[k] * (d0 - md[k] - (xv0[k] - mu[k]) * is[k] * mx[k]);
-            xv1[k] = a[k] * (d1 - md[k] - (xv1[k] - mu[k]) * is[k] * mx[k]);
-        }
-        st8<T>(dx + (size_t)r * p.C, xv0);
-        if (dr) st8<T>(dr + (size_t)r * p.C, dv0);
-        if (two) {
-            st8<T>(dx + (size_t)r2 * p.C, xv1);
-            if (dr) st8<T>(dr + (size_t)r2 * p.C, dv1);
+            st8<T>(dx + (size_t)ru * p.C, xv);
+            if (dr) st8<T>(dr + (size_t)ru * p.C, dv);
         }
     }
 }
@@ -414,6 +486,8 @@ static void plan_grid(long long M, int C, int* nblk, int* rows_per_blk, dim3* gr
     long long rows = (M + target - 1) / target;
     const long long min_rows = 4LL * rpp;
     if (rows < min_rows) rows = min_rows;
+    const long long max_blk = 32LL * 20;                 // k_bn_finalize holds <= 20 partials per lane
+    if ((M + rows - 1) / rows > max_blk) rows = (M + max_blk - 1) / max_blk;
     rows = (rows + rpp - 1) / rpp * rpp;
     *rows_per_blk = (int)rows;
     *nblk = (int)((M + rows - 1) / rows);
@@ -454,30 +528,31 @@ extern "C" int lwc_bn_forward(const void* x, void* y, const void* res, const flo
     plan_grid(M, C, &p.nblk, &p.rows_per_blk, &grid);
     if (training) {
         LWC_BN_DISPATCH(dtype, k_bn_stats<T><<<grid, THREADS, 0, st>>>(p));
-        k_bn_finalize<<<(C + 31) / 32, 256, 0, st>>>(p);
+        k_bn_finalize<<<(C + 7) / 8, 256, 0, st>>>(p);
     }
     LWC_BN_DISPATCH(dtype, k_bn_apply<T><<<grid, THREADS, 0, st>>>(p, training ? 0 : 1));
     return (int)cudaGetLastError();
 }
 
-// y: the forward output (needed only when relu=1); dres: gradient of the fused residual input (nullable).
+// y: the forward output (needed only when relu=1 and a residual was fused; NULL -> the ReLU mask is recomputed
+// from x, gamma, beta); dres: gradient of the fused residual input (nullable).
 extern "C" int lwc_bn_backward(const void* dy, const void* x, const void* y, void* dx, void* dres, const float* gamma,
-                               const float* mean, const float* invstd, float* dgamma, float* dbeta, float* workspace,
+                               const float* beta, const float* mean, const float* invstd, float* dgamma, float* dbeta, float* workspace,
                                long long M, int C, int dtype, int relu, void* stream) {
     if (!dy || !x || !dx || !mean || !invstd || !dgamma || !dbeta || !workspace) return LWC_EINVAL;
-    if (relu && !y) return LWC_EINVAL;
+    if (relu && !y && dres) return LWC_EINVAL;    // with a fused residual the mask needs the saved output
     if (M <= 0 || C <= 0 || (C % VEC)) return LWC_EINVAL;
     cudaStream_t st = (cudaStream_t)stream;
     Params p;
     memset(&p, 0, sizeof(p));
-    p.x = x; p.y = const_cast<void*>(y); p.dy = dy; p.dx = dx; p.dres = dres; p.gamma = gamma;
+    p.x = x; p.y = const_cast<void*>(y); p.dy = dy; p.dx = dx; p.dres = dres; p.gamma = gamma; p.beta = beta;
     p.mean = const_cast<float*>(mean); p.invstd = const_cast<float*>(invstd);
     p.dgamma = dgamma; p.dbeta = dbeta; p.partial = workspace;
     p.M = M; p.C = C; p.relu = relu;
     dim3 grid;
     plan_grid(M, C, &p.nblk, &p.rows_per_blk, &grid);
     LWC_BN_DISPATCH(dtype, k_bn_bwd_reduce<T><<<grid, THREADS, 0, st>>>(p));
-    k_bn_bwd_finalize<<<(C + 31) / 32, 256, 0, st>>>(p);
+    k_bn_bwd_finalize<<<(C + 7) / 8, 256, 0, st>>>(p);
     LWC_BN_DISPATCH(dtype, k_bn_bwd_apply<T><<<grid, THREADS, 0, st>>>(p));
     return (int)cudaGetLastError();
 }

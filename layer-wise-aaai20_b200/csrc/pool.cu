@@ -1,0 +1,201 @@
+// Max pooling for channels-last activations (NHWC), forward with a one-byte argmax per element and a
+// gather-style backward (no atomics): each input pixel sums dy over the <= ceil(k/s)^2 output windows
+// that cover it and whose argmax points at it.  A thread owns 8 consecutive channels (16-byte vectors),
+// consecutive threads own consecutive channel groups, so every access is coalesced.
+// (reference ops: nn.MaxPool2d 2x2/2, 4x4/4 in CIFAR10/dawn.py:51,70-71; 3x3/2 pad 1 in
+//  IMAGENET/training/resnet.py:104 -- ATen max_pool2d forward/backward kernels)
+#include <cuda_bf16.h>
+#include <cuda_fp16.h>
+#include <cuda_runtime.h>
+#include <string.h>
+
+#include "common.cuh"
+
+namespace lwc {
+namespace pool {
+
+struct Params {
+    const void* x;
+    void* y;
+    uint8_t* idx;
+    const void* dy;
+    void* dx;
+    int N, H, W, C, OH, OW, k, s, pad;
+};
+
+template <typename T> struct V8;
+template <> struct V8<__nv_bfloat16> {
+    static __device__ __forceinline__ void ld(const __nv_bfloat16* p, float v[8]) {
+        const uint4 t = *reinterpret_cast<const uint4*>(p);
+        const uint32_t w[4] = {t.x, t.y, t.z, t.w};
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            const __nv_bfloat162 h = *reinterpret_cast<const __nv_bfloat162*>(&w[i]);
+            v[2 * i] = __low2float(h); v[2 * i + 1] = __high2float(h);
+        }
+    }
+    static __device__ __forceinline__ void st(__nv_bfloat16* p, const float v[8]) {
+        uint32_t w[4];
+#pragma unroll
+        for (int i = 0; i < 4; ++i) { __nv_bfloat162 h = __floats2bfloat162_rn(v[2 * i], v[2 * i + 1]); w[i] = *reinterpret_cast<uint32_t*>(&h); }
+        *reinterpret_cast<uint4*>(p) = make_uint4(w[0], w[1], w[2], w[3]);
+    }
+};
+template <> struct V8<__half> {
+    static __device__ __forceinline__ void ld(const __half* p, float v[8]) {
+        const uint4 t = *reinterpret_cast<const uint4*>(p);
+        const uint32_t w[4] = {t.x, t.y, t.z, t.w};
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            const __half2 h = *reinterpret_cast<const __half2*>(&w[i]);
+            v[2 * i] = __low2float(h); v[2 * i + 1] = __high2float(h);
+        }
+    }
+    static __device__ __forceinline__ void st(__half* p, const float v[8]) {
+        uint32_t w[4];
+#pragma unroll
+        for (int i = 0; i < 4; ++i) { __half2 h = __floats2half2_rn(v[2 * i], v[2 * i + 1]); w[i] = *reinterpret_cast<uint32_t*>(&h); }
+        *reinterpret_cast<uint4*>(p) = make_uint4(w[0], w[1], w[2], w[3]);
+    }
+};
+template <> struct V8<float> {
+    static __device__ __forceinline__ void ld(const float* p, float v[8]) {
+        const float4 a = *reinterpret_cast<const float4*>(p), b = *reinterpret_cast<const float4*>(p + 4);
+        v[0] = a.x; v[1] = a.y; v[2] = a.z; v[3] = a.w; v[4] = b.x; v[5] = b.y; v[6] = b.z; v[7] = b.w;
+    }
+    static __device__ __forceinline__ void st(float* p, const float v[8]) {
+        *reinterpret_cast<float4*>(p) = make_float4(v[0], v[1], v[2], v[3]);
+        *reinterpret_cast<float4*>(p + 4) = make_float4(v[4], v[5], v[6], v[7]);
+    }
+};
+
+template <typename T>
+__global__ void __launch_bounds__(256) k_maxpool_fwd(Params p) {
+    const int ncg = p.C >> 3;
+    const long long total = (long long)p.N * p.OH * p.OW * ncg;
+    for (long long id = (long long)blockIdx.x * blockDim.x + threadIdx.x; id < total; id += (long long)gridDim.x * blockDim.x) {
+        const int cg = (int)(id % ncg);
+        long long pix = id / ncg;
+        const int ow = (int)(pix % p.OW); pix /= p.OW;
+        const int oh = (int)(pix % p.OH);
+        const int n = (int)(pix / p.OH);
+        float best[8];
+        unsigned arg[8];
+#pragma unroll
+        for (int c = 0; c < 8; ++c) { best[c] = -INFINITY; arg[c] = 0; }
+        const int h0 = oh * p.s - p.pad, w0 = ow * p.s - p.pad;
+        const T* xb = reinterpret_cast<const T*>(p.x) + (size_t)n * p.H * p.W * p.C + cg * 8;
+        for (int kh = 0; kh < p.k; ++kh) {
+            const int h = h0 + kh;
+            if (h < 0 || h >= p.H) continue;
+            for (int kw = 0; kw < p.k; ++kw) {
+                const int w = w0 + kw;
+                if (w < 0 || w >= p.W) continue;
+                float v[8];
+                V8<T>::ld(xb + ((size_t)h * p.W + w) * p.C, v);
+                const unsigned code = kh * p.k + kw;
+#pragma unroll
+                for (int c = 0; c < 8; ++c)
+                    if (v[c] > best[c]) { best[c] = v[c]; arg[c] = code; }
+            }
+        }
+        const size_t o = (((size_t)n * p.OH + oh) * p.OW + ow) * p.C + cg * 8;
+        V8<T>::st(reinterpret_cast<T*>(p.y) + o, best);
+        if (p.idx) {
+            uint2 packed;
+            packed.x = arg[0] | (arg[1] << 8) | (arg[2] << 16) | (arg[3] << 24);
+            packed.y = arg[4] | (arg[5] << 8) | (arg[6] << 16) | (arg[7] << 24);
+            *reinterpret_cast<uint2*>(p.idx + o) = packed;
+        }
+    }
+}
+
+template <typename T>
+__global__ void __launch_bounds__(256) k_maxpool_bwd(Params p) {
+    const int ncg = p.C >> 3;
+    const long long total = (long long)p.N * p.H * p.W * ncg;
+    for (long long id = (long long)blockIdx.x * blockDim.x + threadIdx.x; id < total; id += (long long)gridDim.x * blockDim.x) {
+        const int cg = (int)(id % ncg);
+        long long pix = id / ncg;
+        const int w = (int)(pix % p.W); pix /= p.W;
+        const int h = (int)(pix % p.H);
+        const int n = (int)(pix / p.H);
+        float acc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+        // output rows/cols whose window [o*s - pad, o*s - pad + k) contains h / w
+        int oh_lo = (h + p.pad - p.k + p.s) / p.s;          // ceil((h + pad - k + 1) / s)
+        if (h + p.pad - p.k + 1 < 0) oh_lo = 0;
+        int oh_hi = (h + p.pad) / p.s;
+        if (oh_hi > p.OH - 1) oh_hi = p.OH - 1;
+        int ow_lo = (w + p.pad - p.k + p.s) / p.s;
+        if (w + p.pad - p.k + 1 < 0) ow_lo = 0;
+        int ow_hi = (w + p.pad) / p.s;
+        if (ow_hi > p.OW - 1) ow_hi = p.OW - 1;
+        for (int oh = oh_lo; oh <= oh_hi; ++oh) {
+            const int kh = h - (oh * p.s - p.pad);
+            for (int ow = ow_lo; ow <= ow_hi; ++ow) {
+                const int kw = w - (ow * p.s - p.pad);
+                const unsigned code = kh * p.k + kw;
+                const size_t o = (((size_t)n * p.OH + oh) * p.OW + ow) * p.C + cg * 8;
+                const uint2 packed = *reinterpret_cast<const uint2*>(p.idx + o);
+                float d[8];
+                V8<T>::ld(reinterpret_cast<const T*>(p.dy) + o, d);
+#pragma unroll
+                for (int c = 0; c < 8; ++c) {
+                    const unsigned a = ((c < 4 ? packed.x : packed.y) >> (8 * (c & 3))) & 0xffu;
+                    if (a == code) acc[c] += d[c];
+                }
+            }
+        }
+        V8<T>::st(reinterpret_cast<T*>(p.dx) + (((size_t)n * p.H + h) * p.W + w) * p.C + cg * 8, acc);
+    }
+}
+
+}  // namespace pool
+}  // namespace lwc
+
+using namespace lwc::pool;
+
+static int grid_for(long long total) {
+    long long b = (total + 255) / 256;
+    const long long cap = 148LL * 16;
+    return (int)(b < cap ? (b < 1 ? 1 : b) : cap);
+}
+
+#define LWC_POOL_DISPATCH(dt, ...)                                             \
+    switch (dt) {                                                              \
+        case LWC_F32: { using T = float; __VA_ARGS__; } break;                 \
+        case LWC_BF16: { using T = __nv_bfloat16; __VA_ARGS__; } break;        \
+        case LWC_F16: { using T = __half; __VA_ARGS__; } break;                \
+        default: return LWC_EINVAL;                                            \
+    }
+
+// idx (N*OH*OW*C bytes) may be NULL for inference.
+extern "C" int lwc_maxpool_forward(const void* x, void* y, void* idx, int N, int H, int W, int C, int k, int stride,
+                                   int pad, int dtype, void* stream) {
+    if (!x || !y || N <= 0 || H <= 0 || W <= 0 || C <= 0 || (C & 7) || k < 1 || k > 15 || stride < 1 || pad < 0 || 2 * pad > k)
+        return LWC_EINVAL;
+    Params p;
+    memset(&p, 0, sizeof(p));
+    p.x = x; p.y = y; p.idx = (uint8_t*)idx;
+    p.N = N; p.H = H; p.W = W; p.C = C; p.k = k; p.s = stride; p.pad = pad;
+    p.OH = (H + 2 * pad - k) / stride + 1;
+    p.OW = (W + 2 * pad - k) / stride + 1;
+    if (p.OH < 1 || p.OW < 1) return LWC_EINVAL;
+    const long long total = (long long)N * p.OH * p.OW * (C >> 3);
+    LWC_POOL_DISPATCH(dtype, k_maxpool_fwd<T><<<grid_for(total), 256, 0, (cudaStream_t)stream>>>(p));
+    return (int)cudaGetLastError();
+}
+
+extern "C" int lwc_maxpool_backward(const void* dy, const void* idx, void* dx, int N, int H, int W, int C, int k,
+                                    int stride, int pad, int dtype, void* stream) {
+    if (!dy || !idx || !dx || N <= 0 || (C & 7) || k < 1 || k > 15 || stride < 1) return LWC_EINVAL;
+    Params p;
+    memset(&p, 0, sizeof(p));
+    p.dy = dy; p.idx = (uint8_t*)const_cast<void*>(idx); p.dx = dx;
+    p.N = N; p.H = H; p.W = W; p.C = C; p.k = k; p.s = stride; p.pad = pad;
+    p.OH = (H + 2 * pad - k) / stride + 1;
+    p.OW = (W + 2 * pad - k) / stride + 1;
+    const long long total = (long long)N * H * W * (C >> 3);
+    LWC_POOL_DISPATCH(dtype, k_maxpool_bwd<T><<<grid_for(total), 256, 0, (cudaStream_t)stream>>>(p));
+    return (int)cudaGetLastError();
+}

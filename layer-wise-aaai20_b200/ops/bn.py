@@ -78,16 +78,18 @@ class _BatchNormAct(torch.autograd.Function):
         _native.counters.add(3 if training else 1)
         ctx.training, ctx.relu, ctx.has_res = training, relu, residual is not None
         ctx.eps = eps
+        # the ReLU mask is recomputed from x unless a residual was fused (then it depends on y)
+        need_y = relu and (residual is not None or not training)
         if training:
-            ctx.save_for_backward(x, y if relu else None, weight, mean, invstd)
+            ctx.save_for_backward(x, y if need_y else None, weight, mean, invstd, bias)
         else:
-            ctx.save_for_backward(x, y if relu else None, weight, running_mean, running_var)
+            ctx.save_for_backward(x, y if need_y else None, weight, running_mean, running_var, bias)
         return y
 
     @staticmethod
     def backward(ctx, dy):
         lib = _native.lib()
-        x, y, weight, mean, invstd = ctx.saved_tensors
+        x, y, weight, mean, invstd, bias = ctx.saved_tensors
         M, Cc = _rows_channels(x)
         if _rows_channels(dy) is None or dy.stride() != x.stride():
             dy = dy.contiguous(memory_format=torch.channels_last) if x.dim() == 4 else dy.contiguous()
@@ -108,7 +110,7 @@ class _BatchNormAct(torch.autograd.Function):
         ws_ptr = _workspace(int(lib.lwc_bn_workspace_bytes(M, Cc)), x.device).data_ptr()
         st = torch.cuda.current_stream().cuda_stream
         rc = lib.lwc_bn_backward(dy.data_ptr(), x.data_ptr(), _ptr(y), dx.data_ptr(), _ptr(dres), _ptr(weight),
-                                 mean.data_ptr(), invstd.data_ptr(), dgamma.data_ptr(), dbeta.data_ptr(), ws_ptr,
+                                 _ptr(bias), mean.data_ptr(), invstd.data_ptr(), dgamma.data_ptr(), dbeta.data_ptr(), ws_ptr,
                                  M, Cc, abi.dtype_code(x.dtype), int(ctx.relu), C.c_void_p(st))
         abi.check(rc, "lwc_bn_backward")
         _native.counters.add(3)

@@ -45,6 +45,23 @@ def main():
     tot = sum(v[1] for v in agg.values())
     rows = sorted(agg.items(), key=lambda kv: -kv[1][1])
     print(f"total device time per step: {tot / args.steps / 1e3:.3f} ms over {sum(v[0] for v in agg.values()) / args.steps:.0f} kernels")
+    cats = collections.OrderedDict([("bn (ours)", "lwc::bn"), ("exchange (ours)", "lwc::k_"), ("sgd (ours)", "lwc::k_sgd"),
+                                    ("pool (ours)", "lwc::pool"), ("gemm (ours)", "lwc::gemm"),
+                                    ("conv/gemm (cudnn/cublas)", ("cutlass", "nvjet", "xmma", "cudnn", "implicit_gemm", "nhwc")),
+                                    ("elementwise/other (aten)", "at::native")])
+    csum = collections.defaultdict(float)
+    for name, (c, t) in rows:
+        for cat, pat in cats.items():
+            pats = pat if isinstance(pat, tuple) else (pat,)
+            if cat == "exchange (ours)" and "k_sgd" in name:
+                continue
+            if any(x in name for x in pats):
+                csum[cat] += t
+                break
+        else:
+            csum["unclassified"] += t
+    for cat, t in csum.items():
+        print(f"  [{cat:28s}] {t / args.steps / 1e3:8.3f} ms/step {100 * t / tot:5.1f}%")
     out = []
     for name, (c, t) in rows[:args.top]:
         print(f"{t / args.steps:10.1f} us/step {c / args.steps:7.1f} calls {100 * t / tot:5.1f}%  {name[:100]}")
