@@ -80,3 +80,20 @@ def train(model, optimizer, train_batches, test_batches, epochs, master_address=
         for logger in loggers:
             logger.append(summary)
     return summary
+
+
+def warmup(model, batch_size: int, device=None, dtype=torch.float32, channels_last: bool = False):
+    """One forward/backward on random inputs before timing starts (kernel selection, allocator
+    warm-up, native-library load) -- the role of the reference's ``warmup_cudnn``
+    (CIFAR10/torch_backend.py:18-29)."""
+    device = device or next(model.parameters()).device
+    x = torch.rand(batch_size, 3, 32, 32, device=device).to(dtype)
+    if channels_last:
+        x = x.contiguous(memory_format=torch.channels_last)
+    batch = {"input": x, "target": torch.randint(0, 10, (batch_size,), device=device)}
+    model.train(True)
+    out = model(batch)
+    out["loss"].sum().backward()
+    model.zero_grad(set_to_none=False)
+    if torch.cuda.is_available():
+        torch.cuda.synchronize()

@@ -115,6 +115,10 @@ class DataManager:
 
     def set_epoch(self, epoch):
         phase = self.get_phase(epoch)
+        if phase is None and self.trn_dl is None:
+            # resumed in the middle of a phase: fall back to the latest data phase that has started
+            started = [p for p in self.phases if not p.get("keep_dl", False) and p["ep"] <= epoch]
+            phase = max(started, key=lambda p: p["ep"]) if started else None
         if phase:
             self.set_data(phase)
         for smp in (self.trn_smp, self.val_smp):
@@ -193,7 +197,8 @@ def main(argv=None):
     last_epoch = scheduler.tot_epochs if args.epochs is None else min(scheduler.tot_epochs, args.start_epoch + args.epochs)
     top1 = top5 = 0.0
     for epoch in range(args.start_epoch, last_epoch):
-        dm.set_epoch(epoch)
+        phase = dm.get_phase(epoch)      # looked up before set_epoch consumes it (the reference looks
+        dm.set_epoch(epoch)              # afterwards and therefore never writes its phase checkpoints)
         train_epoch(trainer, dm.trn_dl, scheduler, epoch, log, tb, args.short_epoch, args.print_freq)
         top1, top5 = validate(trainer, dm.val_dl, epoch, log, tb, args.short_epoch, args.print_freq)
         hours = (datetime.now() - start_time).total_seconds() / 3600.0
@@ -203,7 +208,6 @@ def main(argv=None):
         if is_rank0:
             if is_best:
                 trainer.save(epoch, best_top5, "model_best.pth.tar", is_best=True, logdir=args.logdir or None)
-            phase = dm.get_phase(epoch)
             if phase:
                 trainer.save(epoch, best_top5, f'sz{phase["bs"]}_checkpoint.path.tar')
     tb.close()
