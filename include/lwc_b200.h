@@ -118,6 +118,14 @@ int lwc_plan_recv(LwcPlan* plan, uint64_t step, void* stream);
  * [2]=flag wait timeouts, [3]=payload bytes stored per destination */
 int lwc_plan_stats(LwcPlan* plan, uint64_t out[4], void* stream);
 
+/* Dense two-shot all-reduce over peer memory, in place on gradient arenas that live in the
+ * peer-mapped heap: rank r sums slice r of all arenas in rank order, scales by 1/world and stores it
+ * into every arena.  arena_dev[r] / flags_dev[r] = rank r's arena base and flag block
+ * (2 * LWC_MAX_WORLD uint64, zero-initialised); counters_dev = 2 local uint64 (zeroed).
+ * (CIFAR10/core.py:316-319; IMAGENET/training/train_imagenet_nv.py:382-386; ddp.py:434-475) */
+int lwc_dense_allreduce(void* const* arena_dev, void* const* flags_dev, void* counters_dev, int64_t off,
+                        int64_t n, int dtype, int world, int rank, uint64_t step, void* stream);
+
 /* ------------------------------------------------------------------------------------------
  * Stand-alone exact Top-k selection of one fp32 vector (the K1 kernel family without the
  * exchange): threshold = keep-th largest |x|, every |x| >= threshold and != 0 is emitted in

@@ -71,6 +71,7 @@ def declare(lib: C.CDLL):
     sig("lwc_plan_send", C.c_int, vp, u64, vp)
     sig("lwc_plan_recv", C.c_int, vp, u64, vp)
     sig("lwc_plan_stats", C.c_int, vp, C.POINTER(u64), vp)
+    sig("lwc_dense_allreduce", C.c_int, c_void_pp, c_void_pp, vp, i64, i64, C.c_int, C.c_int, C.c_int, u64, vp)
     sig("lwc_topk_workspace_bytes", sz, i64)
     sig("lwc_topk_select_f32", C.c_int, vp, i64, i64, i64, vp, vp, vp, vp, vp)
     sig("lwc_topk_select_f32_noalloc", C.c_int, vp, i64, i64, i64, vp, vp, vp, vp)

@@ -1206,3 +1206,124 @@ extern "C" int lwc_topk_select_f32_noalloc(const float* x_dev, int64_t n, int64_
     return lwc_topk_select_impl(x_dev, n, keep, cap, idx_out_dev, val_out_dev, count_out_dev, scratch,
                                 (cudaStream_t)stream);
 }
+
+// =====================================================================================================
+// Dense two-shot all-reduce over peer memory (the `--compress none` / DDP path for large dense models).
+//
+// Every rank's gradient arena lives in the peer-mapped heap.  Rank r owns slice r: it loads that slice
+// from all W arenas (P2P loads over NVLink), sums in rank order, scales by 1/W and stores the result
+// into slice r of all W arenas (P2P stores) -- reduce-scatter and all-gather in one kernel, 2(W-1)/W of
+// the data per direction instead of the (W-1)x of the one-shot slots.  Two flag rounds: READY ("my
+// gradients are final", written at kernel start) and DONE ("my slice has landed everywhere").
+// Reference op: per-tensor dist.all_reduce + /W (CIFAR10/core.py:316-319; train_imagenet_nv.py:382-386).
+// =====================================================================================================
+namespace lwc {
+struct DevAR {
+    char* arena[LWC_MAX_WORLD];
+    uint64_t* flags[LWC_MAX_WORLD];     // per rank: [2][LWC_MAX_WORLD] (ready row, done row)
+    unsigned long long* counters;       // [0] ticket, [1] timeouts   (local)
+    long long off, n;                   // element range [off, off + n) of the arena
+    int world, rank;
+    unsigned long long step;
+};
+
+__device__ __forceinline__ void ar_wait(const DevAR& p, int row) {
+    if (threadIdx.x < p.world && (int)threadIdx.x != p.rank) {
+        const uint64_t* f = p.flags[p.rank] + row * LWC_MAX_WORLD + threadIdx.x;
+        const uint64_t want = p.step + 1;
+        const uint64_t t0 = global_timer_ns();
+        unsigned spins = 0;
+        while (ld_acquire_sys(f) < want) {
+            if ((++spins & 1023u) == 0 && global_timer_ns() - t0 > 10000000000ULL) {
+                atomicAdd(p.counters + 1, 1ULL);
+                break;
+            }
+            __nanosleep(64);
+        }
+    }
+    __syncthreads();
+}
+
+template <typename T>
+__global__ void __launch_bounds__(512) k_allreduce_two_shot(DevAR p) {
+    constexpr int V = 16 / sizeof(T);         // elements per 16-byte vector
+    if (blockIdx.x == 0 && threadIdx.x < p.world)
+        st_release_sys(p.flags[threadIdx.x] + 0 * LWC_MAX_WORLD + p.rank, p.step + 1);     // READY
+    ar_wait(p, 0);
+    // slice of this rank, in vectors
+    const long long nvec = (p.n + V - 1) / V;                 // arena padding makes the tail vector addressable
+    const long long per = (nvec + p.world - 1) / p.world;
+    const long long v0 = per * p.rank, v1 = min(nvec, v0 + per);
+    const float inv = 1.0f / (float)p.world;
+    for (long long v = v0 + (long long)blockIdx.x * blockDim.x + threadIdx.x; v < v1; v += (long long)gridDim.x * blockDim.x) {
+        const size_t byte = ((size_t)p.off * sizeof(T)) + (size_t)v * 16;
+        float acc[V];
+#pragma unroll
+        for (int k = 0; k < V; ++k) acc[k] = 0.0f;
+        uint4 raw[LWC_MAX_WORLD];
+#pragma unroll
+        for (int s = 0; s < LWC_MAX_WORLD; ++s)
+            if (s < p.world) raw[s] = *reinterpret_cast<const uint4*>(p.arena[s] + byte);
+#pragma unroll
+        for (int s = 0; s < LWC_MAX_WORLD; ++s) {
+            if (s >= p.world) break;
+            const T* e = reinterpret_cast<const T*>(&raw[s]);
+#pragma unroll
+            for (int k = 0; k < V; ++k) acc[k] += DT<T>::ld(e + k);
+        }
+        uint4 outv;
+        T* o = reinterpret_cast<T*>(&outv);
+#pragma unroll
+        for (int k = 0; k < V; ++k) DT<T>::st(o + k, acc[k] * inv);
+#pragma unroll
+        for (int d = 0; d < LWC_MAX_WORLD; ++d)
+            if (d < p.world) *reinterpret_cast<uint4*>(p.arena[d] + byte) = outv;
+    }
+    __threadfence_system();
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        const unsigned long long ticket = atomicAdd(p.counters, 1ULL);
+        if (ticket == gridDim.x - 1) {
+            __threadfence_system();
+            p.counters[0] = 0;
+            for (int d = 0; d < p.world; ++d) st_release_sys(p.flags[d] + 1 * LWC_MAX_WORLD + p.rank, p.step + 1);   // DONE
+        }
+    }
+}
+
+__global__ void k_allreduce_wait_done(DevAR p) { ar_wait(p, 1); }
+}  // namespace lwc
+
+// arena_dev[r] / flags_dev[r]: rank r's arena base and flag block (2 * LWC_MAX_WORLD uint64, zeroed) as seen from
+// this rank; counters_dev: 2 local uint64 (zeroed).  The arena allocation must be padded to a multiple of 16 bytes
+// past off + n.  In-place: on return (stream order) every arena holds the average.
+extern "C" int lwc_dense_allreduce(void* const* arena_dev, void* const* flags_dev, void* counters_dev, int64_t off,
+                                   int64_t n, int dtype, int world, int rank, uint64_t step, void* stream) {
+    if (!arena_dev || !flags_dev || !counters_dev || n <= 0 || world < 1 || world > LWC_MAX_WORLD || rank < 0 || rank >= world)
+        return LWC_EINVAL;
+    const size_t esz = dtype == LWC_F32 ? 4 : 2;
+    if (((size_t)off * esz) & 15) return LWC_EINVAL;
+    DevAR p;
+    memset(&p, 0, sizeof(p));
+    for (int r = 0; r < world; ++r) {
+        if (!arena_dev[r] || !flags_dev[r]) return LWC_EINVAL;
+        p.arena[r] = (char*)arena_dev[r];
+        p.flags[r] = (uint64_t*)flags_dev[r];
+    }
+    p.counters = (unsigned long long*)counters_dev;
+    p.off = off; p.n = n; p.world = world; p.rank = rank; p.step = step;
+    cudaStream_t st = (cudaStream_t)stream;
+    const long long nvec = ((long long)n * (long long)esz + 15) / 16;
+    const long long per = (nvec + world - 1) / world;
+    long long blocks = (per + 511) / 512;
+    if (blocks > 148 * 2) blocks = 148 * 2;
+    if (blocks < 1) blocks = 1;
+    switch (dtype) {
+        case LWC_F32: k_allreduce_two_shot<float><<<(int)blocks, 512, 0, st>>>(p); break;
+        case LWC_BF16: k_allreduce_two_shot<__nv_bfloat16><<<(int)blocks, 512, 0, st>>>(p); break;
+        case LWC_F16: k_allreduce_two_shot<__half><<<(int)blocks, 512, 0, st>>>(p); break;
+        default: return LWC_EINVAL;
+    }
+    k_allreduce_wait_done<<<1, 32, 0, st>>>(p);
+    return (int)cudaGetLastError();
+}

@@ -225,8 +225,11 @@ class GradientExchanger:
         if engine == "fused" and not use_fused:
             raise RuntimeError("fused engine needs CUDA parameters")
         if use_fused:
-            from .fused import FusedEngine
-            self.engine = FusedEngine(self.params, cfg, group=group, overlap=overlap, **engine_kw)
+            from .fused import DenseEngine, FusedEngine
+            if cfg.method_name == cref.NONE and engine_kw.pop("dense", "two_shot") == "two_shot":
+                self.engine = DenseEngine(self.params, cfg, group=group, overlap=overlap, **engine_kw)
+            else:
+                self.engine = FusedEngine(self.params, cfg, group=group, overlap=overlap, **engine_kw)
         else:
             self.engine = TorchEngine(self.params, cfg, group=group)
 

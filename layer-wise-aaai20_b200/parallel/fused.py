@@ -375,3 +375,163 @@ class FusedEngine:
         for b in self.buckets:
             b.plan.close()
         self.heap.close()
+
+
+# --------------------------------------------------------------------------------------------------------
+class DenseEngine:
+    """Uncompressed gradient averaging (``--compress none`` and the dense DDP wrapper) as a two-shot
+    all-reduce over peer memory (``lwc_dense_allreduce``): the gradient arenas themselves live in the
+    peer-mapped heap, rank r reduces slice r of every arena and stores the average back everywhere.
+    Buckets are contiguous arena ranges in reverse parameter order; with ``overlap=True`` each is
+    launched from the hook of its last gradient on a side stream.
+    Reference: per-tensor ``dist.all_reduce`` + ``/W`` (CIFAR10/core.py:316-319) and the bucketed hook-driven
+    all-reduce of the vendored DDP (IMAGENET/training/ddp.py:394-475)."""
+
+    name = "fused-dense"
+    FLAGS = 2 * abi.LWC_MAX_WORLD * 8       # ready row + done row
+    AUX = FLAGS + 64                        # + ticket / timeout counters
+
+    def __init__(self, params: List[torch.nn.Parameter], cfg, group=None, overlap: bool = False, **_unused):
+        _native.require()
+        self.lib = _native.lib()
+        self.params, self.cfg, self.group = params, cfg, group
+        self.world, self.rank = comm.world_size(group), comm.rank(group)
+        if self.world > abi.LWC_MAX_WORLD:
+            raise ValueError(f"fused engine supports up to {abi.LWC_MAX_WORLD} ranks per node")
+        self.device = params[0].device
+        self.step = 0
+        self.overlap = overlap
+        # ---- arena layout inside the heap ------------------------------------------------------------------
+        by_dtype: Dict[torch.dtype, List[int]] = {}
+        for i, p in enumerate(params):
+            by_dtype.setdefault(p.dtype, []).append(i)
+        self._layout = {}
+        heap_bytes = 0
+        offs_in_arena = {}
+        for dt, idx in by_dtype.items():
+            esz = torch.empty((), dtype=dt).element_size()
+            total = 0
+            for i in idx:
+                offs_in_arena[i] = total
+                total += (params[i].numel() + 63) // 64 * 64
+            self._layout[dt] = (heap_bytes, total, esz, idx)
+            heap_bytes += (total * esz + 255) // 256 * 256
+        # ---- buckets: contiguous ranges per dtype, reverse order --------------------------------------------
+        cap = cfg.bucket_cap_mb * (1 << 20) if overlap else float("inf")
+        self.buckets = []
+        for dt, (base, total, esz, idx) in self._layout.items():
+            cur: List[int] = []
+            size = 0
+            for i in reversed(idx):
+                nbytes = params[i].numel() * esz
+                if cur and size + nbytes > cap:
+                    self.buckets.append({"dtype": dt, "idxs": cur})
+                    cur, size = [], 0
+                cur.append(i)
+                size += nbytes
+            if cur:
+                self.buckets.append({"dtype": dt, "idxs": cur})
+        aux_base = heap_bytes
+        heap_bytes += self.AUX * len(self.buckets)
+        self.heap = PeerHeap(heap_bytes, group=group, device=self.device)
+        self._grad_arena = {}
+        self.grad_views: List[torch.Tensor] = [None] * len(params)
+        for dt, (base, total, esz, idx) in self._layout.items():
+            arena = self.heap.local.view(dt, total, base)
+            self._grad_arena[dt] = arena
+            for i in idx:
+                self.grad_views[i] = arena[offs_in_arena[i]:offs_in_arena[i] + params[i].numel()]
+        for bi, b in enumerate(self.buckets):
+            base, total, esz, _ = self._layout[b["dtype"]]
+            lo = min(offs_in_arena[i] for i in b["idxs"])
+            hi = max(offs_in_arena[i] + (params[i].numel() + 63) // 64 * 64 for i in b["idxs"])
+            b.update(off=lo, n=hi - lo, pending=0, launched=False,
+                     arenas=_ptr_array([ptr + base for ptr in self.heap.ptrs]),
+                     flags=_ptr_array([ptr + aux_base + bi * self.AUX for ptr in self.heap.ptrs]),
+                     counters=self.heap.local.ptr + aux_base + bi * self.AUX + self.FLAGS)
+        self._adopt_grads()
+        self.comm_stream = torch.cuda.Stream(device=self.device) if overlap else None
+        self._hooks = []
+        if overlap:
+            self._param_bucket = {i: bi for bi, b in enumerate(self.buckets) for i in b["idxs"]}
+            for i, p in enumerate(params):
+                self._hooks.append(p.register_post_accumulate_grad_hook(self._make_hook(i)))
+            self._reset_pending()
+
+    _shaped = FusedEngine._shaped
+    _adopt_grads = FusedEngine._adopt_grads
+    zero_grad = FusedEngine.zero_grad
+
+    def _launch(self, b, stream=None):
+        if self.world == 1:
+            return
+        st = (stream or torch.cuda.current_stream()).cuda_stream
+        abi.check(self.lib.lwc_dense_allreduce(b["arenas"], b["flags"], C.c_void_p(b["counters"]), b["off"], b["n"],
+                                               abi.dtype_code(b["dtype"]), self.world, self.rank, C.c_uint64(self.step),
+                                               C.c_void_p(st)), "lwc_dense_allreduce")
+        _native.counters.add(2)
+
+    @torch.no_grad()
+    def exchange(self):
+        if self.overlap:
+            return self.finish()
+        self._adopt_grads()
+        for b in self.buckets:
+            self._launch(b)
+        self.step += 1
+
+    def _reset_pending(self):
+        for b in self.buckets:
+            b["pending"] = len(b["idxs"])
+            b["launched"] = False
+
+    def _make_hook(self, i: int):
+        def hook(param):
+            b = self.buckets[self._param_bucket[i]]
+            if param.grad is not None and param.grad.data_ptr() != self.grad_views[i].data_ptr():
+                shaped = self._shaped(i)
+                shaped.copy_(param.grad)
+                param.grad = shaped
+            b["pending"] -= 1
+            if b["pending"] == 0 and not b["launched"]:
+                b["launched"] = True
+                self.comm_stream.wait_stream(torch.cuda.current_stream())
+                self._launch(b, self.comm_stream)
+        return hook
+
+    @torch.no_grad()
+    def finish(self):
+        if not self.overlap:
+            return
+        cur = torch.cuda.current_stream()
+        self.comm_stream.wait_stream(cur)
+        for b in self.buckets:
+            if not b["launched"]:
+                self._launch(b, self.comm_stream)
+        cur.wait_stream(self.comm_stream)
+        self.step += 1
+        self._reset_pending()
+
+    def state_dict(self):
+        return {"residual": None, "step": self.step}
+
+    def load_state_dict(self, sd):
+        self.step = max(self.step, int(sd.get("step", 0)))
+
+    def stats(self):
+        timeouts = 0
+        for b in self.buckets:
+            base, total, esz, _ = self._layout[b["dtype"]]
+        torch.cuda.synchronize()
+        aux = self.heap.local.view(torch.int64, (self.AUX * len(self.buckets)) // 8,
+                                   self.heap.nbytes - self.AUX * len(self.buckets))
+        per = self.AUX // 8
+        for bi in range(len(self.buckets)):
+            timeouts += int(aux[bi * per + self.FLAGS // 8 + 1].item())
+        nbytes = sum(b["n"] * self._layout[b["dtype"]][2] for b in self.buckets)
+        return {"sent": 0, "dropped": 0, "timeouts": timeouts, "bytes": int(2 * nbytes * (self.world - 1) / max(self.world, 1))}
+
+    def close(self):
+        for h in self._hooks:
+            h.remove()
+        self.heap.close()
