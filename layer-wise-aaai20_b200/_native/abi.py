@@ -68,6 +68,7 @@ def declare(lib: C.CDLL):
     sig("lwc_plan_region_bytes", sz, vp)
     sig("lwc_plan_bind", C.c_int, vp, c_void_pp, c_void_pp)
     sig("lwc_plan_set_random", C.c_int, vp, c_void_pp)
+    sig("lwc_plan_update_grads", C.c_int, vp, c_void_pp, vp)
     sig("lwc_plan_send", C.c_int, vp, u64, vp)
     sig("lwc_plan_recv", C.c_int, vp, u64, vp)
     sig("lwc_plan_stats", C.c_int, vp, C.POINTER(u64), vp)
@@ -88,6 +89,7 @@ def declare(lib: C.CDLL):
         C.c_int, vp)
     sig("lwc_maxpool_backward", C.c_int, vp, vp, vp, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int,
         C.c_int, vp)
+    sig("lwc_normalize_u8", C.c_int, vp, vp, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, vp, vp, C.c_int, vp)
     sig("lwc_sgd_plan_create", C.c_int, c_void_pp, C.POINTER(LwcSgdTensor), i32)
     sig("lwc_sgd_plan_destroy", C.c_int, vp)
     sig("lwc_sgd_step", C.c_int, vp, C.POINTER(LwcSgdDesc), vp)

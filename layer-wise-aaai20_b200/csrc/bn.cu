@@ -228,7 +228,7 @@ __device__ __forceinline__ double warp_sum_d(double v) {
     return v;
 }
 
-constexpr int MAX_PART_PER_LANE = 20;     // plan_grid keeps nblk <= 32 * 20
+constexpr int MAX_PART_PER_LANE = 10;     // plan_grid keeps nblk <= 32 * 10
 
 // All partials of a channel are fetched up front (<= 20 independent loads per lane), so the kernel pays
 // the memory latency once instead of once per loop iteration.
@@ -481,12 +481,12 @@ static void plan_grid(long long M, int C, int* nblk, int* rows_per_blk, dim3* gr
     const int tpr = ncg < THREADS ? ncg : THREADS;
     const int rpp = THREADS / tpr;
     const int gy = (ncg + tpr - 1) / tpr;
-    // ~4 CTAs per SM, at least 4 passes of rows per CTA
-    long long target = (148LL * 4 + gy - 1) / gy;
+    // 2 CTAs per SM (16 warps x 8-12 outstanding 16-byte loads each), at least 16 passes of rows per CTA
+    long long target = (148LL * 2 + gy - 1) / gy;
     long long rows = (M + target - 1) / target;
-    const long long min_rows = 4LL * rpp;
+    const long long min_rows = 16LL * rpp;
     if (rows < min_rows) rows = min_rows;
-    const long long max_blk = 32LL * 20;                 // k_bn_finalize holds <= 20 partials per lane
+    const long long max_blk = 32LL * 10;                 // k_bn_finalize holds <= 10 partials per lane
     if ((M + rows - 1) / rows > max_blk) rows = (M + max_blk - 1) / max_blk;
     rows = (rows + rpp - 1) / rpp * rpp;
     *rows_per_blk = (int)rows;

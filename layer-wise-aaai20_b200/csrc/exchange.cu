@@ -468,7 +468,6 @@ __global__ void __launch_bounds__(kThreads) k_compact_send(DevPlan p) {
     __shared__ uint32_t st_idx[kStage];
     __shared__ float st_val[kStage];
     __shared__ unsigned sh_warp[kThreads / 32];
-    __shared__ unsigned sh_base;
     const ChunkRec c = p.chunks[blockIdx.x];
     const TensorRec t = p.tensors[c.tensor];
     const GroupCfg cfg = p.gcfg[t.group];
@@ -500,76 +499,88 @@ __global__ void __launch_bounds__(kThreads) k_compact_send(DevPlan p) {
         long long* hdr = reinterpret_cast<long long*>(slot_ptr(p, tid, p.rank));
         hdr[t.group] = (long long)gs.kept;
     }
-    if (tid == 0) sh_base = 0;
-    __syncthreads();
-
+    // Each warp owns a contiguous 1024-element range (8 coalesced iterations of 128 elements); the values and
+    // predicate bits stay in registers, so the gradient is read once and the block synchronises twice.
+    constexpr int kWarps = kThreads / 32;
+    constexpr int kPerWarp = kChunk / kWarps;
+    constexpr int kIters = kPerWarp / 128;
+    float v[kIters][4];
+    unsigned fl[kIters], excl[kIters];
     if (n_out > 0) {
-        for (int it = 0; it < kQuadsPerThread; ++it) {
-            const int j = (it * kThreads + tid) * 4;
-            float v[4] = {0.f, 0.f, 0.f, 0.f};
-            unsigned fl = 0;      // bit k: gt, bit 4+k: eq
+        unsigned run_base = 0;        // packed (gt | eq << 16) count of this warp before iteration `it`
+#pragma unroll
+        for (int it = 0; it < kIters; ++it) {
+            const int j = warp * kPerWarp + it * 128 + lane * 4;
+            v[it][0] = v[it][1] = v[it][2] = v[it][3] = 0.0f;
+            unsigned f = 0;           // bit k: key > T, bit 4+k: key == T
             if (j < c.len) {
-                load_acc<GradT>(t, c.start, j, c.len, v);
+                load_acc<GradT>(t, c.start, j, c.len, v[it]);
 #pragma unroll
                 for (int k = 0; k < 4; ++k) {
-                    if (j + k >= c.len || v[k] == 0.0f) continue;
+                    if (j + k >= c.len || v[it][k] == 0.0f) continue;
                     const long long i = c.start + j + k;
-                    const uint32_t key = make_key(p.method, v[k], t.rnd, i, t.goff + i, salt);
-                    fl |= (key > T) ? (1u << k) : (key == T ? (16u << k) : 0u);
+                    const uint32_t key = make_key(p.method, v[it][k], t.rnd, i, t.goff + i, salt);
+                    f |= (key > T) ? (1u << k) : (key == T ? (16u << k) : 0u);
                 }
             }
-            const unsigned mine = __popc(fl & 0xfu) | (__popc(fl >> 4) << 16);
+            fl[it] = f;
+            const unsigned mine = __popc(f & 0xfu) | (__popc(f >> 4) << 16);
             const unsigned incl = warp_incl_scan(mine);
-            if (lane == 31) sh_warp[warp] = incl;
-            __syncthreads();
-            unsigned wbase = sh_base;
-#pragma unroll
-            for (int w = 0; w < kThreads / 32; ++w)
-                if (w < warp) wbase += sh_warp[w];
-            unsigned run = wbase + incl - mine;     // exclusive (gt | eq<<16) before this thread
-            if (fl) {
-#pragma unroll
-                for (int k = 0; k < 4; ++k) {
-                    const bool is_gt = (fl >> k) & 1u, is_eq = (fl >> (4 + k)) & 1u;
-                    if (!(is_gt || is_eq)) continue;
-                    const unsigned long long g_before = gt_off + (run & 0xffffu);
-                    const unsigned long long e_before = eq_off + (run >> 16);
-                    const unsigned long long pos = pos_of(g_before, e_before);
-                    const bool keep = pos < cap && (is_gt || e_before < quota);
-                    run += is_gt ? 1u : 0x10000u;
-                    if (!keep) continue;
-                    const long long i = c.start + j + k;
-                    const uint32_t gidx = (uint32_t)(t.goff + i);
-                    if (staged) {
-                        st_idx[pos - pos_begin] = gidx;
-                        st_val[pos - pos_begin] = v[k];
-                    } else if (p.direct_idx) {
-                        p.direct_idx[cfg.pay_off + pos] = gidx;
-                        p.direct_val[cfg.pay_off + pos] = v[k];
-                    } else {
-                        for (int d = 0; d < p.world; ++d) {
-                            char* s = slot_ptr(p, d, p.rank);
-                            reinterpret_cast<uint32_t*>(s + p.idx_off)[cfg.pay_off + pos] = gidx;
-                            reinterpret_cast<float*>(s + p.val_off)[cfg.pay_off + pos] = v[k];
-                        }
-                    }
-                    if (t.resid) t.resid[i] = 0.0f;     // sent exactly: nothing left behind
-                }
-            }
-            __syncthreads();
-            if (tid == kThreads - 1) sh_base = wbase + incl;   // last thread holds the block total
-            __syncthreads();
+            excl[it] = run_base + incl - mine;
+            run_base += __shfl_sync(0xffffffffu, incl, 31);
         }
-        if (staged) {
-            const int ndst = p.direct_idx ? 1 : p.world;
-            for (int d = 0; d < ndst; ++d) {
-                char* s = p.direct_idx ? nullptr : slot_ptr(p, d, p.rank);
-                uint32_t* di = (p.direct_idx ? p.direct_idx : reinterpret_cast<uint32_t*>(s + p.idx_off)) + cfg.pay_off + pos_begin;
-                float* dv = (p.direct_val ? p.direct_val : reinterpret_cast<float*>(s + p.val_off)) + cfg.pay_off + pos_begin;
-                for (unsigned e = tid; e < n_out; e += kThreads) {
-                    di[e] = st_idx[e];
-                    dv[e] = st_val[e];
+        if (lane == 0) sh_warp[warp] = run_base;
+    }
+    __syncthreads();
+    if (n_out > 0) {
+        unsigned wbase = 0;
+#pragma unroll
+        for (int w = 0; w < kWarps; ++w)
+            if (w < warp) wbase += sh_warp[w];
+#pragma unroll
+        for (int it = 0; it < kIters; ++it) {
+            if (!fl[it]) continue;
+            const int j = warp * kPerWarp + it * 128 + lane * 4;
+            unsigned run = wbase + excl[it];
+#pragma unroll
+            for (int k = 0; k < 4; ++k) {
+                const bool is_gt = (fl[it] >> k) & 1u, is_eq = (fl[it] >> (4 + k)) & 1u;
+                if (!(is_gt || is_eq)) continue;
+                const unsigned long long g_before = gt_off + (run & 0xffffu);
+                const unsigned long long e_before = eq_off + (run >> 16);
+                const unsigned long long pos = pos_of(g_before, e_before);
+                const bool keep = pos < cap && (is_gt || e_before < quota);
+                run += is_gt ? 1u : 0x10000u;
+                if (!keep) continue;
+                const long long i = c.start + j + k;
+                const uint32_t gidx = (uint32_t)(t.goff + i);
+                if (staged) {
+                    st_idx[pos - pos_begin] = gidx;
+                    st_val[pos - pos_begin] = v[it][k];
+                } else if (p.direct_idx) {
+                    p.direct_idx[cfg.pay_off + pos] = gidx;
+                    p.direct_val[cfg.pay_off + pos] = v[it][k];
+                } else {
+                    for (int d = 0; d < p.world; ++d) {
+                        char* s = slot_ptr(p, d, p.rank);
+                        reinterpret_cast<uint32_t*>(s + p.idx_off)[cfg.pay_off + pos] = gidx;
+                        reinterpret_cast<float*>(s + p.val_off)[cfg.pay_off + pos] = v[it][k];
+                    }
                 }
+                if (t.resid) t.resid[i] = 0.0f;     // sent exactly: nothing left behind
+            }
+        }
+    }
+    __syncthreads();
+    if (n_out > 0 && staged) {
+        const int ndst = p.direct_idx ? 1 : p.world;
+        for (int d = 0; d < ndst; ++d) {
+            char* s = p.direct_idx ? nullptr : slot_ptr(p, d, p.rank);
+            uint32_t* di = (p.direct_idx ? p.direct_idx : reinterpret_cast<uint32_t*>(s + p.idx_off)) + cfg.pay_off + pos_begin;
+            float* dv = (p.direct_val ? p.direct_val : reinterpret_cast<float*>(s + p.val_off)) + cfg.pay_off + pos_begin;
+            for (unsigned e = tid; e < n_out; e += kThreads) {
+                di[e] = st_idx[e];
+                dv[e] = st_val[e];
             }
         }
     }
@@ -1326,4 +1337,19 @@ extern "C" int lwc_dense_allreduce(void* const* arena_dev, void* const* flags_de
     }
     k_allreduce_wait_done<<<1, 32, 0, st>>>(p);
     return (int)cudaGetLastError();
+}
+
+// Re-point the *input* gradient of every tensor of a plan (outputs, residuals and geometry unchanged).
+// Lets autograd hand over freshly allocated gradient tensors without an accumulate/copy pass: the
+// plan reads them where they are and writes the averaged gradient into its stable output arena.
+// The table upload is ordered on `stream` before the kernels that follow.
+extern "C" int lwc_plan_update_grads(LwcPlan* P, const void* const* grad_dev, void* stream) {
+    if (!P || !grad_dev) return LWC_EINVAL;
+    for (int t = 0; t < P->num_tensors; ++t) {
+        if (!grad_dev[t]) return LWC_EINVAL;
+        P->h_tensors[t].grad = grad_dev[t];
+    }
+    LWC_CUDA_CHECK(cudaMemcpyAsync(P->d_tensors, P->h_tensors.data(), sizeof(TensorRec) * P->h_tensors.size(),
+                                   cudaMemcpyHostToDevice, (cudaStream_t)stream));
+    return 0;
 }

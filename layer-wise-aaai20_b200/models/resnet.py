@@ -10,7 +10,9 @@ starts at zero and the classifier weights are drawn from N(0, 0.01)
 """
 from __future__ import annotations
 
+import torch
 import torch.nn as nn
+import torch.nn.functional as F
 
 from ..ops import nn as lnn
 
@@ -114,8 +116,17 @@ class ResNet(nn.Module):
         layers += [block(self.inplanes, planes) for _ in range(1, blocks)]
         return nn.Sequential(*layers)
 
+    def stem(self, x):
+        """7x7/2 stem.  A 16-channel input is the 2x2 space-to-depth form produced by
+        ``ops.input.normalize_u8(..., s2d=True)``: the same convolution expressed as a dense 4x4/1 one
+        (K = 256 instead of a 3-channel 7x7 window), which maps onto the tensor cores far better."""
+        if x.shape[1] == 16:
+            from ..ops.input import stem_s2d
+            return stem_s2d(x, self.conv1.weight)
+        return self.conv1(x)
+
     def forward(self, x):
-        x = self.maxpool(self.bn1(self.conv1(x), relu=True))
+        x = self.maxpool(self.bn1(self.stem(x), relu=True))
         x = self.layer4(self.layer3(self.layer2(self.layer1(x))))
         x = self.avgpool(x)
         return self.fc(x.reshape(x.size(0), -1))

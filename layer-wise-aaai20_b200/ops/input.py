@@ -1,0 +1,96 @@
+"""Input normalisation: uint8 NCHW batch -> normalised channels-last activations in one kernel, optionally
+in 2x2 space-to-depth form for the 7x7/2 ResNet stem (``csrc/input.cu``).
+
+Reference op: ``BatchTransformDataLoader.process_tensors`` (IMAGENET/training/dataloader.py:88-93).
+"""
+from __future__ import annotations
+
+import ctypes as C
+
+import torch
+import torch.nn.functional as F
+
+from .. import _native
+from .._native import abi
+
+IMAGENET_MEAN = (0.485 * 255, 0.456 * 255, 0.406 * 255)
+IMAGENET_STD = (0.229 * 255, 0.224 * 255, 0.225 * 255)
+
+
+def space_to_depth_reference(xn: torch.Tensor) -> torch.Tensor:
+    """Normalised NCHW [N,3,H,W] -> [N,16,H/2+3,W/2+3] (12 used channels, 2/1 zero border); pure torch."""
+    n, c, h, w = xn.shape
+    x = xn.reshape(n, c, h // 2, 2, w // 2, 2).permute(0, 3, 5, 1, 2, 4).reshape(n, 4 * c, h // 2, w // 2)
+    x = F.pad(x, (2, 1, 2, 1, 0, 16 - 4 * c))
+    return x
+
+
+def s2d_stem_weight(w7: torch.Tensor) -> torch.Tensor:
+    """[Co,3,7,7] stride-2 pad-3 kernel -> the equivalent [Co,16,4,4] stride-1 kernel on the s2d input."""
+    co = w7.shape[0]
+    w8 = F.pad(w7, (1, 0, 1, 0))                                   # zero row / column in front
+    w = w8.reshape(co, 3, 4, 2, 4, 2).permute(0, 3, 5, 1, 2, 4).reshape(co, 12, 4, 4)
+    return F.pad(w, (0, 0, 0, 0, 0, 4))
+
+
+class _StemS2D(torch.autograd.Function):
+    """Stem convolution: forward on the space-to-depth input (dense 4x4/1, K = 256), weight gradient in the
+    original 7x7/2 formulation on the plain 3-channel input (cuDNN's wgrad for the 16-channel 4x4 form is
+    ~2x slower than its 7x7 one on B200).  No input gradient: the stem consumes data."""
+
+    @staticmethod
+    def forward(ctx, xs, x3, w7):
+        w = s2d_stem_weight(w7)
+        if xs.is_contiguous(memory_format=torch.channels_last):
+            w = w.contiguous(memory_format=torch.channels_last)
+        ctx.save_for_backward(x3, w7)
+        return F.conv2d(xs, w, None, stride=1, padding=0)
+
+    @staticmethod
+    def backward(ctx, dy):
+        x3, w7 = ctx.saved_tensors
+        gw = torch.ops.aten.convolution_backward(dy, x3, w7, None, [2, 2], [3, 3], [1, 1], False, [0, 0], 1,
+                                                 [False, True, False])[1]
+        return None, None, gw
+
+
+def stem_s2d(xs: torch.Tensor, w7: torch.Tensor) -> torch.Tensor:
+    x3 = getattr(xs, "plain3", None)
+    if x3 is None or not w7.requires_grad or not torch.is_grad_enabled():
+        w = s2d_stem_weight(w7)
+        if xs.is_contiguous(memory_format=torch.channels_last):
+            w = w.contiguous(memory_format=torch.channels_last)
+        return F.conv2d(xs, w, None, stride=1, padding=0)
+    return _StemS2D.apply(xs, x3, w7)
+
+
+def normalize_u8(x: torch.Tensor, dtype=torch.bfloat16, s2d: bool = False, mean=IMAGENET_MEAN, std=IMAGENET_STD,
+                 keep_plain: bool = False):
+    """uint8 NCHW -> normalised tensor.  CUDA: one fused kernel; returns a channels-last tensor
+    ([N,8,H,W] with 5 zero channels dropped by a view -> [N,3,H,W] is not possible, so the plain mode returns
+    a dense channels-last [N,3,H,W] via torch ops when ``s2d`` is False)."""
+    if s2d and x.is_cuda and _native.available() and x.is_contiguous() and x.dtype == torch.uint8:
+        n, c, h, w = x.shape
+        assert c == 3 and h % 2 == 0 and w % 2 == 0
+        out = torch.empty((n, h // 2 + 3, w // 2 + 3, 16), dtype=dtype, device=x.device)
+        m = (C.c_float * 3)(*mean)
+        s = (C.c_float * 3)(*std)
+        st = torch.cuda.current_stream().cuda_stream
+        abi.check(_native.lib().lwc_normalize_u8(x.data_ptr(), out.data_ptr(), n, h, w, 16, 1, m, s,
+                                                 abi.dtype_code(dtype), C.c_void_p(st)), "lwc_normalize_u8")
+        _native.counters.add(1)
+        res = out.permute(0, 3, 1, 2)           # logical NCHW view of NHWC storage (= channels_last)
+        if keep_plain:
+            # the stem's weight gradient is cheaper in the original 7x7 formulation: keep a 3-channel copy too
+            plain = torch.empty((n, h, w, 3), dtype=dtype, device=x.device)
+            abi.check(_native.lib().lwc_normalize_u8(x.data_ptr(), plain.data_ptr(), n, h, w, 3, 0, m, s,
+                                                     abi.dtype_code(dtype), C.c_void_p(st)), "lwc_normalize_u8")
+            _native.counters.add(1)
+            res.plain3 = plain.permute(0, 3, 1, 2)
+        return res
+    mean_t = torch.tensor(mean, device=x.device).view(1, 3, 1, 1)
+    std_t = torch.tensor(std, device=x.device).view(1, 3, 1, 1)
+    xn = (x.float() - mean_t) / std_t
+    if s2d:
+        return space_to_depth_reference(xn).to(dtype).contiguous(memory_format=torch.channels_last)
+    return xn.to(dtype)

@@ -119,6 +119,11 @@ class ExchangePlan:
             arr = _ptr_array([0 if r is None else r.data_ptr() for r in rand])
             abi.check(self.lib.lwc_plan_set_random(self.handle, arr), "lwc_plan_set_random")
 
+    def update_grads(self, ptrs: Sequence[int], stream=None):
+        """Re-point the input gradients (stream-ordered table upload)."""
+        st = (stream or torch.cuda.current_stream()).cuda_stream
+        abi.check(self.lib.lwc_plan_update_grads(self.handle, _ptr_array(ptrs), C.c_void_p(st)), "lwc_plan_update_grads")
+
     def send(self, step: int, stream=None):
         st = (stream or torch.cuda.current_stream()).cuda_stream
         abi.check(self.lib.lwc_plan_send(self.handle, C.c_uint64(step), C.c_void_p(st)), "lwc_plan_send")
@@ -173,9 +178,13 @@ class FusedEngine:
     name = "fused"
 
     def __init__(self, params: List[torch.nn.Parameter], cfg, group=None, overlap: bool = False,
-                 out_dtype: Optional[torch.dtype] = None, num_buckets: Optional[int] = None):
+                 out_dtype: Optional[torch.dtype] = None, num_buckets: Optional[int] = None, steal: bool = True):
         _native.require()
         self.params, self.cfg, self.group = params, cfg, group
+        # steal=True: ``zero_grad`` sets ``p.grad = None`` so autograd hands over its freshly written
+        # gradient tensors (no accumulate/copy pass); the plans read them in place and write the averaged
+        # gradient into the arena, to which ``p.grad`` is re-pointed after the exchange.
+        self.steal = steal
         self.world = comm.world_size(group)
         self.rank = comm.rank(group)
         if self.world > abi.LWC_MAX_WORLD:
@@ -237,6 +246,11 @@ class FusedEngine:
         self.comm_stream = torch.cuda.Stream(device=self.device) if overlap else None
         self._hooks = []
         self._param_bucket = {}
+        self._shaped_views = [self._shaped(i) for i in range(len(params))]
+        self._arena_ptr = [v.data_ptr() for v in self.grad_views]
+        self._cur_ptr: List[Optional[int]] = list(self._arena_ptr)
+        for b in self.buckets:
+            b.ptrs = [self._arena_ptr[i] for i in b.idxs]
         if overlap:
             for bi, b in enumerate(self.buckets):
                 for i in b.idxs:
@@ -290,20 +304,61 @@ class FusedEngine:
             p.grad = shaped
 
     def zero_grad(self):
-        """One memset per dtype arena instead of one launch per parameter."""
+        """steal mode: drop the gradients (``None``) so the next backward writes fresh tensors that are
+        consumed in place; otherwise one memset per dtype arena instead of one launch per parameter."""
+        if self.steal:
+            for i, p in enumerate(self.params):
+                p.grad = None
+                self._cur_ptr[i] = None
+            return
         for arena in self._grad_arena.values():
             arena.zero_()
+
+    def _note_grad(self, i: int, param):
+        """Record where this step's gradient of parameter i lives (or move it into the arena)."""
+        g = param.grad
+        if g is None:
+            return
+        if g.data_ptr() == self._arena_ptr[i]:
+            self._cur_ptr[i] = self._arena_ptr[i]
+        elif self.steal and g.dtype == param.dtype and g.stride() == param.stride() and g.data_ptr() % 16 == 0:
+            self._cur_ptr[i] = g.data_ptr()
+        else:
+            self._shaped_views[i].copy_(g)
+            param.grad = self._shaped_views[i]
+            self._cur_ptr[i] = self._arena_ptr[i]
+
+    def _send(self, b, stream=None):
+        ptrs = []
+        for i in b.idxs:
+            ptr = self._cur_ptr[i]
+            if ptr is None:                      # parameter produced no gradient this step
+                self.grad_views[i].zero_()
+                ptr = self._arena_ptr[i]
+            ptrs.append(ptr)
+        if ptrs != b.ptrs:
+            b.plan.update_grads(ptrs, stream)
+            b.ptrs = ptrs
+        b.plan.send(self.step, stream)
+
+    def _repoint(self):
+        """After the receivers are queued: every ``p.grad`` is the arena view holding the average."""
+        for p, v in zip(self.params, self._shaped_views):
+            p.grad = v
 
     # ---- after-backward mode -----------------------------------------------------------------------------
     @torch.no_grad()
     def exchange(self):
         if self.overlap:
             return self.finish()
-        self._adopt_grads()
+        for i, p in enumerate(self.params):
+            self._cur_ptr[i] = None
+            self._note_grad(i, p)
         for b in self.buckets:
-            b.plan.send(self.step)
+            self._send(b)
         for b in self.buckets:
             b.plan.recv(self.step)
+        self._repoint()
         self.step += 1
 
     # ---- hook-driven mode ----------------------------------------------------------------------------------
@@ -314,17 +369,13 @@ class FusedEngine:
 
     def _make_hook(self, i: int):
         def hook(param):
-            bi = self._param_bucket[i]
-            b = self.buckets[bi]
-            if param.grad is not None and param.grad.data_ptr() != self.grad_views[i].data_ptr():
-                shaped = self._shaped(i)
-                shaped.copy_(param.grad)
-                param.grad = shaped
+            b = self.buckets[self._param_bucket[i]]
+            self._note_grad(i, param)
             b.pending -= 1
             if b.pending == 0 and not b.launched:
                 b.launched = True
                 self.comm_stream.wait_stream(torch.cuda.current_stream())
-                b.plan.send(self.step, self.comm_stream)
+                self._send(b, self.comm_stream)
         return hook
 
     @torch.no_grad()
@@ -336,10 +387,14 @@ class FusedEngine:
         self.comm_stream.wait_stream(cur)
         for b in self.buckets:
             if not b.launched:
-                b.plan.send(self.step, self.comm_stream)
+                for i in b.idxs:                 # gradients that arrived without completing the bucket
+                    if self._cur_ptr[i] is None:
+                        self._note_grad(i, self.params[i])
+                self._send(b, self.comm_stream)
         for b in self.buckets:
             b.plan.recv(self.step, self.comm_stream)
         cur.wait_stream(self.comm_stream)
+        self._repoint()
         self.step += 1
         self._reset_pending()
 
@@ -460,7 +515,10 @@ class DenseEngine:
 
     _shaped = FusedEngine._shaped
     _adopt_grads = FusedEngine._adopt_grads
-    zero_grad = FusedEngine.zero_grad
+
+    def zero_grad(self):
+        for arena in self._grad_arena.values():
+            arena.zero_()
 
     def _launch(self, b, stream=None):
         if self.world == 1:

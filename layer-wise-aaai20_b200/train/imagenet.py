@@ -71,13 +71,17 @@ def accuracy(output, target, topk=(1,)):
 class InputNormalizer(nn.Module):
     """uint8 NCHW batch -> normalised compute dtype (reference dataloader.py:88-93)."""
 
-    def __init__(self, dtype=torch.float32, channels_last=True):
+    def __init__(self, dtype=torch.float32, channels_last=True, s2d=False):
         super().__init__()
-        self.dtype, self.channels_last = dtype, channels_last
+        self.dtype, self.channels_last, self.s2d = dtype, channels_last, s2d
         self.register_buffer("mean", torch.tensor(IMAGENET_MEAN).view(1, 3, 1, 1), persistent=False)
         self.register_buffer("std", torch.tensor(IMAGENET_STD).view(1, 3, 1, 1), persistent=False)
 
     def forward(self, x):
+        if self.s2d and x.is_cuda and x.shape[2] % 2 == 0 and x.shape[3] % 2 == 0:
+            # one fused kernel: normalise + channels-last + 2x2 space-to-depth for the ResNet stem
+            from ..ops.input import normalize_u8
+            return normalize_u8(x.contiguous(), self.dtype, s2d=True, keep_plain=self.training)
         x = x.float().sub_(self.mean).div_(self.std).to(self.dtype)
         return x.contiguous(memory_format=torch.channels_last) if self.channels_last else x
 
@@ -102,7 +106,9 @@ class Trainer:
         if self.dtype != torch.float32:
             net = mixed.bn_to_float(net.to(self.dtype))
         self.net = net
-        self.normalize = InputNormalizer(self.dtype, channels_last and self.device.type == "cuda").to(self.device)
+        on_gpu = self.device.type == "cuda"
+        s2d = on_gpu and channels_last and isinstance(net, resnet_zoo.ResNet)
+        self.normalize = InputNormalizer(self.dtype, channels_last and on_gpu, s2d=s2d).to(self.device)
         self.criterion = lnn.CrossEntropyLoss().to(self.device)
         self.cfg = cfg or CompressionConfig()
         self.model_params = [p for p in net.parameters() if p.requires_grad]
@@ -149,6 +155,7 @@ class Trainer:
     def train_step(self, images: torch.Tensor, target: torch.Tensor):
         """``images``: uint8 NCHW (host pinned or device) or already-normalised float; returns (logits, loss)."""
         self.net.train()
+        self.normalize.train()
         if images.device != self.device:
             images = images.to(self.device, non_blocking=True)
             target = target.to(self.device, non_blocking=True)
@@ -181,6 +188,7 @@ class Trainer:
     @torch.no_grad()
     def predict(self, images, target):
         self.net.eval()
+        self.normalize.eval()
         if images.device != self.device:
             images = images.to(self.device, non_blocking=True)
             target = target.to(self.device, non_blocking=True)

@@ -62,3 +62,19 @@ def test_dot_export_and_remove_by_type():
 def test_unknown_network_raises():
     with pytest.raises(ValueError):
         models.build_cifar_model("lenet")
+
+
+def test_space_to_depth_stem_is_the_same_convolution():
+    import torch.nn.functional as F
+    from layerwise_b200.ops.input import normalize_u8, s2d_stem_weight, space_to_depth_reference
+    torch.manual_seed(0)
+    x = torch.randint(0, 256, (2, 3, 32, 48), dtype=torch.uint8)
+    w7 = torch.randn(8, 3, 7, 7)
+    ref = F.conv2d(normalize_u8(x, torch.float32), w7, stride=2, padding=3)
+    xs = normalize_u8(x, torch.float32, s2d=True)
+    assert xs.shape == (2, 16, 19, 27)
+    got = F.conv2d(xs, s2d_stem_weight(w7))
+    assert got.shape == ref.shape and torch.allclose(got, ref, atol=1e-3)
+    m = models.resnet18(num_classes=4).eval()
+    xn = normalize_u8(x, torch.float32)
+    assert torch.allclose(m(xn), m(space_to_depth_reference(xn)), atol=1e-3)
