@@ -15,7 +15,7 @@ def _ref(a, b, a_mn, b_mn):
 
 @pytest.mark.parametrize("a_mn,b_mn", [(False, False), (False, True), (True, True), (True, False)])
 @pytest.mark.parametrize("M,N,K", [(128, 64, 64), (256, 128, 256), (304, 200, 136), (1000, 10 * 8, 512),
-                                   (4096, 256, 1024), (64, 64, 8192)])
+                                   (4096, 256, 1024), (64, 64, 8192), (512, 512, 256), (712, 520, 192), (1024, 2048, 64)])
 def test_gemm_matches_fp32(a_mn, b_mn, M, N, K):
     from layerwise_b200.ops.gemm import gemm
     torch.manual_seed(0)
