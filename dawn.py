@@ -47,6 +47,7 @@ def get_parser():
     p.add_argument("--max_batches", type=int, default=None)
     p.add_argument("--dtype", type=str, default="fp32", choices=["fp32", "bf16", "fp16"])
     p.add_argument("--host_loader", action="store_true", help="DataLoader pipeline instead of device-resident data")
+    p.add_argument("--nchw", action="store_true", help="keep NCHW activations (default on CUDA: channels_last, which the fused kernels need)")
     return p
 
 
@@ -65,6 +66,9 @@ def main(argv=None):
     bs = args.batch_size
 
     model = build_cifar_model(args.network).to(device)
+    channels_last = use_cuda and not args.nchw
+    if channels_last:
+        model = model.to(memory_format=torch.channels_last)
     dtype = {"fp32": torch.float32, "bf16": torch.bfloat16, "fp16": torch.float16}[args.dtype]
     if dtype != torch.float32:
         from layerwise_b200.utils.mixed import bn_to_float
@@ -72,7 +76,8 @@ def main(argv=None):
 
     timer = Timer(synch=torch.cuda.synchronize if use_cuda else None)
     train_batches, test_batches = cifar_batches(dataset, bs, device=device,
-                                                on_device=not args.host_loader, dtype=dtype)
+                                                on_device=not args.host_loader, dtype=dtype,
+                                                channels_last=channels_last)
     lr = lambda step: lr_schedule(step / len(train_batches)) / bs  # noqa: E731
     if args.momentum > 0:
         opt = SGD(trainable_params(model), lr=lr, momentum=args.momentum, weight_decay=5e-4 * bs,

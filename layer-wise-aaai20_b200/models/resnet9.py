@@ -28,11 +28,18 @@ def batch_norm(num_channels, bn_bias_init=None, bn_bias_freeze=False, bn_weight_
     return m
 
 
-def conv_bn(c_in, c_out, bn_weight_init=1.0, stride=1, **kw):
+def conv_bn(c_in, c_out, bn_weight_init=1.0, stride=1, fuse=True, **kw):
+    """conv3x3 -> BN -> ReLU.  With ``fuse`` the ReLU runs inside the batch-norm kernel: the ``relu`` node stays in
+    the graph (same node names / state_dict keys as the reference) but is a no-op, and the ``bn`` entry of the
+    activation cache then holds the post-ReLU tensor."""
+    bn = batch_norm(c_out, bn_weight_init=bn_weight_init, **kw)
+    relu = lnn.ReLU(True)
+    bn.fuse_relu = bool(fuse)
+    relu.already_applied = bool(fuse)
     return {
         "conv": lnn.Conv2d(c_in, c_out, kernel_size=3, stride=stride, padding=1, bias=False),
-        "bn": batch_norm(c_out, bn_weight_init=bn_weight_init, **kw),
-        "relu": lnn.ReLU(True),
+        "bn": bn,
+        "relu": relu,
     }
 
 

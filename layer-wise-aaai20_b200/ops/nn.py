@@ -64,6 +64,7 @@ class BatchNorm2d(nn.BatchNorm2d):
     """
 
     def forward(self, x, residual=None, relu=False):
+        relu = relu or getattr(self, "fuse_relu", False)      # graph nets mark conv-bn-relu triples
         if _native_ok(x):
             from . import bn as _bn
             y = _bn.maybe_batch_norm(self, x, residual, relu)
@@ -76,7 +77,13 @@ class BatchNorm2d(nn.BatchNorm2d):
 
 
 class ReLU(nn.ReLU):
-    pass
+    """``nn.ReLU``; ``already_applied=True`` marks a node whose producer (a fused batch norm) has applied the
+    activation already, so the node is kept for graph/name compatibility but does no work."""
+
+    def forward(self, x):
+        if getattr(self, "already_applied", False):
+            return x
+        return super().forward(x)
 
 
 class MaxPool2d(nn.MaxPool2d):
