@@ -175,6 +175,56 @@ int lwc_sgd_plan_create(LwcSgdPlan** out, const LwcSgdTensor* tensors_host, int3
 int lwc_sgd_plan_destroy(LwcSgdPlan* plan);
 int lwc_sgd_step(LwcSgdPlan* plan, const LwcSgdDesc* desc, void* stream);
 
+/* Re-point the input gradients of a plan (autograd's freshly written tensors are consumed in place; outputs
+ * stay in the arena).  Stream-ordered table upload.  (no accumulate pass: cf. core.py:177 `layer.grad.data`) */
+int lwc_plan_update_grads(LwcPlan* plan, const void* const* grad_dev, void* stream);
+/* Upper bound (ms, default 10000) of every in-kernel wait on a peer flag; expiry is counted in
+ * lwc_plan_stats()[2] and the kernel proceeds -- a dead peer cannot hang a GPU. */
+int lwc_set_flag_timeout_ms(unsigned int ms);
+
+/* ------------------------------------------------------------------------------------------
+ * bf16 GEMM on tcgen05 / TMEM / TMA: C[M,N] (+)= A * B^T (+bias)(ReLU).  a_mn / b_mn select MN-major
+ * operands (A stored [K][M], B stored [K][N]) so forward, dgrad and wgrad of a linear / 1x1-conv layer
+ * need no transposes.  M,N >= 256 run on CTA pairs (cta_group::2, 256x256 tiles).
+ * (nn.Linear / 1x1 nn.Conv2d: CIFAR10/alexnet.py:31-36, CIFAR10/vgg16.py:24-30, IMAGENET/training/resnet.py:110)
+ * ---------------------------------------------------------------------------------------- */
+size_t lwc_gemm_workspace_bytes(int M, int N, int splits);
+int lwc_gemm_pick_splits(int M, int N, int K);
+int lwc_gemm_bf16(const void* A, const void* B, void* C, int M, int N, int K, int lda, int ldb, int ldc,
+                  int a_mn, int b_mn, int out_dtype, const float* bias, int relu, int accumulate,
+                  int splits, float* ws, void* stream);
+
+/* ------------------------------------------------------------------------------------------
+ * Fused batch-norm (+ residual) (+ ReLU) on channels-last activations [M = N*H*W, C], C % 8 == 0.
+ * (nn.BatchNorm2d + nn.ReLU + `out += residual`: CIFAR10/dawn.py:23-28, IMAGENET/training/resnet.py:40-95)
+ * ---------------------------------------------------------------------------------------- */
+size_t lwc_bn_workspace_bytes(long long M, int C);
+int lwc_bn_forward(const void* x, void* y, const void* res, const float* gamma, const float* beta,
+                   float* mean, float* invstd, float* running_mean, float* running_var, float* workspace,
+                   long long M, int C, int dtype, int training, int relu, float eps, float momentum, void* stream);
+int lwc_bn_backward(const void* dy, const void* x, const void* y, void* dx, void* dres, const float* gamma,
+                    const float* beta, const float* mean, const float* invstd, float* dgamma, float* dbeta,
+                    float* workspace, long long M, int C, int dtype, int relu, void* stream);
+
+/* Max pooling, NHWC, byte argmax forward + gather backward (CIFAR10/dawn.py:51,:70; resnet.py:104). */
+int lwc_maxpool_forward(const void* x, void* y, void* idx, int N, int H, int W, int C, int k, int stride,
+                        int pad, int dtype, void* stream);
+int lwc_maxpool_backward(const void* dy, const void* idx, void* dx, int N, int H, int W, int C, int k,
+                         int stride, int pad, int dtype, void* stream);
+
+/* uint8 NCHW -> normalised channels-last (mode 0) or 2x2 space-to-depth with zero border (mode 1)
+ * (IMAGENET/training/dataloader.py:88-93). */
+int lwc_normalize_u8(const void* x_u8_nchw, void* y, int N, int H, int W, int c_out, int mode,
+                     const float* mean3, const float* std3, int dtype, void* stream);
+
+/* Cross entropy: per-sample loss + log-sum-exp; backward = (softmax - onehot) * gscale * g[n]
+ * (CIFAR10/dawn.py:85; IMAGENET/training/train_imagenet_nv.py:187). */
+int lwc_cross_entropy_forward(const void* logits, const void* target_i64, float* loss, float* lse, int N, int C,
+                              int dtype, void* stream);
+int lwc_cross_entropy_backward(const void* logits, const void* target_i64, const float* lse,
+                               const float* grad_per_sample, void* dlogits, int N, int C, int dtype,
+                               float gscale, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -62,6 +62,7 @@ def declare(lib: C.CDLL):
     sig("lwc_ipc_close_handle", C.c_int, vp)
     sig("lwc_enable_peer_access", C.c_int, C.c_int)
     sig("lwc_error_string", C.c_char_p, C.c_int)
+    sig("lwc_set_flag_timeout_ms", C.c_int, C.c_uint)
     sig("lwc_plan_create", C.c_int, c_void_pp, C.POINTER(LwcPlanDesc))
     sig("lwc_plan_destroy", C.c_int, vp)
     sig("lwc_plan_slot_bytes", sz, vp)
@@ -90,6 +91,8 @@ def declare(lib: C.CDLL):
     sig("lwc_maxpool_backward", C.c_int, vp, vp, vp, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int,
         C.c_int, vp)
     sig("lwc_normalize_u8", C.c_int, vp, vp, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, vp, vp, C.c_int, vp)
+    sig("lwc_cross_entropy_forward", C.c_int, vp, vp, vp, vp, C.c_int, C.c_int, C.c_int, vp)
+    sig("lwc_cross_entropy_backward", C.c_int, vp, vp, vp, vp, vp, C.c_int, C.c_int, C.c_int, C.c_float, vp)
     sig("lwc_sgd_plan_create", C.c_int, c_void_pp, C.POINTER(LwcSgdTensor), i32)
     sig("lwc_sgd_plan_destroy", C.c_int, vp)
     sig("lwc_sgd_step", C.c_int, vp, C.POINTER(LwcSgdDesc), vp)

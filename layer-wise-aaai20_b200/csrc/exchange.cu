@@ -107,6 +107,7 @@ struct DevPlan {     // passed by value to kernels
     float threshold;
     unsigned long long seed;
     unsigned long long step;
+    unsigned long long timeout_ns;   // bounded wait on peer flags
     // slot geometry
     unsigned long long slot_bytes;
     unsigned long long hdr_bytes;
@@ -595,7 +596,7 @@ __device__ __forceinline__ void wait_sources(const DevPlan& p) {
         const uint64_t t0 = global_timer_ns();
         unsigned spins = 0;
         while (ld_acquire_sys(f) < want) {
-            if ((++spins & 1023u) == 0 && global_timer_ns() - t0 > 10000000000ULL) {   // 10 s
+            if ((++spins & 63u) == 0 && global_timer_ns() - t0 > p.timeout_ns) {
                 atomicAdd(&p.counters->timeouts, 1ULL);
                 break;
             }
@@ -815,6 +816,14 @@ __global__ void __launch_bounds__(kThreads) k_recv_dense(DevPlan p) {
 // =====================================================================================================
 using namespace lwc;
 
+// Upper bound of every wait on a peer's flag (default 10 s).  A rank whose peer died or hung leaves its kernels
+// after this long, counts the event (stats()[2]) and lets the host decide -- it never spins forever.
+static unsigned long long g_flag_timeout_ns = 10000000000ULL;
+extern "C" int lwc_set_flag_timeout_ms(unsigned int ms) {
+    g_flag_timeout_ns = (unsigned long long)(ms ? ms : 1) * 1000000ULL;
+    return 0;
+}
+
 struct LwcPlan {
     DevPlan dev;
     int num_tensors;
@@ -987,6 +996,7 @@ extern "C" int lwc_plan_send(LwcPlan* P, uint64_t step, void* stream_) {
     cudaStream_t st = (cudaStream_t)stream_;
     DevPlan D = P->dev;
     D.step = step;
+    D.timeout_ns = g_flag_timeout_ns;
     const int NC = D.num_chunks, G = D.num_groups, m = D.method;
     LWC_CUDA_CHECK(cudaMemsetAsync(P->d_gstate, 0, P->state_bytes, st));
     switch (m) {
@@ -1043,6 +1053,7 @@ extern "C" int lwc_plan_recv(LwcPlan* P, uint64_t step, void* stream_) {
     cudaStream_t st = (cudaStream_t)stream_;
     DevPlan D = P->dev;
     D.step = step;
+    D.timeout_ns = g_flag_timeout_ns;
     const int m = D.method;
     if (m >= LWC_TOPK && m <= LWC_ADAPTIVE) {
         switch (P->out_dtype) {
@@ -1236,6 +1247,7 @@ struct DevAR {
     long long off, n;                   // element range [off, off + n) of the arena
     int world, rank;
     unsigned long long step;
+    unsigned long long timeout_ns;
 };
 
 __device__ __forceinline__ void ar_wait(const DevAR& p, int row) {
@@ -1245,7 +1257,7 @@ __device__ __forceinline__ void ar_wait(const DevAR& p, int row) {
         const uint64_t t0 = global_timer_ns();
         unsigned spins = 0;
         while (ld_acquire_sys(f) < want) {
-            if ((++spins & 1023u) == 0 && global_timer_ns() - t0 > 10000000000ULL) {
+            if ((++spins & 63u) == 0 && global_timer_ns() - t0 > p.timeout_ns) {
                 atomicAdd(p.counters + 1, 1ULL);
                 break;
             }
@@ -1322,7 +1334,7 @@ extern "C" int lwc_dense_allreduce(void* const* arena_dev, void* const* flags_de
         p.flags[r] = (uint64_t*)flags_dev[r];
     }
     p.counters = (unsigned long long*)counters_dev;
-    p.off = off; p.n = n; p.world = world; p.rank = rank; p.step = step;
+    p.off = off; p.n = n; p.world = world; p.rank = rank; p.step = step; p.timeout_ns = g_flag_timeout_ns;
     cudaStream_t st = (cudaStream_t)stream;
     const long long nvec = ((long long)n * (long long)esz + 15) / 16;
     const long long per = (nvec + world - 1) / world;

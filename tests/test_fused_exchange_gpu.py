@@ -221,3 +221,19 @@ def test_standalone_topk_select():
     ref = x.abs().topk(keep).indices.sort().values
     assert torch.equal(idx[:k].long(), ref)
     assert torch.equal(val[:k], x[ref])
+
+
+def test_missing_peer_times_out_instead_of_hanging():
+    """A receiver whose peer never sends must leave its kernel after the configured timeout and count it."""
+    from layerwise_b200 import _native
+    lib = _native.lib()
+    cfg = CompressionConfig(compress="layerwise", method="Topk", ratio=0.1)
+    grads, outs, _, plans, lw = _world(2, [4096], cfg, False)
+    lib.lwc_set_flag_timeout_ms(50)
+    try:
+        plans[0].send(0)
+        plans[0].recv(0)            # rank 1 never sent step 0
+        torch.cuda.synchronize()
+        assert plans[0].stats()["timeouts"] >= 1
+    finally:
+        lib.lwc_set_flag_timeout_ms(10000)
