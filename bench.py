@@ -273,8 +273,10 @@ def main():
                "ms_per_step": ms2 / args.steps}
 
     extra = {}
-    if args.impl == "ours" and args.phase_times:
-        extra["exchange"] = tr.exchanger.engine.stats() if hasattr(tr.exchanger.engine, "stats") else None
+    if args.impl == "ours" and hasattr(tr.exchanger.engine, "benchmark_exchange"):
+        # compress + exchange + decompress alone (no backward to overlap with), device-timed, max over ranks
+        extra["compress_comm_ms_per_step"] = max_over_ranks(tr.exchanger.engine.benchmark_exchange(10))
+        extra["exchange_stats"] = tr.exchanger.engine.stats()
     if rank == 0:
         out = {
             "metric": "ResNet-50 img/s, layerwise Top-k 1% (train step incl. compress+exchange+SGD)",

@@ -126,7 +126,7 @@ def batch_norm_act(x, weight, bias, running_mean, running_var, residual=None, tr
 
 def maybe_batch_norm(module, x, residual=None, relu=False):
     """Module dispatch; returns ``None`` when the stock implementation must run."""
-    if module.momentum is None or (module.training and not module.track_running_stats and False):
+    if module.momentum is None:          # cumulative moving average: stock implementation
         return None
     if not supported(x, module.weight, module.bias, residual):
         return None

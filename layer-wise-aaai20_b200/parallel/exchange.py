@@ -226,7 +226,8 @@ class GradientExchanger:
             raise RuntimeError("fused engine needs CUDA parameters")
         if use_fused:
             from .fused import DenseEngine, FusedEngine
-            if cfg.method_name == cref.NONE and engine_kw.pop("dense", "two_shot") == "two_shot":
+            dense = engine_kw.pop("dense", "two_shot")     # "two_shot" (peer all-reduce) | "slots" (one-shot)
+            if cfg.method_name == cref.NONE and dense == "two_shot":
                 self.engine = DenseEngine(self.params, cfg, group=group, overlap=overlap, **engine_kw)
             else:
                 self.engine = FusedEngine(self.params, cfg, group=group, overlap=overlap, **engine_kw)

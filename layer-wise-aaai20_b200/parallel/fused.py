@@ -398,6 +398,33 @@ class FusedEngine:
         self.step += 1
         self._reset_pending()
 
+    @torch.no_grad()
+    def benchmark_exchange(self, iters: int = 10) -> float:
+        """Device time (ms) of one full compress -> exchange -> decompress of this engine's buckets, run back
+        to back on the current stream over the arena contents (no backward to hide behind).  Advances the step
+        counter and the error-feedback state like real exchanges do."""
+        for b in self.buckets:
+            ptrs = [self._arena_ptr[i] for i in b.idxs]
+            if ptrs != b.ptrs:
+                b.plan.update_grads(ptrs)
+                b.ptrs = ptrs
+
+        def once():
+            for b in self.buckets:
+                b.plan.send(self.step)
+            for b in self.buckets:
+                b.plan.recv(self.step)
+            self.step += 1
+        for _ in range(2):
+            once()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(iters):
+            once()
+        e1.record()
+        torch.cuda.synchronize()
+        return e0.elapsed_time(e1) / iters
+
     # ---- state -------------------------------------------------------------------------------------------------
     def state_dict(self):
         res = None if self.resid_views is None else [r.detach().cpu().clone() for r in self.resid_views]
@@ -578,8 +605,6 @@ class DenseEngine:
 
     def stats(self):
         timeouts = 0
-        for b in self.buckets:
-            base, total, esz, _ = self._layout[b["dtype"]]
         torch.cuda.synchronize()
         aux = self.heap.local.view(torch.int64, (self.AUX * len(self.buckets)) // 8,
                                    self.heap.nbytes - self.AUX * len(self.buckets))

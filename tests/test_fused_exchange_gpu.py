@@ -237,3 +237,38 @@ def test_missing_peer_times_out_instead_of_hanging():
         assert plans[0].stats()["timeouts"] >= 1
     finally:
         lib.lwc_set_flag_timeout_ms(10000)
+
+
+def _tiny_net():
+    torch.manual_seed(0)
+    # GEMM-only network: its backward is bitwise reproducible run to run (cuDNN wgrad kernels are not), so the
+    # three exchange modes can be compared exactly
+    net = torch.nn.Sequential(torch.nn.Flatten(), torch.nn.Linear(3 * 16 * 16, 256), torch.nn.ReLU(),
+                              torch.nn.Linear(256, 64), torch.nn.ReLU(), torch.nn.Linear(64, 10)).cuda()
+    return net
+
+
+@pytest.mark.parametrize("method,kw", [("Topk", dict(ratio=0.05)), ("none", {})])
+def test_hook_overlap_and_grad_steal_match_plain_exchange(method, kw):
+    """Hook-driven (side stream, stolen gradient tensors) and after-backward exchanges give identical averages."""
+    from layerwise_b200.parallel.exchange import GradientExchanger
+    x = torch.randn(8, 3, 16, 16, device="cuda")
+    y = torch.randint(0, 10, (8,), device="cuda")
+    results = []
+    for overlap, steal in ((False, False), (True, True), (False, True)):
+        net = _tiny_net()
+        cfg = CompressionConfig(compress="layerwise" if method != "none" else "none", method=method, error_feedback=True, **kw)
+        ex = GradientExchanger(net, cfg, engine="fused", overlap=overlap, steal=steal, dense="slots")
+        outs = []
+        for _ in range(3):
+            if hasattr(ex.engine, "zero_grad"):
+                ex.engine.zero_grad()
+            torch.nn.functional.cross_entropy(net(x), y).backward()
+            ex.exchange()
+            outs.append([p.grad.detach().clone() for p in net.parameters()])
+        results.append(outs)
+        ex.engine.close()
+    for other in results[1:]:
+        for sa, sb in zip(results[0], other):
+            for a, b in zip(sa, sb):
+                assert torch.equal(a, b)
