@@ -1,6 +1,133 @@
-"""Convolution dispatch (native implicit-GEMM kernels where available)."""
+"""Convolution front end for the persistent tcgen05 implicit-GEMM kernel (``csrc/conv.cu``).
+
+Covers stride-1 "same" convolutions with 1x1 and 3x3 kernels on channels-last bf16 activations whose channel
+counts are multiples of 64: forward (optionally emitting batch-norm statistics partials from the epilogue) and the
+data gradient (a convolution with the spatially flipped, channel-transposed kernel).  Weight gradients of 1x1
+layers go through the split-K MN-major GEMM (``ops/gemm.py``); everything else falls back to the stock op.
+
+Reference ops: ``nn.Conv2d`` forward / backward through cuDNN (IMAGENET/training/resnet.py:21-24,:55-69,
+CIFAR10/dawn.py:23-35).
+"""
+from __future__ import annotations
+
+import ctypes as C
+from typing import Optional, Tuple
+
+import torch
+
+from .. import _native
+from .._native import abi
+
+
+def _nhwc(x: torch.Tensor) -> bool:
+    return x.dim() == 4 and x.is_contiguous(memory_format=torch.channels_last)
+
+
+def supported(x: torch.Tensor, weight: torch.Tensor, stride, padding, dilation, groups) -> bool:
+    if not (x.is_cuda and x.dtype == torch.bfloat16 and weight.dtype == torch.bfloat16 and _nhwc(x)):
+        return False
+    co, ci, kh, kw = weight.shape
+    if kh != kw or kh not in (1, 3) or tuple(stride) != (1, 1) or tuple(dilation) != (1, 1) or groups != 1:
+        return False
+    if tuple(padding) != (kh // 2, kh // 2) or ci % 64 or co % 64:
+        return False
+    return weight.is_contiguous(memory_format=torch.channels_last) or kh == 1
+
+
+def tiles_m(n: int, h: int, w: int, kh: int) -> Tuple[int, int]:
+    rows = C.c_int(0)
+    t = int(_native.lib().lwc_conv_tiles_m(n, h, w, kh, C.byref(rows)))
+    return t, int(rows.value)
+
+
+def conv_forward(x: torch.Tensor, weight: torch.Tensor, bias: Optional[torch.Tensor] = None, relu: bool = False,
+                 want_stats: bool = False, b_mn: bool = False, out_channels: Optional[int] = None):
+    """``y = conv(x, weight)``; returns ``(y, stats)`` with ``stats`` = ``[tiles_m, 2, Cout]`` fp32 or ``None``.
+
+    ``weight`` is the channels-last forward weight ``[Cout, Cin, k, k]`` (memory order Cout, k, k, Cin).  With
+    ``b_mn`` (1x1 only) ``weight`` is used as stored ``[K][N]``, which turns the call into the data-gradient GEMM.
+    """
+    lib = _native.lib()
+    n, ci, h, w = x.shape
+    kh = weight.shape[2]
+    co = out_channels if out_channels is not None else weight.shape[0]
+    y = torch.empty((n, co, h, w), dtype=x.dtype, device=x.device, memory_format=torch.channels_last)
+    stats = None
+    if want_stats:
+        tm, _ = tiles_m(n, h, w, kh)
+        stats = torch.empty((tm, 2, co), dtype=torch.float32, device=x.device)
+    if bias is not None:
+        bias = bias.float().contiguous()
+    st = torch.cuda.current_stream().cuda_stream
+    rc = lib.lwc_conv_forward(x.data_ptr(), weight.data_ptr(), y.data_ptr(), n, h, w, ci, co, kh, int(b_mn),
+                              0 if bias is None else bias.data_ptr(), int(relu), 0 if stats is None else stats.data_ptr(),
+                              C.c_void_p(st))
+    abi.check(rc, "lwc_conv_forward")
+    _native.counters.add(1)
+    return y, stats
+
+
+def flipped_transposed(weight: torch.Tensor) -> torch.Tensor:
+    """Kernel of the data-gradient convolution: ``Wd[ci, co, a, b] = W[co, ci, k-1-a, k-1-b]`` (channels-last)."""
+    return weight.flip(2, 3).transpose(0, 1).contiguous(memory_format=torch.channels_last)
+
+
+class _ConvFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x, weight, bias, want_stats):
+        y, stats = conv_forward(x, weight, bias, want_stats=want_stats)
+        ctx.save_for_backward(x, weight)
+        ctx.has_bias = bias is not None
+        ctx.mark_non_differentiable(*([stats] if stats is not None else []))
+        return (y, stats) if stats is not None else (y, None)
+
+    @staticmethod
+    def backward(ctx, dy, _dstats=None):
+        x, weight = ctx.saved_tensors
+        if not _nhwc(dy):
+            dy = dy.contiguous(memory_format=torch.channels_last)
+        kh = weight.shape[2]
+        dx = dw = db = None
+        if ctx.needs_input_grad[0]:
+            if kh == 1:        # dX = dY * W with W used as stored [Cout][Cin] (MN-major B): no transpose pass
+                dx, _ = conv_forward(dy, weight, b_mn=True, out_channels=weight.shape[1])
+            else:
+                dx, _ = conv_forward(dy, flipped_transposed(weight))
+        if ctx.needs_input_grad[1]:
+            if kh == 1:
+                from .gemm import gemm
+                n, co, h, w = dy.shape
+                dy2 = dy.permute(0, 2, 3, 1).reshape(-1, co)
+                x2 = x.permute(0, 2, 3, 1).reshape(-1, x.shape[1])
+                dw = gemm(dy2, x2, a_mn=True, b_mn=True).view(co, x.shape[1], 1, 1).contiguous(memory_format=torch.channels_last)
+            else:
+                dw = torch.ops.aten.convolution_backward(dy, x, weight, None, [1, 1], [1, 1], [1, 1], False, [0, 0], 1,
+                                                         [False, True, False])[1]
+        if ctx.has_bias and ctx.needs_input_grad[2]:
+            db = dy.float().sum((0, 2, 3)).to(dy.dtype)
+        return dx, dw, db, None
+
+
+def conv2d(x, weight, bias=None, want_stats: bool = False):
+    """Autograd-aware native convolution; returns ``(y, stats_or_None)``."""
+    return _ConvFn.apply(x, weight, bias, want_stats)
+
+
+_ENABLED = {"on": False}
+
+
+def enable(flag: bool = True):
+    """Route eligible ``ops.nn.Conv2d`` layers through the native kernel (off by default: see DESIGN.md)."""
+    _ENABLED["on"] = bool(flag)
 
 
 def maybe_conv2d(module, x):
-    """Return the native result, or ``None`` to fall back to the stock op."""
-    return None
+    """Module dispatch; returns ``None`` when the stock implementation must run."""
+    if not _ENABLED["on"]:
+        return None
+    if not supported(x, module.weight, module.stride, module.padding, module.dilation, module.groups):
+        return None
+    y, stats = conv2d(x, module.weight, module.bias, want_stats=getattr(module, "emit_bn_stats", False))
+    if stats is not None:
+        y.bn_stats = stats
+    return y
