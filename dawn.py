@@ -57,6 +57,7 @@ def main(argv=None):
     world = args.world_size if args.world_size is not None else comm.env_world_size()
     use_cuda = torch.cuda.is_available()
     if use_cuda:
+        torch.backends.cudnn.benchmark = True         # reference: CIFAR10/torch_backend.py:7
         torch.cuda.set_device(comm.env_local_rank() % torch.cuda.device_count())
     device = torch.device("cuda", torch.cuda.current_device()) if use_cuda else torch.device("cpu")
 

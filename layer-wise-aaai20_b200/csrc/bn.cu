@@ -228,7 +228,7 @@ __device__ __forceinline__ double warp_sum_d(double v) {
     return v;
 }
 
-constexpr int MAX_PART_PER_LANE = 10;     // plan_grid keeps nblk <= 32 * 10
+constexpr int MAX_PART_PER_LANE = 20;     // plan_grid keeps nblk <= 32 * 20
 
 // All partials of a channel are fetched up front (<= 20 independent loads per lane), so the kernel pays
 // the memory latency once instead of once per loop iteration.
@@ -476,17 +476,17 @@ __global__ void __launch_bounds__(THREADS) k_bn_bwd_apply(Params p) {
 
 using namespace lwc::bn;
 
-static void plan_grid(long long M, int C, int* nblk, int* rows_per_blk, dim3* grid) {
+static void plan_grid(long long M, int C, int* nblk, int* rows_per_blk, dim3* grid, int ctas_per_sm = 2) {
     const int ncg = C / VEC;
     const int tpr = ncg < THREADS ? ncg : THREADS;
     const int rpp = THREADS / tpr;
     const int gy = (ncg + tpr - 1) / tpr;
     // 2 CTAs per SM (16 warps x 8-12 outstanding 16-byte loads each), at least 16 passes of rows per CTA
-    long long target = (148LL * 2 + gy - 1) / gy;
+    long long target = (148LL * ctas_per_sm + gy - 1) / gy;
     long long rows = (M + target - 1) / target;
     const long long min_rows = 16LL * rpp;
     if (rows < min_rows) rows = min_rows;
-    const long long max_blk = 32LL * 10;                 // k_bn_finalize holds <= 10 partials per lane
+    const long long max_blk = 32LL * 20;                 // k_bn_finalize holds <= 20 partials per lane
     if ((M + rows - 1) / rows > max_blk) rows = (M + max_blk - 1) / max_blk;
     rows = (rows + rpp - 1) / rpp * rpp;
     *rows_per_blk = (int)rows;
@@ -497,7 +497,7 @@ static void plan_grid(long long M, int C, int* nblk, int* rows_per_blk, dim3* gr
 extern "C" size_t lwc_bn_workspace_bytes(long long M, int C) {
     int nblk, rows;
     dim3 g;
-    plan_grid(M, C, &nblk, &rows, &g);
+    plan_grid(M, C, &nblk, &rows, &g, 4);       // the largest partial count any pass uses
     return (size_t)nblk * 2 * C * sizeof(float);
 }
 
@@ -525,11 +525,13 @@ extern "C" int lwc_bn_forward(const void* x, void* y, const void* res, const flo
     p.running_mean = running_mean; p.running_var = running_var; p.partial = workspace;
     p.M = M; p.C = C; p.relu = relu; p.eps = eps; p.momentum = momentum;
     dim3 grid;
-    plan_grid(M, C, &p.nblk, &p.rows_per_blk, &grid);
     if (training) {
+        // the pure-read statistics pass (50 registers) likes 4 CTAs per SM; the apply pass 2
+        plan_grid(M, C, &p.nblk, &p.rows_per_blk, &grid, 4);
         LWC_BN_DISPATCH(dtype, k_bn_stats<T><<<grid, THREADS, 0, st>>>(p));
         k_bn_finalize<<<(C + 7) / 8, 256, 0, st>>>(p);
     }
+    plan_grid(M, C, &p.nblk, &p.rows_per_blk, &grid, 2);
     LWC_BN_DISPATCH(dtype, k_bn_apply<T><<<grid, THREADS, 0, st>>>(p, training ? 0 : 1));
     return (int)cudaGetLastError();
 }

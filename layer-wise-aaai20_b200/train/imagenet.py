@@ -96,6 +96,8 @@ class Trainer:
                  engine: str = "auto", channels_last: bool = True, model: Optional[nn.Module] = None,
                  wrapper: Optional[str] = None, randk: float = 1.0, seed: int = 2147483647):
         self.device = torch.device(device or ("cuda" if torch.cuda.is_available() else "cpu"))
+        if self.device.type == "cuda":
+            torch.backends.cudnn.benchmark = True     # as the reference does (train_imagenet_nv.py:95): autotune conv algos
         self.dtype = {"fp32": torch.float32, "bf16": torch.bfloat16, "fp16": torch.float16}[dtype]
         self.loss_scale = loss_scale if self.dtype == torch.float16 else 1.0
         torch.manual_seed(seed)          # identical initial replicas (reference :117-118)
