@@ -42,6 +42,7 @@ struct Params {
     int relu;
     const float* bias;
     float* stats;                    // [tiles_m][2][N] per-tile column sums / sums of squares, or NULL
+    const __nv_bfloat16* addend;     // optional [M][N] tensor added in the epilogue (2-D mode): Y = conv(X) + addend
 };
 
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
@@ -150,7 +151,8 @@ __device__ __forceinline__ TileCoord tile_coord(const Params& p, int tile) {
 
 template <int BN, bool B_MN>
 __global__ void __launch_bounds__(THREADS, 1) k_conv(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
-                                                     const __grid_constant__ CUtensorMap tmC, Params p) {
+                                                     const __grid_constant__ CUtensorMap tmC, const __grid_constant__ CUtensorMap tmD,
+                                                     Params p) {
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
     using S = Smem<BN>;
@@ -158,7 +160,8 @@ __global__ void __launch_bounds__(THREADS, 1) k_conv(const __grid_constant__ CUt
     uint64_t* empty = full + STAGES;
     uint64_t* tmem_full = empty + STAGES;      // [2]
     uint64_t* tmem_empty = tmem_full + 2;      // [2]
-    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_empty + 2);
+    uint64_t* add_full = tmem_empty + 2;       // [2] addend tile landed in the staging buffer
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(add_full + 2);
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int num_tiles = p.tiles_m * p.tiles_n;
@@ -171,7 +174,7 @@ __global__ void __launch_bounds__(THREADS, 1) k_conv(const __grid_constant__ CUt
         asm volatile("prefetch.tensormap [%0];" ::"l"(&tmB) : "memory");
         asm volatile("prefetch.tensormap [%0];" ::"l"(&tmC) : "memory");
         for (int s = 0; s < STAGES; ++s) { mbar_init(&full[s], 1); mbar_init(&empty[s], 1); }
-        for (int a = 0; a < 2; ++a) { mbar_init(&tmem_full[a], 1); mbar_init(&tmem_empty[a], 4); }
+        for (int a = 0; a < 2; ++a) { mbar_init(&tmem_full[a], 1); mbar_init(&tmem_empty[a], 4); mbar_init(&add_full[a], 1); }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     if (warp == 1) {
@@ -243,6 +246,17 @@ __global__ void __launch_bounds__(THREADS, 1) k_conv(const __grid_constant__ CUt
         const int q = warp & 3;                        // TMEM lane quarter
         const int r = q * 32 + lane;                   // row inside the tile
         const bool leader = (warp == 2 && lane == 0);
+        const bool has_add = p.addend != nullptr && !p.mode4d;
+        // The addend tile (e.g. the skip connection's gradient) is TMA-prefetched into the staging buffer one tile
+        // ahead; the epilogue adds the accumulator onto it in place and TMA-stores the sum.
+        auto prefetch_addend = [&](int tile_, uint32_t buf) {
+            const TileCoord tt = tile_coord(p, tile_);
+            uint8_t* dst = smem + S::C_OFF + buf * S::C_BYTES;
+            mbar_expect_tx(&add_full[buf], S::C_BYTES);
+#pragma unroll
+            for (int h = 0; h < BN / 64; ++h) tma_load_2d(dst + h * (BM * 128), &tmD, &add_full[buf], tt.nt * BN + h * 64, tt.m0);
+        };
+        if (has_add && leader && (int)blockIdx.x < num_tiles) prefetch_addend(blockIdx.x, 0);
         uint32_t tcount = 0;
         for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++tcount) {
             const TileCoord t = tile_coord(p, tile);
@@ -251,12 +265,30 @@ __global__ void __launch_bounds__(THREADS, 1) k_conv(const __grid_constant__ CUt
             uint8_t* cst = smem + S::C_OFF + (tcount & 1) * S::C_BYTES;
             mbar_wait(&tmem_full[as], aph);
             tcgen05_fence_after();
-            if (leader) asm volatile("cp.async.bulk.wait_group.read 1;" ::: "memory");     // staging buffer free again
-            epi_bar_sync();
+            if (has_add) {
+                mbar_wait(&add_full[tcount & 1], aph);        // this tile's addend is in cst (its prefetch also guarded reuse)
+            } else {
+                if (leader) asm volatile("cp.async.bulk.wait_group.read 1;" ::: "memory");     // staging buffer free again
+                epi_bar_sync();
+            }
 #pragma unroll 1
             for (int c = 0; c < BN; c += 32) {
                 uint32_t v[32];
                 tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16) + as * BN + (uint32_t)c, v);
+                if (has_add) {
+                    const uint8_t* asub = cst + (c / 64) * (BM * 128) + r * 128;
+                    const int achunk0 = (c % 64) / 8;
+#pragma unroll
+                    for (int j = 0; j < 4; ++j) {
+                        const uint4 a4 = *reinterpret_cast<const uint4*>(asub + (((achunk0 + j) ^ (r & 7)) * 16));
+                        const uint32_t aw[4] = {a4.x, a4.y, a4.z, a4.w};
+#pragma unroll
+                        for (int e = 0; e < 4; ++e) {
+                            v[j * 8 + 2 * e] = __float_as_uint(__uint_as_float(v[j * 8 + 2 * e]) + __uint_as_float(aw[e] << 16));
+                            v[j * 8 + 2 * e + 1] = __float_as_uint(__uint_as_float(v[j * 8 + 2 * e + 1]) + __uint_as_float(aw[e] & 0xffff0000u));
+                        }
+                    }
+                }
                 uint8_t* sub = cst + (c / 64) * (BM * 128) + r * 128;     // 128x64 sub-tile, 128-byte rows
                 const int chunk0 = (c % 64) / 8;
 #pragma unroll
@@ -334,6 +366,11 @@ __global__ void __launch_bounds__(THREADS, 1) k_conv(const __grid_constant__ CUt
                     else tma_store_2d(&tmC, cst + h * (BM * 128), co0 + h * 64, t.m0);
                 }
                 asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+                if (has_add && tile + (int)gridDim.x < num_tiles) {
+                    // the other buffer was last read by the store issued one tile ago: wait for it, then refill it
+                    asm volatile("cp.async.bulk.wait_group.read 1;" ::: "memory");
+                    prefetch_addend(tile + gridDim.x, (tcount + 1) & 1);
+                }
             }
         }
         if (leader) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
@@ -372,7 +409,8 @@ static int encode(CUtensorMap* map, const void* ptr, int rank, const cuuint64_t*
 }
 
 template <int BN, bool B_MN>
-static int launch(const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMap& tc, const Params& p, cudaStream_t st) {
+static int launch(const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMap& tc, const CUtensorMap& td, const Params& p,
+                  cudaStream_t st) {
     using S = Smem<BN>;
     static bool attr_set = false;
     if (!attr_set) {
@@ -381,7 +419,7 @@ static int launch(const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMa
     }
     int grid = p.tiles_m * p.tiles_n;
     if (grid > 148) grid = 148;
-    k_conv<BN, B_MN><<<grid, THREADS, S::TOTAL, st>>>(ta, tb, tc, p);
+    k_conv<BN, B_MN><<<grid, THREADS, S::TOTAL, st>>>(ta, tb, tc, td, p);
     return 0;
 }
 
@@ -410,15 +448,30 @@ extern "C" int lwc_conv_tiles_m(int Nimg, int H, int W, int kh, int* rows_per_ti
 //   b_mn = 1 : 1x1 only; Wt is stored [Cin_of_this_pass][Cout_of_this_pass] (i.e. the forward weight [Cout_f][Cin_f]
 //              used un-transposed for the data gradient dX = dY * W)
 // stats (optional): [tiles_m][2][Cout] fp32 per-tile sums / sums of squares of the bf16 outputs.
+static int conv_forward_impl(const void* x, const void* wt, void* y, int Nimg, int H, int W, int Cin, int Cout, int kh,
+                             int b_mn, const float* bias, int relu, float* stats, const void* addend, void* stream);
+
 extern "C" int lwc_conv_forward(const void* x, const void* wt, void* y, int Nimg, int H, int W, int Cin, int Cout, int kh,
                                 int b_mn, const float* bias, int relu, float* stats, void* stream) {
+    return conv_forward_impl(x, wt, y, Nimg, H, W, Cin, Cout, kh, b_mn, bias, relu, stats, nullptr, stream);
+}
+
+// 1x1 only: Y = conv(X) + addend, addend bf16 with the shape of Y (used for dX = dY * W + d_identity at residual forks).
+extern "C" int lwc_conv1x1_add(const void* x, const void* wt, const void* addend, void* y, int Nimg, int H, int W, int Cin,
+                               int Cout, int b_mn, void* stream) {
+    if (!addend) return LWC_EINVAL;
+    return conv_forward_impl(x, wt, y, Nimg, H, W, Cin, Cout, 1, b_mn, nullptr, 0, nullptr, addend, stream);
+}
+
+static int conv_forward_impl(const void* x, const void* wt, void* y, int Nimg, int H, int W, int Cin, int Cout, int kh,
+                             int b_mn, const float* bias, int relu, float* stats, const void* addend, void* stream) {
     if (!x || !wt || !y || Nimg <= 0 || H <= 0 || W <= 0) return LWC_EINVAL;
     if ((Cin % 64) || (Cout % 64) || (kh != 1 && kh != 3) || (b_mn && kh != 1)) return LWC_EINVAL;
     ensure_context();
     cudaStream_t st = (cudaStream_t)stream;
     Params p;
     memset(&p, 0, sizeof(p));
-    p.N = Cout; p.Kc = Cin; p.taps = kh * kh; p.kw = kh; p.pad = kh / 2; p.relu = relu; p.bias = bias; p.stats = stats;
+    p.N = Cout; p.Kc = Cin; p.taps = kh * kh; p.kw = kh; p.pad = kh / 2; p.relu = relu; p.bias = bias; p.stats = stats; p.addend = (const __nv_bfloat16*)addend;
     p.H = H; p.W = W; p.Nimg = Nimg;
     const int BN = (Cout % 128 == 0) ? 128 : 64;
     p.tiles_n = Cout / BN;
@@ -470,8 +523,16 @@ extern "C" int lwc_conv_forward(const void* x, const void* wt, void* y, int Nimg
         rc = encode(&tb, wt, 2, bd, bs, bb);
     }
     if (rc) return rc;
-    if (BN == 128) rc = b_mn ? launch<128, true>(ta, tb, tc, p, st) : launch<128, false>(ta, tb, tc, p, st);
-    else rc = b_mn ? launch<64, true>(ta, tb, tc, p, st) : launch<64, false>(ta, tb, tc, p, st);
+    CUtensorMap td = tc;                 // addend: same geometry as the output, different base pointer
+    if (addend) {
+        if (kh != 1) return LWC_EINVAL;
+        cuuint64_t dd[2] = {(cuuint64_t)Cout, (cuuint64_t)p.M}, ds[1] = {(cuuint64_t)Cout * 2};
+        cuuint32_t db[2] = {64, BM};
+        rc = encode(&td, addend, 2, dd, ds, db);
+        if (rc) return rc;
+    }
+    if (BN == 128) rc = b_mn ? launch<128, true>(ta, tb, tc, td, p, st) : launch<128, false>(ta, tb, tc, td, p, st);
+    else rc = b_mn ? launch<64, true>(ta, tb, tc, td, p, st) : launch<64, false>(ta, tb, tc, td, p, st);
     if (rc) return rc;
     return (int)cudaGetLastError();
 }

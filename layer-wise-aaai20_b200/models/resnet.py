@@ -70,8 +70,14 @@ class Bottleneck(nn.Module):
         return self.bn3
 
     def forward(self, x):
-        identity = x if self.downsample is None else self.downsample(x)
-        out = self.bn1(self.conv1(x), relu=True)
+        if self.downsample is None:
+            # the block input forks into conv1 and the skip connection: fused backward (ops/conv.py)
+            from ..ops.conv import fork_conv1x1
+            out, identity = fork_conv1x1(self.conv1, x)
+        else:
+            identity = self.downsample(x)
+            out = self.conv1(x)
+        out = self.bn1(out, relu=True)
         out = self.bn2(self.conv2(out), relu=True)
         return self.bn3(self.conv3(out), residual=identity, relu=True)
 

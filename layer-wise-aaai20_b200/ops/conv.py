@@ -131,3 +131,60 @@ def maybe_conv2d(module, x):
     if stats is not None:
         y.bn_stats = stats
     return y
+
+
+# ---- residual fork: conv1x1(x) and the identity branch share one fused backward --------------------------------
+def conv1x1_dgrad_add(dy: torch.Tensor, weight: torch.Tensor, addend: torch.Tensor) -> torch.Tensor:
+    """``dX = dY * W + addend`` in one pass of the native kernel (W = forward weight ``[Cout, Cin, 1, 1]``)."""
+    lib = _native.lib()
+    n, co, h, w = dy.shape
+    ci = weight.shape[1]
+    dx = torch.empty((n, ci, h, w), dtype=dy.dtype, device=dy.device, memory_format=torch.channels_last)
+    st = torch.cuda.current_stream().cuda_stream
+    rc = lib.lwc_conv1x1_add(dy.data_ptr(), weight.data_ptr(), addend.data_ptr(), dx.data_ptr(), n, h, w, co, ci, 1,
+                             C.c_void_p(st))
+    abi.check(rc, "lwc_conv1x1_add")
+    _native.counters.add(1)
+    return dx
+
+
+class _ForkConv1x1(torch.autograd.Function):
+    """``(conv1x1(x, w), x)``: the block input feeds both the first 1x1 convolution and the skip connection.  In the
+    backward pass the two gradients w.r.t. ``x`` would be summed by a separate elementwise kernel; here the data
+    gradient runs on the tcgen05 kernel whose epilogue adds the skip-connection gradient on the way out."""
+
+    @staticmethod
+    def forward(ctx, x, weight):
+        ctx.save_for_backward(x, weight)
+        y = torch.nn.functional.conv2d(x, weight)
+        return y, x.view_as(x)
+
+    @staticmethod
+    def backward(ctx, dy, d_identity):
+        x, weight = ctx.saved_tensors
+        dx = dw = None
+        if not _nhwc(dy):
+            dy = dy.contiguous(memory_format=torch.channels_last)
+        if ctx.needs_input_grad[0]:
+            if d_identity is not None and _nhwc(d_identity) and d_identity.dtype == dy.dtype:
+                dx = conv1x1_dgrad_add(dy, weight, d_identity)
+            else:
+                dx, _ = conv_forward(dy, weight, b_mn=True, out_channels=weight.shape[1])
+                if d_identity is not None:
+                    dx = dx + d_identity
+        if ctx.needs_input_grad[1]:
+            dw = torch.ops.aten.convolution_backward(dy, x, weight, None, [1, 1], [0, 0], [1, 1], False, [0, 0], 1,
+                                                     [False, True, False])[1]
+        return dx, dw
+
+
+def fork_conv1x1(module, x):
+    """``(module(x), x)`` with the fused backward when the layer qualifies; plain ops otherwise."""
+    w = module.weight
+    ok = (x.is_cuda and _native.available() and torch.is_grad_enabled() and x.requires_grad and module.bias is None
+          and tuple(module.kernel_size) == (1, 1) and tuple(module.stride) == (1, 1) and tuple(module.padding) == (0, 0)
+          and module.groups == 1 and x.dtype == torch.bfloat16 and w.dtype == torch.bfloat16 and _nhwc(x)
+          and w.shape[0] % 64 == 0 and w.shape[1] % 64 == 0)
+    if not ok:
+        return module(x), x
+    return _ForkConv1x1.apply(x, w)

@@ -56,3 +56,23 @@ def test_conv3x3_forward_stats_and_dgrad(n, ci, co, h, w):
     yr.backward(dy.float())
     assert (x1.grad.float() - ref_in.grad).abs().max() <= 2e-2 * ref_in.grad.abs().max()
     assert (w1.grad.float() - ref_w.grad).abs().max() <= 3e-2 * ref_w.grad.abs().max()
+
+
+def test_fork_conv1x1_fused_residual_gradient():
+    from layerwise_b200.ops.conv import fork_conv1x1
+    torch.manual_seed(0)
+    conv = torch.nn.Conv2d(256, 64, 1, bias=False).cuda().to(torch.bfloat16).to(memory_format=torch.channels_last)
+    x = torch.randn(4, 256, 14, 14, device="cuda").to(torch.bfloat16).contiguous(memory_format=torch.channels_last)
+    x1 = x.clone().requires_grad_(True)
+    y, ident = fork_conv1x1(conv, x1)
+    gy, gi = torch.randn_like(y), torch.randn_like(ident)
+    torch.autograd.backward([y, ident], [gy, gi])
+    gw1 = conv.weight.grad.clone()
+    conv.weight.grad = None
+    x2 = x.float().requires_grad_(True)
+    w2 = conv.weight.detach().float().requires_grad_(True)
+    y2 = F.conv2d(x2, w2)
+    torch.autograd.backward([y2, x2 * 1.0], [gy.float(), gi.float()])
+    assert (y.float() - y2).abs().max() <= 2e-2 * y2.abs().max()
+    assert (x1.grad.float() - x2.grad).abs().max() <= 2e-2 * x2.grad.abs().max()
+    assert (gw1.float() - w2.grad).abs().max() <= 3e-2 * w2.grad.abs().max()
