@@ -243,3 +243,49 @@ def get_loaders(traindir, valdir, sz, bs, dtype=torch.float32, val_bs=None, work
     val_loader = DataLoader(val_ds, batch_sampler=val_sampler, **kw)
     return (BatchTransformLoader(train_loader, dtype, device, channels_last),
             BatchTransformLoader(val_loader, dtype, device, channels_last), train_sampler, val_sampler)
+
+
+class DevicePrefetcher:
+    """Iterates ``(images, target)`` host batches (ideally pinned) and hands out device tensors, copying batch
+    i+1 on a side stream while batch i is being consumed -- the host->device transfer (33.7 MB per 224-image uint8
+    batch, ~1.3 ms over PCIe) then overlaps the previous step's kernels instead of sitting in front of them.
+    The reference copies with ``non_blocking=True`` on the compute stream (dataloader.py:88-99), which serialises."""
+
+    def __init__(self, loader, device=None):
+        self.loader = loader
+        self.device = torch.device(device or ("cuda" if torch.cuda.is_available() else "cpu"))
+        self.stream = torch.cuda.Stream(device=self.device) if self.device.type == "cuda" else None
+
+    def __len__(self):
+        return len(self.loader)
+
+    def _stage(self, batch):
+        x, y = batch
+        if self.stream is None:
+            return x.to(self.device), y.to(self.device), None
+        with torch.cuda.stream(self.stream):
+            xd = x.to(self.device, non_blocking=True)
+            yd = y.to(self.device, non_blocking=True)
+            ev = torch.cuda.Event()
+            ev.record(self.stream)
+        return xd, yd, ev
+
+    def __iter__(self):
+        it = iter(self.loader)
+        try:
+            staged = self._stage(next(it))
+        except StopIteration:
+            return
+        while staged is not None:
+            xd, yd, ev = staged
+            try:
+                nxt = self._stage(next(it))      # launch the next copy before the consumer enqueues its compute
+            except StopIteration:
+                nxt = None
+            if ev is not None:
+                cur = torch.cuda.current_stream(self.device)
+                cur.wait_event(ev)
+                xd.record_stream(cur)
+                yd.record_stream(cur)
+            yield xd, yd
+            staged = nxt

@@ -56,3 +56,9 @@ def test_synthetic_imagenet_loaders():
     x, y = next(iter(trn))
     assert x.shape == (4, 3, 32, 32) and x.dtype == torch.float32 and abs(float(x.mean())) < 1.0
     assert len(trn) == 4 and len(val) >= 1
+
+
+def test_device_prefetcher_cpu_passthrough():
+    batches = [(torch.full((2, 3), i, dtype=torch.uint8), torch.tensor([i, i])) for i in range(4)]
+    out = list(data.DevicePrefetcher(batches, device="cpu"))
+    assert len(out) == 4 and all(int(x[0, 0]) == i and y.tolist() == [i, i] for i, (x, y) in enumerate(out))
