@@ -169,10 +169,15 @@ class TorchEngine:
         live = [(i, p) for i, p in enumerate(self.params) if p.grad is not None]
         if cfg.compress == LAYERWISE:
             for i, p in live:
-                g = p.grad.data.view(-1)
+                gd = p.grad.data
+                # channels_last (or otherwise strided) gradients cannot be viewed flat: work on a logical-order copy
+                g = gd.view(-1) if gd.is_contiguous() else gd.reshape(-1)
                 c = self._compress(g, None if self.residual is None else self.residual[i], i)
                 self._allreduce_avg(c, W)
-                g.copy_(c)
+                if gd.is_contiguous():
+                    g.copy_(c)
+                else:
+                    gd.copy_(c.view(gd.shape))
         elif cfg.compress == ENTIREMODEL:
             if live:
                 if self.flat_residual is not None and len(live) != len(self.params):
