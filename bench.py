@@ -53,6 +53,7 @@ def parse():
     p.add_argument("--engine", default="auto")
     p.add_argument("--ref-dtype", default="fp16", choices=["fp16", "fp32"])
     p.add_argument("--skip-e2e", action="store_true")
+    p.add_argument("--nvls", action="store_true", help="NVSwitch-multicast payload stores (N > 1)")
     p.add_argument("--phase-times", action="store_true", help="also report compress+comm ms/step")
     return p.parse_args()
 
@@ -154,7 +155,7 @@ def build_ours(args, world, rank):
     from layerwise_b200.train.imagenet import Trainer
     _native.require()
     cfg = CompressionConfig(compress=args.compress, method=args.method, ratio=args.ratio,
-                            error_feedback=not args.no_ef)
+                            error_feedback=not args.no_ef, nvls=args.nvls)
     tr = Trainer(arch=args.arch, dtype="bf16", cfg=cfg, lr=0.1, momentum=0.9, weight_decay=1e-4,
                  overlap=not args.no_overlap, engine=args.engine, device=torch.device("cuda", torch.cuda.current_device()))
     return tr

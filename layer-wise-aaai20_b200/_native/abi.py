@@ -68,6 +68,7 @@ def declare(lib: C.CDLL):
     sig("lwc_plan_slot_bytes", sz, vp)
     sig("lwc_plan_region_bytes", sz, vp)
     sig("lwc_plan_bind", C.c_int, vp, c_void_pp, c_void_pp)
+    sig("lwc_plan_bind_multicast", C.c_int, vp, vp)
     sig("lwc_plan_set_random", C.c_int, vp, c_void_pp)
     sig("lwc_plan_update_grads", C.c_int, vp, c_void_pp, vp)
     sig("lwc_plan_send", C.c_int, vp, u64, vp)

@@ -117,6 +117,9 @@ struct DevPlan {     // passed by value to kernels
     unsigned long long code_stride; // bytes per chunk in the code area
     char* region[LWC_MAX_WORLD];
     uint64_t* flags[LWC_MAX_WORLD];
+    // NVLS variant: multicast address of this plan's region (one store lands in every rank's slot through the
+    // NVSwitch); NULL -> one unicast store per destination
+    char* mc_region;
     // stand-alone selection: write (idx, val, count) here instead of into exchange slots
     uint32_t* direct_idx;
     float* direct_val;
@@ -126,6 +129,24 @@ struct DevPlan {     // passed by value to kernels
 __device__ __forceinline__ char* slot_ptr(const DevPlan& p, int dst, int src) {
     const unsigned long long parity = p.step & 1ULL;
     return p.region[dst] + (parity * p.world + src) * p.slot_bytes;
+}
+
+__device__ __forceinline__ char* mc_slot_ptr(const DevPlan& p, int src) {
+    const unsigned long long parity = p.step & 1ULL;
+    return p.mc_region + (parity * p.world + src) * p.slot_bytes;
+}
+// multimem.st: a store to a multicast address is replicated by the switch to every GPU bound to it
+__device__ __forceinline__ void mm_st_u32(void* a, uint32_t v) {
+    asm volatile("multimem.st.relaxed.sys.global.u32 [%0], %1;" ::"l"(a), "r"(v) : "memory");
+}
+__device__ __forceinline__ void mm_st_f32(void* a, float v) {
+    asm volatile("multimem.st.relaxed.sys.global.f32 [%0], %1;" ::"l"(a), "f"(v) : "memory");
+}
+__device__ __forceinline__ void mm_st_u64(void* a, unsigned long long v) {
+    asm volatile("multimem.st.relaxed.sys.global.u64 [%0], %1;" ::"l"(a), "l"(v) : "memory");
+}
+__device__ __forceinline__ void mm_st_v4(void* a, float x, float y, float z, float w) {
+    asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(a), "f"(x), "f"(y), "f"(z), "f"(w) : "memory");
 }
 
 // ---- selection key -----------------------------------------------------------------------------
@@ -496,6 +517,8 @@ __global__ void __launch_bounds__(kThreads) k_compact_send(DevPlan p) {
     // header: the CTA owning the group's first chunk publishes the entry count to every rank
     if (p.direct_idx) {
         if ((int)blockIdx.x == cfg.chunk_begin && tid == 0) p.direct_count[t.group] = (long long)gs.kept;
+    } else if ((int)blockIdx.x == cfg.chunk_begin && p.mc_region) {
+        if (tid == 0) mm_st_u64(reinterpret_cast<long long*>(mc_slot_ptr(p, p.rank)) + t.group, (unsigned long long)gs.kept);
     } else if ((int)blockIdx.x == cfg.chunk_begin && tid < p.world) {
         long long* hdr = reinterpret_cast<long long*>(slot_ptr(p, tid, p.rank));
         hdr[t.group] = (long long)gs.kept;
@@ -561,6 +584,10 @@ __global__ void __launch_bounds__(kThreads) k_compact_send(DevPlan p) {
                 } else if (p.direct_idx) {
                     p.direct_idx[cfg.pay_off + pos] = gidx;
                     p.direct_val[cfg.pay_off + pos] = v[it][k];
+                } else if (p.mc_region) {
+                    char* s = mc_slot_ptr(p, p.rank);
+                    mm_st_u32(reinterpret_cast<uint32_t*>(s + p.idx_off) + cfg.pay_off + pos, gidx);
+                    mm_st_f32(reinterpret_cast<float*>(s + p.val_off) + cfg.pay_off + pos, v[it][k]);
                 } else {
                     for (int d = 0; d < p.world; ++d) {
                         char* s = slot_ptr(p, d, p.rank);
@@ -573,7 +600,15 @@ __global__ void __launch_bounds__(kThreads) k_compact_send(DevPlan p) {
         }
     }
     __syncthreads();
-    if (n_out > 0 && staged) {
+    if (n_out > 0 && staged && p.mc_region && !p.direct_idx) {
+        char* s = mc_slot_ptr(p, p.rank);
+        uint32_t* di = reinterpret_cast<uint32_t*>(s + p.idx_off) + cfg.pay_off + pos_begin;
+        float* dv = reinterpret_cast<float*>(s + p.val_off) + cfg.pay_off + pos_begin;
+        for (unsigned e = tid; e < n_out; e += kThreads) {
+            mm_st_u32(di + e, st_idx[e]);
+            mm_st_f32(dv + e, st_val[e]);
+        }
+    } else if (n_out > 0 && staged) {
         const int ndst = p.direct_idx ? 1 : p.world;
         for (int d = 0; d < ndst; ++d) {
             char* s = p.direct_idx ? nullptr : slot_ptr(p, d, p.rank);
@@ -682,7 +717,9 @@ __global__ void __launch_bounds__(kThreads) k_quant_send(DevPlan p) {
     const uint64_t salt = group_salt(p, cfg.uid);
     const unsigned long long coff = p.code_off + (unsigned long long)blockIdx.x * p.code_stride;
 
-    if ((int)blockIdx.x == cfg.chunk_begin && tid < p.world) {
+    if ((int)blockIdx.x == cfg.chunk_begin && p.mc_region) {
+        if (tid == 0) mm_st_f32(reinterpret_cast<float*>(mc_slot_ptr(p, p.rank)) + t.group, scale);
+    } else if ((int)blockIdx.x == cfg.chunk_begin && tid < p.world) {
         float* hdr = reinterpret_cast<float*>(slot_ptr(p, tid, p.rank));
         hdr[t.group] = scale;
     }
@@ -694,9 +731,13 @@ __global__ void __launch_bounds__(kThreads) k_quant_send(DevPlan p) {
         if (j < c.len) load_acc<GradT>(t, c.start, j, c.len, v);
         if (p.method == LWC_NONE) {
             if (j < c.len) {
-                for (int d = 0; d < p.world; ++d) {
-                    GradT* dst = reinterpret_cast<GradT*>(slot_ptr(p, d, p.rank) + coff);
-                    store_quad<GradT>(dst, j, c.len, true, v);
+                if (p.mc_region && sizeof(GradT) == 4 && j + 4 <= c.len) {
+                    mm_st_v4(reinterpret_cast<float*>(mc_slot_ptr(p, p.rank) + coff) + j, v[0], v[1], v[2], v[3]);
+                } else {
+                    for (int d = 0; d < p.world; ++d) {
+                        GradT* dst = reinterpret_cast<GradT*>(slot_ptr(p, d, p.rank) + coff);
+                        store_quad<GradT>(dst, j, c.len, true, v);
+                    }
                 }
             }
             continue;
@@ -719,8 +760,12 @@ __global__ void __launch_bounds__(kThreads) k_quant_send(DevPlan p) {
             word |= __shfl_xor_sync(0xffffffffu, word, 1);
             word |= __shfl_xor_sync(0xffffffffu, word, 2);
             if ((lane & 3) == 0 && j < c.len) {
-                for (int d = 0; d < p.world; ++d)
-                    reinterpret_cast<uint32_t*>(slot_ptr(p, d, p.rank) + coff)[q >> 2] = word;
+                if (p.mc_region) {
+                    mm_st_u32(reinterpret_cast<uint32_t*>(mc_slot_ptr(p, p.rank) + coff) + (q >> 2), word);
+                } else {
+                    for (int d = 0; d < p.world; ++d)
+                        reinterpret_cast<uint32_t*>(slot_ptr(p, d, p.rank) + coff)[q >> 2] = word;
+                }
             }
         } else {   // LWC_DITHERING
 #pragma unroll
@@ -740,10 +785,16 @@ __global__ void __launch_bounds__(kThreads) k_quant_send(DevPlan p) {
             sw |= __shfl_xor_sync(0xffffffffu, sw, 2);
             sw |= __shfl_xor_sync(0xffffffffu, sw, 4);
             if (j < c.len) {
-                for (int d = 0; d < p.world; ++d) {
-                    char* base = slot_ptr(p, d, p.rank) + coff;
-                    reinterpret_cast<uint32_t*>(base)[q] = code;
-                    if ((lane & 7) == 0) reinterpret_cast<uint32_t*>(base + kChunk)[q >> 3] = sw;
+                if (p.mc_region) {
+                    char* base = mc_slot_ptr(p, p.rank) + coff;
+                    mm_st_u32(reinterpret_cast<uint32_t*>(base) + q, code);
+                    if ((lane & 7) == 0) mm_st_u32(reinterpret_cast<uint32_t*>(base + kChunk) + (q >> 3), sw);
+                } else {
+                    for (int d = 0; d < p.world; ++d) {
+                        char* base = slot_ptr(p, d, p.rank) + coff;
+                        reinterpret_cast<uint32_t*>(base)[q] = code;
+                        if ((lane & 7) == 0) reinterpret_cast<uint32_t*>(base + kChunk)[q >> 3] = sw;
+                    }
                 }
             }
         }
@@ -972,6 +1023,14 @@ extern "C" int lwc_plan_bind(LwcPlan* P, void* const* region_dev, void* const* f
         P->dev.flags[d] = (uint64_t*)flags_dev[d];
     }
     P->bound = true;
+    return 0;
+}
+
+// NVLS variant: mc_region_dev is the multicast mapping of the SAME symmetric region that lwc_plan_bind received
+// as unicast pointers (all ranks bound to one multicast object at identical offsets).  NULL switches back.
+extern "C" int lwc_plan_bind_multicast(LwcPlan* P, void* mc_region_dev) {
+    if (!P) return LWC_EINVAL;
+    P->dev.mc_region = (char*)mc_region_dev;
     return 0;
 }
 

@@ -67,6 +67,7 @@ class CompressionConfig:
     capacity_factor: float = 1.25   # fused engine: payload slots hold factor * nominal + slack
     dense_capacity: float = 0.25    # fused engine: slot fraction for threshold-style methods
     bucket_cap_mb: float = 25.0     # hook-driven mode: bucket size (dense bytes)
+    nvls: bool = False              # fused engine: NVSwitch-multicast payload stores when the host exposes them
 
     def __post_init__(self):
         self.compress = canonical_compress(self.compress)
@@ -235,6 +236,7 @@ class GradientExchanger:
             if cfg.method_name == cref.NONE and dense == "two_shot":
                 self.engine = DenseEngine(self.params, cfg, group=group, overlap=overlap, **engine_kw)
             else:
+                engine_kw.setdefault("nvls", cfg.nvls)
                 self.engine = FusedEngine(self.params, cfg, group=group, overlap=overlap, **engine_kw)
         else:
             self.engine = TorchEngine(self.params, cfg, group=group)

@@ -111,6 +111,10 @@ class ExchangePlan:
         abi.check(self.lib.lwc_plan_bind(self.handle, _ptr_array(region_ptrs), _ptr_array(flag_ptrs)),
                   "lwc_plan_bind")
 
+    def bind_multicast(self, mc_region_ptr: int):
+        """NVLS variant: payload stores go once to the multicast mapping of the region (0 switches back)."""
+        abi.check(self.lib.lwc_plan_bind_multicast(self.handle, C.c_void_p(mc_region_ptr or None)), "lwc_plan_bind_multicast")
+
     def set_random(self, rand: Optional[List[Optional[torch.Tensor]]]):
         self._rand_keep = rand
         if rand is None:
@@ -178,7 +182,8 @@ class FusedEngine:
     name = "fused"
 
     def __init__(self, params: List[torch.nn.Parameter], cfg, group=None, overlap: bool = False,
-                 out_dtype: Optional[torch.dtype] = None, num_buckets: Optional[int] = None, steal: bool = True):
+                 out_dtype: Optional[torch.dtype] = None, num_buckets: Optional[int] = None, steal: bool = True,
+                 nvls: bool = False):
         _native.require()
         self.params, self.cfg, self.group = params, cfg, group
         # steal=True: ``zero_grad`` sets ``p.grad = None`` so autograd hands over its freshly written
@@ -239,10 +244,15 @@ class FusedEngine:
             total += (b.plan.region_bytes + 255) // 256 * 256
         flag_off = total
         total += FLAG_BYTES * len(self.buckets)
-        self.heap = PeerHeap(total, group=group, device=self.device)
+        # nvls=True: allocate the heap through the symmetric-memory allocator and, if the host exposes NVSwitch
+        # multicast, send every payload with ONE multimem store instead of one unicast store per peer
+        self.heap = PeerHeap(total, group=group, device=self.device, multicast=nvls)
+        self.nvls = bool(nvls and self.heap.mc_ptr)
         for bi, b in enumerate(self.buckets):
             b.plan.bind([ptr + offs[bi] for ptr in self.heap.ptrs],
                         [ptr + flag_off + bi * FLAG_BYTES for ptr in self.heap.ptrs])
+            if self.nvls:
+                b.plan.bind_multicast(self.heap.mc_ptr + offs[bi])
         self.comm_stream = torch.cuda.Stream(device=self.device) if overlap else None
         self._hooks = []
         self._param_bucket = {}

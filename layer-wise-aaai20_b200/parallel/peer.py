@@ -77,11 +77,15 @@ class DeviceBuffer:
 class PeerHeap:
     """One symmetric heap per rank; ``ptrs[r]`` is rank r's heap base as seen from here."""
 
-    def __init__(self, nbytes: int, group=None, device=None):
+    def __init__(self, nbytes: int, group=None, device=None, multicast: bool = False):
         self.group = group
         self.world = dist.get_world_size(group) if dist.is_initialized() else 1
         self.rank = dist.get_rank(group) if dist.is_initialized() else 0
         self.nbytes = int(nbytes)
+        self.mc_ptr = 0          # NVLS multicast mapping of the heap (0 = not available / not requested)
+        self._symm = None
+        if multicast and self.world > 1 and self._init_symmetric(device):
+            return
         self.local = DeviceBuffer.allocate(self.nbytes, device)
         self.ptrs: List[int] = [0] * self.world
         self.ptrs[self.rank] = self.local.ptr
@@ -100,12 +104,43 @@ class PeerHeap:
                 self._opened.append(out.value)
             dist.barrier(group=group)
 
+    def _init_symmetric(self, device) -> bool:
+        """Heap through torch's symmetric-memory allocator, which also maps an NVLS *multicast* view of it when the
+        host exposes NVSwitch multicast to user processes (CUDA VMM + cuMulticast*; fabric/fd handle exchange is
+        plumbing we do not re-implement).  Returns False (caller falls back to cudaIpc) when unavailable."""
+        try:
+            import torch.distributed._symmetric_memory as sm
+            device = torch.device("cuda", torch.cuda.current_device()) if device is None else torch.device(device)
+            pg = self.group if self.group is not None else dist.group.WORLD
+            try:
+                sm.enable_symm_mem_for_group(pg.group_name)
+            except Exception:
+                pass
+            t = sm.empty(self.nbytes, dtype=torch.uint8, device=device)
+            t.zero_()
+            torch.cuda.synchronize(device)
+            h = sm.rendezvous(t, pg.group_name)
+            mc = int(getattr(h, "multicast_ptr", 0) or 0)
+            ptrs = [int(p) for p in h.buffer_ptrs]
+            if len(ptrs) != self.world:
+                return False
+        except Exception:
+            return False
+        self._symm = (t, h)
+        self.ptrs = ptrs
+        self.mc_ptr = mc
+        self._opened = []
+        self.local = DeviceBuffer(ptrs[self.rank], self.nbytes, device, owner=False)
+        dist.barrier(group=self.group)
+        return True
+
     def close(self):
         lib = _native.lib()
         for p in self._opened:
             lib.lwc_ipc_close_handle(C.c_void_p(p))
         self._opened = []
         self.local.free()
+        self._symm = None
 
 
 class LocalWorld:

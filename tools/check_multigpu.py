@@ -20,6 +20,9 @@ from layerwise_b200.ops import compress_ref as cr  # noqa: E402
 from layerwise_b200.parallel.exchange import CompressionConfig, GradientExchanger  # noqa: E402
 
 
+NVLS = "--nvls" in sys.argv
+
+
 def main():
     rank, world, local = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"]), int(os.environ["LOCAL_RANK"])
     torch.cuda.set_device(local)
@@ -35,7 +38,7 @@ def main():
                                     capacity_factor=1.5, dense_capacity=1.0, **kw)
             g = torch.Generator(device="cuda").manual_seed(1000 + rank)
             params = [torch.nn.Parameter(torch.zeros(n, device="cuda")) for n in sizes]
-            ex = GradientExchanger(params, cfg, engine="fused")
+            ex = GradientExchanger(params, cfg, engine="fused", nvls=NVLS)
             for p in params:
                 p.grad.copy_(torch.randn(p.shape, device="cuda", generator=g))
             local_g = [p.grad.clone() for p in params]
@@ -80,7 +83,7 @@ def main():
             dist.all_reduce(ms, op=dist.ReduceOp.MAX)
             flag = torch.tensor([1.0 if good else 0.0], device="cuda")
             dist.all_reduce(flag, op=dist.ReduceOp.MIN)
-            results[name] = {"ok": bool(flag.item()), "ms_per_exchange": round(float(ms.item()), 4), "stats": st}
+            results[name] = {"nvls": bool(getattr(ex.engine, "nvls", False)), "ok": bool(flag.item()), "ms_per_exchange": round(float(ms.item()), 4), "stats": st}
             ok = ok and bool(flag.item())
             ex.engine.close()
     if rank == 0:
