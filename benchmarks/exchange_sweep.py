@@ -65,6 +65,8 @@ def main():
     ap.add_argument("--models", default="resnet9,alexnet,vgg16,resnet50")
     ap.add_argument("--iters", type=int, default=10)
     ap.add_argument("--quick", action="store_true")
+    ap.add_argument("--nvls", action="store_true", help="multicast payload stores in the fused engine")
+    ap.add_argument("--only-ours", action="store_true")
     ap.add_argument("--out", default="gpurun_out/exchange_sweep.json")
     args = ap.parse_args()
     world, rank, local = int(os.environ.get("WORLD_SIZE", 1)), int(os.environ.get("RANK", 0)), int(os.environ.get("LOCAL_RANK", 0))
@@ -81,7 +83,8 @@ def main():
              ("Randomk", dict(ratio=0.001)), ("Randomk", dict(ratio=0.01)), ("Randomk", dict(ratio=0.1)),
              ("TernGrad", {}), ("RandomDithering", dict(qstates=255)), ("none", {})]
     if args.quick:
-        cases = [("Topk", dict(ratio=0.01)), ("Randomk", dict(ratio=0.01)), ("RandomDithering", dict(qstates=255))]
+        cases = [("Topk", dict(ratio=0.01)), ("Randomk", dict(ratio=0.01)), ("TernGrad", {}), ("RandomDithering", dict(qstates=255)),
+                 ("none", {})]
     rows = []
     for mname in args.models.split(","):
         shapes = param_shapes(mname)
@@ -92,7 +95,7 @@ def main():
                 g = torch.Generator(device="cuda").manual_seed(7 + rank)
                 # ---- ours --------------------------------------------------------------------------
                 bag = Bag(shapes, "cuda")
-                ex = GradientExchanger(bag, cfg, engine="fused")
+                ex = GradientExchanger(bag, cfg, engine="fused", nvls=args.nvls)
                 for p in bag.parameters():
                     p.grad.copy_(torch.randn(p.shape, device="cuda", generator=g))
                 ms_ours = time_ms(ex.exchange, args.iters, local)
@@ -101,6 +104,13 @@ def main():
                 del bag, ex
                 torch.cuda.empty_cache()
                 # ---- reference ---------------------------------------------------------------------
+                if args.only_ours:
+                    row = {"model": mname, "compress": compress, "method": method, **kw, "world": world, "nvls": args.nvls,
+                           "ms_ours": ms_ours, "timeouts": st["timeouts"], "dropped": st["dropped"]}
+                    rows.append(row)
+                    if rank == 0:
+                        print(json.dumps(row), flush=True)
+                    continue
                 bag = Bag(shapes, "cuda")
                 for p in bag.parameters():
                     p.grad = torch.randn(p.shape, device="cuda", generator=g)
