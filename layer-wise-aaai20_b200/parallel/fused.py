@@ -199,8 +199,8 @@ class FusedEngine:
         self.overlap = overlap
         dts = {p.dtype for p in params}
         self.entire = cfg.compress == "entiremodel"
-        if self.entire and len(dts) > 1:
-            raise ValueError("entire-model mode needs all parameters in one dtype")
+        # entire-model selection runs over one flat gradient; with mixed precision (bf16 weights, fp32 batch-norm
+        # parameters) there is one flat gradient -- hence one selection group -- per precision class
         # ---- arenas: grads (per dtype) and fp32 error-feedback residuals ----------------------------
         self._grad_arena: Dict[torch.dtype, torch.Tensor] = {}
         self.grad_views: List[torch.Tensor] = [None] * len(params)
@@ -227,7 +227,7 @@ class FusedEngine:
         # ---- buckets -----------------------------------------------------------------------------------------
         order = list(range(len(params)))[::-1] if overlap else list(range(len(params)))
         if self.entire:
-            buckets = [list(range(len(params)))]
+            buckets = [[i for i, p in enumerate(params) if p.dtype == dt] for dt in sorted(dts, key=str)]
         else:
             buckets = self._make_buckets(order, num_buckets)
         self.buckets = [_Bucket(b) for b in buckets]
