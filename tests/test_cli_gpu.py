@@ -50,3 +50,21 @@ def test_trainer_with_ddp_wrappers(wrapper):
     for _ in range(2):
         _, loss = tr.train_step(x, y)
     assert torch.isfinite(loss)
+
+
+@pytest.mark.parametrize("dtype,compress,method", [("fp16", "entiremodel", "Topk"), ("fp32", "layerwise", "AdaptiveThreshold"),
+                                                   ("bf16", "entiremodel", "RandomDithering")])
+def test_trainer_precisions_and_modes(dtype, compress, method):
+    """--fp16 (loss scale 1024, fp32 masters) as in the reference recipe, fp32, and bf16; entire-model and layer-wise."""
+    from layerwise_b200.parallel.exchange import CompressionConfig
+    from layerwise_b200.train.imagenet import Trainer
+    cfg = CompressionConfig(compress=compress, method=method, ratio=0.05, qstates=255, error_feedback=True)
+    tr = Trainer(arch="resnet18", num_classes=10, dtype=dtype, cfg=cfg, lr=0.01, loss_scale=1024.0, device="cuda:0")
+    x = torch.randint(0, 256, (8, 3, 64, 64), dtype=torch.uint8, device="cuda")
+    y = torch.randint(0, 10, (8,), device="cuda")
+    w0 = tr.master_params[0].detach().clone()
+    for _ in range(3):
+        out, loss = tr.train_step(x, y)
+    assert torch.isfinite(loss) and out.dtype == tr.dtype
+    assert not torch.equal(w0, tr.master_params[0])
+    assert tr.exchanger.engine_name.startswith("fused")
