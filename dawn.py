@@ -44,6 +44,8 @@ def get_parser():
     p.add_argument("--backend", type=str, default=None)
     p.add_argument("--engine", type=str, default="auto")
     p.add_argument("--synthetic", action="store_true")
+    p.add_argument("--synthetic_size", type=int, nargs=2, default=[4096, 1024], metavar=("TRAIN", "TEST"),
+                   help="images in the synthetic train / test sets (50000 10000 = CIFAR-10's sizes)")
     p.add_argument("--max_batches", type=int, default=None)
     p.add_argument("--dtype", type=str, default="fp32", choices=["fp32", "bf16", "fp16"])
     p.add_argument("--host_loader", action="store_true", help="DataLoader pipeline instead of device-resident data")
@@ -61,7 +63,7 @@ def main(argv=None):
         torch.cuda.set_device(comm.env_local_rank() % torch.cuda.device_count())
     device = torch.device("cuda", torch.cuda.current_device()) if use_cuda else torch.device("cpu")
 
-    dataset = synthetic_cifar10(4096, 1024) if args.synthetic else cifar10(args.data_dir)
+    dataset = synthetic_cifar10(*args.synthetic_size) if args.synthetic else cifar10(args.data_dir)
     epochs = args.epochs or (40 if args.method in ("Randomk", "Thresholdv") else 24)
     lr_schedule = PiecewiseLinear([0, 5, epochs], [0, 0.4, 0])
     bs = args.batch_size
