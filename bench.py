@@ -55,6 +55,9 @@ def parse():
     p.add_argument("--skip-e2e", action="store_true")
     p.add_argument("--nvls", action="store_true", help="NVSwitch-multicast payload stores (N > 1)")
     p.add_argument("--phase-times", action="store_true", help="also report compress+comm ms/step")
+    p.add_argument("--graph", action="store_true", default=True,
+                   help="replay the whole train step as one CUDA graph (default; bitwise identical to eager stepping)")
+    p.add_argument("--no-graph", dest="graph", action="store_false", help="step eagerly (~1.5k launches per step)")
     return p.parse_args()
 
 
@@ -243,6 +246,8 @@ def main():
         dtype, par = args.ref_dtype, f"dp{world}"
     else:
         tr = build_ours(args, world, rank)
+        if args.graph:
+            tr.capture_graph(dev_x[0], dev_y[0], warmup=3)
         step_dev = lambda i: tr.train_step(dev_x[i % nbuf], dev_y[i % nbuf])[1]     # noqa: E731
         step_e2e = lambda i: tr.train_step(host_x[i % nbuf], host_y[i % nbuf])[1]   # noqa: E731
         dtype, par = "bf16", f"dp{world}"
@@ -305,7 +310,8 @@ def main():
                        "image_size": S, "parallelism": par, "compress": args.compress, "method": args.method,
                        "ratio": args.ratio, "error_feedback": (not args.no_ef) if args.impl == "ours" else False,
                        "l2_policy": "inputs+activations per step (>1 GB) exceed the 126 MB L2; 4 rotating input buffers",
-                       "optimizer": "SGD momentum 0.9 nesterov wd 1e-4, fp32 masters"},
+                       "optimizer": "SGD momentum 0.9 nesterov wd 1e-4, fp32 masters",
+                       "cuda_graph": bool(args.graph and args.impl == "ours")},
             "clocks": clocks, "e2e": e2e, "gpu_launches": launches["n"],
         }
         out.update(extra)

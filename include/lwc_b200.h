@@ -52,6 +52,9 @@ int lwc_malloc(void** out_dev, size_t bytes);
 int lwc_free(void* dev);
 int lwc_memset_async(void* dev, int value, size_t bytes, void* stream);
 int lwc_ipc_get_handle(void* dev, void* handle_out_64B);
+/* A handle names the driver's whole underlying block; the importer adds the exporter's offset inside that block
+ * (lwc_ipc_base_offset) to the base that lwc_ipc_open_handle returns.  Opens are reference-counted per handle. */
+int lwc_ipc_base_offset(void* dev, uint64_t* offset_out);
 int lwc_ipc_open_handle(const void* handle_64B, void** out_dev);
 int lwc_ipc_close_handle(void* dev);
 int lwc_enable_peer_access(int peer_device);           /* idempotent */
@@ -167,6 +170,7 @@ typedef struct {
     int32_t model_dtype;     /* dtype of model copies (ignored when model_dev == NULL) */
     float lr, momentum, dampening, weight_decay, grad_scale;
     int32_t nesterov, first_step;
+    const float* lr_dev;     /* optional: learning rate read from device memory (CUDA-graph replay) */
 } LwcSgdDesc;
 /* table_dev: device array of num_tensors LwcSgdTensor; chunk table built by lwc_sgd_plan */
 typedef struct { void* param; const void* grad; void* mom; void* model; int64_t n; } LwcSgdTensor;
@@ -181,6 +185,11 @@ int lwc_plan_update_grads(LwcPlan* plan, const void* const* grad_dev, void* stre
 /* Upper bound (ms, default 10000) of every in-kernel wait on a peer flag; expiry is counted in
  * lwc_plan_stats()[2] and the kernel proceeds -- a dead peer cannot hang a GPU. */
 int lwc_set_flag_timeout_ms(unsigned int ms);
+/* Graph-safe mode: keep the step counter on the device (read by every kernel, advanced by the receiver) so a
+ * captured send/recv sequence can be replayed; gradient-table uploads made during capture use pinned staging. */
+int lwc_plan_use_device_step(LwcPlan* plan, int enable, uint64_t start_step);
+/* NVLS variant: multicast mapping of the region given to lwc_plan_bind (NULL switches back to unicast). */
+int lwc_plan_bind_multicast(LwcPlan* plan, void* mc_region_dev);
 
 /* ------------------------------------------------------------------------------------------
  * bf16 GEMM on tcgen05 / TMEM / TMA: C[M,N] (+)= A * B^T (+bias)(ReLU).  a_mn / b_mn select MN-major

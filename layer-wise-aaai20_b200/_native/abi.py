@@ -24,7 +24,7 @@ class LwcSgdDesc(C.Structure):
         ("num_tensors", C.c_int32), ("grad_dtype", C.c_int32), ("model_dtype", C.c_int32),
         ("lr", C.c_float), ("momentum", C.c_float), ("dampening", C.c_float),
         ("weight_decay", C.c_float), ("grad_scale", C.c_float),
-        ("nesterov", C.c_int32), ("first_step", C.c_int32),
+        ("nesterov", C.c_int32), ("first_step", C.c_int32), ("lr_dev", C.c_void_p),
     ]
 
 
@@ -58,6 +58,7 @@ def declare(lib: C.CDLL):
     sig("lwc_free", C.c_int, vp)
     sig("lwc_memset_async", C.c_int, vp, C.c_int, sz, vp)
     sig("lwc_ipc_get_handle", C.c_int, vp, vp)
+    sig("lwc_ipc_base_offset", C.c_int, vp, C.POINTER(C.c_uint64))
     sig("lwc_ipc_open_handle", C.c_int, vp, c_void_pp)
     sig("lwc_ipc_close_handle", C.c_int, vp)
     sig("lwc_enable_peer_access", C.c_int, C.c_int)
@@ -68,6 +69,7 @@ def declare(lib: C.CDLL):
     sig("lwc_plan_slot_bytes", sz, vp)
     sig("lwc_plan_region_bytes", sz, vp)
     sig("lwc_plan_bind", C.c_int, vp, c_void_pp, c_void_pp)
+    sig("lwc_plan_use_device_step", C.c_int, vp, C.c_int, u64)
     sig("lwc_plan_bind_multicast", C.c_int, vp, vp)
     sig("lwc_plan_set_random", C.c_int, vp, c_void_pp)
     sig("lwc_plan_update_grads", C.c_int, vp, c_void_pp, vp)

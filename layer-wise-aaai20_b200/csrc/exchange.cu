@@ -86,7 +86,8 @@ struct Counters {
     unsigned long long timeouts;
     unsigned long long bytes;
     unsigned int done;      // CTA completion ticket of the send kernel
-    unsigned int pad;
+    unsigned int done_recv; // CTA completion ticket of the receive kernel (device-side step counter mode)
+    unsigned long long dev_step;   // step counter kept on the device (CUDA-graph replays cannot change kernel arguments)
 };
 
 struct DevPlan {     // passed by value to kernels
@@ -107,6 +108,7 @@ struct DevPlan {     // passed by value to kernels
     float threshold;
     unsigned long long seed;
     unsigned long long step;
+    unsigned long long* step_ptr;    // non-NULL: the step lives on the device (read at kernel start, bumped by the receiver)
     unsigned long long timeout_ns;   // bounded wait on peer flags
     // slot geometry
     unsigned long long slot_bytes;
@@ -180,6 +182,7 @@ enum { STAT_NONE = 0, STAT_HIST = 1, STAT_MAX = 2, STAT_SUMSQ = 3 };
 // ---- pass 1: error-feedback accumulate + first statistic -----------------------------------------------
 template <typename GradT, int STAT>
 __global__ void __launch_bounds__(kThreads) k_pre(DevPlan p) {
+    if (p.step_ptr) p.step = *p.step_ptr;
     __shared__ unsigned sh_hist[STAT == STAT_HIST ? kHist1 : 1];
     __shared__ float sh_red[kThreads / 32];
     const ChunkRec c = p.chunks[blockIdx.x];
@@ -246,6 +249,7 @@ __global__ void __launch_bounds__(kThreads) k_pre(DevPlan p) {
 // ---- radix levels 2 and 3 -----------------------------------------------------------------------------
 template <typename GradT, int LEVEL>
 __global__ void __launch_bounds__(kThreads) k_hist(DevPlan p) {
+    if (p.step_ptr) p.step = *p.step_ptr;
     __shared__ unsigned sh_hist[kHist2];
     const ChunkRec c = p.chunks[blockIdx.x];
     const TensorRec t = p.tensors[c.tensor];
@@ -435,6 +439,7 @@ __global__ void __launch_bounds__(kThreads) k_group(DevPlan p, int mode) {
 // ---- per chunk counts of keys > T and == T -----------------------------------------------------------
 template <typename GradT>
 __global__ void __launch_bounds__(kThreads) k_count(DevPlan p) {
+    if (p.step_ptr) p.step = *p.step_ptr;
     __shared__ unsigned sh[kThreads / 32];
     const ChunkRec c = p.chunks[blockIdx.x];
     const TensorRec t = p.tensors[c.tensor];
@@ -487,6 +492,7 @@ __device__ __forceinline__ void publish_when_last(const DevPlan& p) {
 // ---- ordered compaction + residual update + stores to every rank ---------------------------------------
 template <typename GradT>
 __global__ void __launch_bounds__(kThreads) k_compact_send(DevPlan p) {
+    if (p.step_ptr) p.step = *p.step_ptr;
     __shared__ uint32_t st_idx[kStage];
     __shared__ float st_val[kStage];
     __shared__ unsigned sh_warp[kThreads / 32];
@@ -644,6 +650,7 @@ __device__ __forceinline__ void wait_sources(const DevPlan& p) {
 // ---- receiver, sparse: every CTA owns one chunk of the dense output --------------------------------------
 template <typename OutT>
 __global__ void __launch_bounds__(kThreads) k_recv_sparse(DevPlan p) {
+    if (p.step_ptr) p.step = *p.step_ptr;
     __shared__ float acc[kChunk];
     __shared__ int sh_rng[2];
     const ChunkRec c = p.chunks[blockIdx.x];
@@ -684,6 +691,17 @@ __global__ void __launch_bounds__(kThreads) k_recv_sparse(DevPlan p) {
         for (int k = 0; k < 4; ++k) v[k] = (j + k < c.len) ? acc[j + k] * inv : 0.0f;
         store_quad<OutT>(o, j, c.len, ov, v);
     }
+    if (p.step_ptr) {      // the last CTA to finish advances the device-side step counter
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            const unsigned ticket = atomicAdd(&p.counters->done_recv, 1u);
+            if (ticket == gridDim.x - 1) {
+                p.counters->done_recv = 0;
+                __threadfence();
+                *p.step_ptr = p.step + 1;
+            }
+        }
+    }
 }
 
 // ---- quantisers and the dense path -------------------------------------------------------------------
@@ -707,6 +725,7 @@ __device__ __forceinline__ void quad_uniforms(const DevPlan& p, const TensorRec&
 
 template <typename GradT>
 __global__ void __launch_bounds__(kThreads) k_quant_send(DevPlan p) {
+    if (p.step_ptr) p.step = *p.step_ptr;
     const ChunkRec c = p.chunks[blockIdx.x];
     const TensorRec t = p.tensors[c.tensor];
     const GroupCfg cfg = p.gcfg[t.group];
@@ -811,6 +830,7 @@ __global__ void __launch_bounds__(kThreads) k_quant_send(DevPlan p) {
 
 template <typename GradT, typename OutT>
 __global__ void __launch_bounds__(kThreads) k_recv_dense(DevPlan p) {
+    if (p.step_ptr) p.step = *p.step_ptr;
     const ChunkRec c = p.chunks[blockIdx.x];
     const TensorRec t = p.tensors[c.tensor];
     const int tid = threadIdx.x;
@@ -858,6 +878,17 @@ __global__ void __launch_bounds__(kThreads) k_recv_dense(DevPlan p) {
         for (int k = 0; k < 4; ++k) sum[k] *= inv;
         store_quad<OutT>(o, j, c.len, ov, sum);
     }
+    if (p.step_ptr) {      // the last CTA to finish advances the device-side step counter
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            const unsigned ticket = atomicAdd(&p.counters->done_recv, 1u);
+            if (ticket == gridDim.x - 1) {
+                p.counters->done_recv = 0;
+                __threadfence();
+                *p.step_ptr = p.step + 1;
+            }
+        }
+    }
 }
 
 }  // namespace lwc
@@ -877,6 +908,8 @@ extern "C" int lwc_set_flag_timeout_ms(unsigned int ms) {
 
 struct LwcPlan {
     DevPlan dev;
+    bool device_step = false;
+    void* h_pinned = nullptr;      // pinned staging of the tensor table (graph-capturable uploads)
     int num_tensors;
     int grad_dtype, out_dtype;
     bool any_resid;
@@ -1006,6 +1039,7 @@ extern "C" int lwc_plan_destroy(LwcPlan* P) {
     if (!P) return 0;
     cudaFree(P->d_tensors); cudaFree(P->d_chunks); cudaFree(P->d_gcfg); cudaFree(P->d_gstate);
     cudaFree(P->d_chunk_cnt); cudaFree(P->d_chunk_off); cudaFree(P->d_chunk_part); cudaFree(P->d_counters);
+    if (P->h_pinned) cudaFreeHost(P->h_pinned);
     delete P;
     return 0;
 }
@@ -1055,6 +1089,7 @@ extern "C" int lwc_plan_send(LwcPlan* P, uint64_t step, void* stream_) {
     cudaStream_t st = (cudaStream_t)stream_;
     DevPlan D = P->dev;
     D.step = step;
+    D.step_ptr = P->device_step ? &reinterpret_cast<Counters*>(P->d_counters)->dev_step : nullptr;
     D.timeout_ns = g_flag_timeout_ns;
     const int NC = D.num_chunks, G = D.num_groups, m = D.method;
     LWC_CUDA_CHECK(cudaMemsetAsync(P->d_gstate, 0, P->state_bytes, st));
@@ -1112,6 +1147,7 @@ extern "C" int lwc_plan_recv(LwcPlan* P, uint64_t step, void* stream_) {
     cudaStream_t st = (cudaStream_t)stream_;
     DevPlan D = P->dev;
     D.step = step;
+    D.step_ptr = P->device_step ? &reinterpret_cast<Counters*>(P->d_counters)->dev_step : nullptr;
     D.timeout_ns = g_flag_timeout_ns;
     const int m = D.method;
     if (m >= LWC_TOPK && m <= LWC_ADAPTIVE) {
@@ -1420,7 +1456,30 @@ extern "C" int lwc_plan_update_grads(LwcPlan* P, const void* const* grad_dev, vo
         if (!grad_dev[t]) return LWC_EINVAL;
         P->h_tensors[t].grad = grad_dev[t];
     }
-    LWC_CUDA_CHECK(cudaMemcpyAsync(P->d_tensors, P->h_tensors.data(), sizeof(TensorRec) * P->h_tensors.size(),
-                                   cudaMemcpyHostToDevice, (cudaStream_t)stream));
+    const size_t bytes = sizeof(TensorRec) * P->h_tensors.size();
+    cudaStream_t st = (cudaStream_t)stream;
+    cudaStreamCaptureStatus cap = cudaStreamCaptureStatusNone;
+    cudaStreamIsCapturing(st, &cap);
+    if (cap != cudaStreamCaptureStatusNone) {
+        // inside a CUDA-graph capture the source must outlive the graph: stage in pinned memory owned by the plan
+        // (every replay re-uploads the same table, which is what the captured kernels expect)
+        if (!P->h_pinned) return LWC_ESTATE;       // lwc_plan_use_device_step() provides it before any capture
+        memcpy(P->h_pinned, P->h_tensors.data(), bytes);
+        LWC_CUDA_CHECK(cudaMemcpyAsync(P->d_tensors, P->h_pinned, bytes, cudaMemcpyHostToDevice, st));
+    } else {
+        LWC_CUDA_CHECK(cudaMemcpyAsync(P->d_tensors, P->h_tensors.data(), bytes, cudaMemcpyHostToDevice, st));
+    }
+    return 0;
+}
+
+// Graph-safe mode: the step counter lives on the device (kernels read it at start, the receiver bumps it), so a
+// captured send/recv sequence can be replayed; `step` arguments are then ignored.  Call outside any capture.
+extern "C" int lwc_plan_use_device_step(LwcPlan* P, int enable, uint64_t start_step) {
+    if (!P) return LWC_EINVAL;
+    if (enable && !P->h_pinned) LWC_CUDA_CHECK(cudaMallocHost(&P->h_pinned, sizeof(TensorRec) * P->h_tensors.size()));
+    Counters* c = reinterpret_cast<Counters*>(P->d_counters);
+    const unsigned long long v = start_step;
+    LWC_CUDA_CHECK(cudaMemcpy(&c->dev_step, &v, sizeof(v), cudaMemcpyHostToDevice));
+    P->device_step = enable != 0;
     return 0;
 }

@@ -602,7 +602,15 @@ extern "C" int lwc_gemm_bf16(const void* A, const void* B, void* C, int M, int N
     if (splits > 1 && !ws) LWC_GEMM_FAIL("split-K needs a workspace");
     // cuTensorMapEncodeTiled is a driver-API call and needs a current context on THIS thread; autograd's
     // worker threads may not have touched the runtime yet (CUDA_ERROR_INVALID_CONTEXT otherwise).
-    cudaFree(0);
+    {
+        CUcontext ctx = nullptr;
+        if (cuCtxGetCurrent(&ctx) != CUDA_SUCCESS || !ctx) {      // no sync, no allocation: safe inside graph capture
+            int dev = 0;
+            cudaGetDevice(&dev);
+            CUcontext prim = nullptr;
+            if (cuDevicePrimaryCtxRetain(&prim, dev) == CUDA_SUCCESS) cuCtxSetCurrent(prim);
+        }
+    }
     cudaStream_t st = (cudaStream_t)stream;
     static int force_1cta = -1;
     if (force_1cta < 0) { const char* e = getenv("LWC_GEMM_1CTA"); force_1cta = (e && e[0] == '1') ? 1 : 0; }

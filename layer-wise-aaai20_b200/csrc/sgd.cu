@@ -27,6 +27,7 @@ __global__ void __launch_bounds__(kThreads) k_sgd(const LwcSgdTensor* __restrict
     ModelT* md = t.model ? reinterpret_cast<ModelT*>(t.model) + c.start : nullptr;
     const bool wv = vec_ok(w), gv = vec_ok(g), mv = m && vec_ok(m), dv = md && vec_ok(md);
     const int tid = threadIdx.x;
+    const float lr = d.lr_dev ? *d.lr_dev : d.lr;      // device-resident learning rate: replayable in a CUDA graph
 #pragma unroll 2
     for (int it = 0; it < kQuadsPerThread; ++it) {
         const int j = (it * kThreads + tid) * 4;
@@ -42,7 +43,7 @@ __global__ void __launch_bounds__(kThreads) k_sgd(const LwcSgdTensor* __restrict
                 mq[k] = d.first_step ? dd : fmaf(d.momentum, mq[k], (1.0f - d.dampening) * dd);
                 dd = d.nesterov ? fmaf(d.momentum, mq[k], dd) : mq[k];
             }
-            wq[k] = fmaf(-d.lr, dd, wq[k]);
+            wq[k] = fmaf(-lr, dd, wq[k]);
         }
         store_quad<float>(w, j, c.len, wv, wq);
         if (m) store_quad<float>(m, j, c.len, mv, mq);

@@ -42,10 +42,29 @@ class FusedSGD(torch.optim.SGD):
                 if model is not master:
                     self._model_copy[id(master)] = model
         self._plans = {}
+        self._lr_dev = None          # graph-safe mode: one device scalar per param group
+        self._lr_dev_val = {}
 
     def set_lr(self, lr: float):
         for g in self.param_groups:
             g["lr"] = lr
+
+    def enable_device_lr(self, device):
+        """Keep each group's learning rate in device memory (read by the kernel) so that a captured step can be
+        replayed with a changing schedule; ``sync_device_lr`` uploads the values that changed."""
+        if self._lr_dev is None:
+            self._lr_dev = {gi: torch.zeros(1, dtype=torch.float32, device=device)
+                            for gi in range(len(self.param_groups))}
+        self.sync_device_lr()
+
+    def sync_device_lr(self):
+        if self._lr_dev is None:
+            return
+        for gi, g in enumerate(self.param_groups):
+            lr = float(g["lr"])
+            if self._lr_dev_val.get(gi) != lr:
+                self._lr_dev[gi].fill_(lr)
+                self._lr_dev_val[gi] = lr
 
     def _native(self, p) -> bool:
         if not p.is_cuda:

@@ -77,6 +77,11 @@ def step_group(opt, gi, group, params):
         d.lr, d.momentum, d.dampening = float(group["lr"]), float(mu), float(group["dampening"])
         d.weight_decay, d.grad_scale = float(group["weight_decay"]), float(opt.grad_scale)
         d.nesterov, d.first_step = int(bool(group["nesterov"])), int(first)
+        lr_dev = opt._lr_dev.get(gi) if opt._lr_dev is not None else None
+        if lr_dev is not None:               # graph-safe: the kernel reads the learning rate from device memory
+            if not torch.cuda.is_current_stream_capturing():
+                opt.sync_device_lr()
+            d.lr_dev = lr_dev.data_ptr()
         st = torch.cuda.current_stream().cuda_stream
         abi.check(lib.lwc_sgd_step(plan.handle, C.byref(d), C.c_void_p(st)), "lwc_sgd_step")
         _native.counters.add(1)

@@ -128,6 +128,12 @@ class ExchangePlan:
         st = (stream or torch.cuda.current_stream()).cuda_stream
         abi.check(self.lib.lwc_plan_update_grads(self.handle, _ptr_array(ptrs), C.c_void_p(st)), "lwc_plan_update_grads")
 
+    def use_device_step(self, enable: bool, start_step: int):
+        """Keep the step counter on the device (kernels read it, the receiver bumps it) so that a captured
+        send/recv sequence can be replayed by a CUDA graph.  The caller synchronises the device first."""
+        abi.check(self.lib.lwc_plan_use_device_step(self.handle, int(bool(enable)), C.c_uint64(start_step)),
+                  "lwc_plan_use_device_step")
+
     def send(self, step: int, stream=None):
         st = (stream or torch.cuda.current_stream()).cuda_stream
         abi.check(self.lib.lwc_plan_send(self.handle, C.c_uint64(step), C.c_void_p(st)), "lwc_plan_send")
@@ -196,6 +202,7 @@ class FusedEngine:
             raise ValueError(f"fused engine supports up to {abi.LWC_MAX_WORLD} ranks per node")
         self.device = params[0].device
         self.step = 0
+        self.graph_mode = False
         self.overlap = overlap
         dts = {p.dtype for p in params}
         self.entire = cfg.compress == "entiremodel"
@@ -351,6 +358,24 @@ class FusedEngine:
             b.ptrs = ptrs
         b.plan.send(self.step, stream)
 
+    def enable_graph_mode(self):
+        """Make send/recv replayable by a CUDA graph: from here on the step counter of every plan lives on the
+        device (``self.step`` stays a host mirror, advanced by :meth:`note_replay`).  Collective across ranks in
+        the sense that every rank must switch at the same step.  One live graph per engine: a later capture
+        reuses each plan's pinned pointer-table staging."""
+        if self.graph_mode:
+            return
+        torch.cuda.synchronize(self.device)
+        for b in self.buckets:
+            b.plan.use_device_step(True, self.step)
+        self.graph_mode = True
+
+    def note_replay(self, n: int = 1):
+        """A captured step was replayed ``n`` times: advance the host mirror of the step counter."""
+        self.step += n
+        for b in self.buckets:
+            b.ptrs = None            # the replay re-uploaded ITS pointer table: the next eager step must upload again
+
     def _repoint(self):
         """After the receivers are queued: every ``p.grad`` is the arena view holding the average."""
         for p, v in zip(self.params, self._shaped_views):
@@ -443,6 +468,10 @@ class FusedEngine:
     def load_state_dict(self, sd):
         # the step counter also keys the peer flags: never move it backwards on a live engine
         self.step = max(self.step, int(sd.get("step", 0)))
+        if self.graph_mode:
+            torch.cuda.synchronize(self.device)
+            for b in self.buckets:
+                b.plan.use_device_step(True, self.step)
         res = sd.get("residual")
         if res is not None and self.resid_views is not None:
             if isinstance(res, torch.Tensor):      # entire-model flat residual from the torch engine

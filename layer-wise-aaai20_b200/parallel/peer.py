@@ -68,6 +68,13 @@ class DeviceBuffer:
         abi.check(_native.lib().lwc_ipc_get_handle(C.c_void_p(self.ptr), buf), "lwc_ipc_get_handle")
         return bytes(buf.raw)
 
+    def ipc_offset(self) -> int:
+        """Offset of this buffer inside the driver allocation its IPC handle names (small ``cudaMalloc`` requests
+        can share one block; the importer gets the block's base)."""
+        off = C.c_uint64()
+        abi.check(_native.lib().lwc_ipc_base_offset(C.c_void_p(self.ptr), C.byref(off)), "lwc_ipc_base_offset")
+        return int(off.value)
+
     def free(self):
         if self.owner and self.ptr:
             _native.lib().lwc_free(C.c_void_p(self.ptr))
@@ -86,21 +93,22 @@ class PeerHeap:
         self._symm = None
         if multicast and self.world > 1 and self._init_symmetric(device):
             return
-        self.local = DeviceBuffer.allocate(self.nbytes, device)
+        # whole 2 MiB pages: the heap gets driver blocks of its own (and maps with large pages on the peers)
+        self.local = DeviceBuffer.allocate((self.nbytes + (2 << 20) - 1) // (2 << 20) * (2 << 20), device)
         self.ptrs: List[int] = [0] * self.world
         self.ptrs[self.rank] = self.local.ptr
         self._opened: List[int] = []
         if self.world > 1:
-            handles: List[Optional[bytes]] = [None] * self.world
-            dist.all_gather_object(handles, (self.local.ipc_handle(), self.local.device.index), group=group)
+            handles: List[Optional[tuple]] = [None] * self.world
+            dist.all_gather_object(handles, (self.local.ipc_handle(), self.local.ipc_offset()), group=group)
             lib = _native.lib()
-            for r, (h, dev_index) in enumerate(handles):
+            for r, (h, offset) in enumerate(handles):
                 if r == self.rank:
                     continue
                 out = C.c_void_p()
                 abi.check(lib.lwc_ipc_open_handle(C.create_string_buffer(h, 64), C.byref(out)),
                           f"lwc_ipc_open_handle(rank {r})")
-                self.ptrs[r] = out.value
+                self.ptrs[r] = out.value + offset       # the handle maps the exporter's whole block
                 self._opened.append(out.value)
             dist.barrier(group=group)
 

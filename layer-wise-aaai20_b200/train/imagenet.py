@@ -94,7 +94,8 @@ class Trainer:
                  weight_decay: float = 1e-4, init_bn0: bool = True, no_bn_wd: bool = True,
                  loss_scale: float = 1.0, lr: float = 0.0, device=None, overlap: bool = True,
                  engine: str = "auto", channels_last: bool = True, model: Optional[nn.Module] = None,
-                 wrapper: Optional[str] = None, randk: float = 1.0, seed: int = 2147483647):
+                 wrapper: Optional[str] = None, randk: float = 1.0, seed: int = 2147483647,
+                 cuda_graph: bool = False):
         self.device = torch.device(device or ("cuda" if torch.cuda.is_available() else "cpu"))
         if self.device.type == "cuda":
             torch.backends.cudnn.benchmark = True     # as the reference does (train_imagenet_nv.py:95): autotune conv algos
@@ -142,6 +143,11 @@ class Trainer:
                                   nesterov=momentum > 0, grad_scale=1.0 / self.loss_scale,
                                   model_params=self._model_in_group_order(groups))
         self.steps = 0
+        self._graph = None
+        # cuda_graph=True: after 3 eager steps with one batch shape, capture the step for that shape and replay it
+        self.cuda_graph = bool(cuda_graph) and self.device.type == "cuda" and self.wrapper is None \
+            and hasattr(self.exchanger.engine, "enable_graph_mode")
+        self._shape_key, self._shape_run = None, 0
 
     def _model_in_group_order(self, groups):
         by_master = {id(m): p for m, p in zip(self.master_params, self.model_params)}
@@ -154,10 +160,80 @@ class Trainer:
         (loss * self.loss_scale if self.loss_scale != 1.0 else loss).backward()
         return out, loss
 
+    # ---- whole-step CUDA graph (opt-in) ---------------------------------------------------------------------
+    def capture_graph(self, images: torch.Tensor, target: torch.Tensor, warmup: int = 3):
+        """Capture ``normalise -> forward -> backward -> compress/exchange -> SGD`` for this batch shape into ONE
+        CUDA graph; later ``train_step`` calls with the same shape copy the batch into static buffers and replay
+        it (one launch instead of ~1.5k).  Needs the fused engine: its step counter and the learning rate move to
+        device memory so the replay sees them change.  ``warmup`` eager steps run first (cuDNN autotuning,
+        momentum buffers, lazily created plans); they are real optimisation steps on the given batch (pass 0 when
+        eager steps of this shape have already run -- capturing itself executes nothing).  In a
+        multi-rank job every rank must capture at the same step.  Returned logits / loss are static tensors that
+        the next replay overwrites."""
+        eng = self.exchanger.engine
+        if self.device.type != "cuda" or self.wrapper is not None or not hasattr(eng, "enable_graph_mode"):
+            raise RuntimeError("capture_graph needs a CUDA device and the fused exchange engine")
+        from .. import _native
+        self._graph = None
+        self._g_images = images.to(self.device, copy=True)
+        self._g_target = target.to(self.device, copy=True)
+        eng.enable_graph_mode()
+        self.optimizer.enable_device_lr(self.device)
+        self.net.train()
+        self.normalize.train()
+        side = torch.cuda.Stream(device=self.device)
+        side.wait_stream(torch.cuda.current_stream())
+        with torch.cuda.stream(side):
+            for _ in range(warmup):
+                self._step_body(self._g_images, self._g_target)
+        torch.cuda.current_stream().wait_stream(side)
+        torch.cuda.synchronize(self.device)
+        graph = torch.cuda.CUDAGraph()
+        n0, step0 = _native.counters.kernels, eng.step
+        with torch.cuda.graph(graph, capture_error_mode="thread_local"):
+            self._g_out = self._step_body(self._g_images, self._g_target)
+        self._graph_launches = _native.counters.kernels - n0
+        _native.counters.add(-self._graph_launches)      # nothing ran during capture
+        eng.step = step0
+        self.steps -= 1
+        self._graph = graph
+        return graph
+
+    def _replay(self, images, target):
+        self._g_images.copy_(images, non_blocking=True)
+        self._g_target.copy_(target, non_blocking=True)
+        self.optimizer.sync_device_lr()
+        self._graph.replay()
+        from .. import _native
+        _native.counters.add(self._graph_launches)
+        self.exchanger.engine.note_replay()
+        self.steps += 1
+        return self._g_out
+
+    def _step_body(self, images, target):
+        x = self.normalize(images) if images.dtype == torch.uint8 else images
+        out, loss = self.forward_backward(x, target)
+        self.exchanger.exchange()
+        self._attach_master_grads()
+        self.optimizer.step()
+        self.zero_grad()
+        self.steps += 1
+        return out, loss
+
     def train_step(self, images: torch.Tensor, target: torch.Tensor):
         """``images``: uint8 NCHW (host pinned or device) or already-normalised float; returns (logits, loss)."""
         self.net.train()
         self.normalize.train()
+        if (self._graph is not None and images.shape == self._g_images.shape
+                and images.dtype == self._g_images.dtype):
+            return self._replay(images, target)
+        if self.cuda_graph:
+            key = (tuple(images.shape), images.dtype)
+            self._shape_run = self._shape_run + 1 if key == self._shape_key else 1
+            self._shape_key = key
+            if self._shape_run > 3:
+                self.capture_graph(images, target, warmup=0)
+                return self._replay(images, target)
         if images.device != self.device:
             images = images.to(self.device, non_blocking=True)
             target = target.to(self.device, non_blocking=True)

@@ -67,6 +67,8 @@ def get_parser():
     p.add_argument("--arch", default="resnet50")
     p.add_argument("--engine", default="auto")
     p.add_argument("--no-overlap", action="store_true")
+    p.add_argument("--cuda-graph", action="store_true",
+                   help="replay the whole train step of each phase's batch shape as one CUDA graph (fused engine)")
     p.add_argument("--synthetic", type=int, default=0, help="N synthetic training images instead of a dataset")
     p.add_argument("--epochs", type=int, default=None, help="stop after this many epochs")
     return p
@@ -170,6 +172,7 @@ def main(argv=None):
     trainer = Trainer(arch=args.arch, dtype=dtype, cfg=cfg, momentum=args.momentum, weight_decay=args.weight_decay,
                       init_bn0=args.init_bn0, no_bn_wd=args.no_bn_wd, loss_scale=args.loss_scale, device=device,
                       overlap=not args.no_overlap, engine=args.engine, wrapper=wrapper, randk=args.randk,
+                      cuda_graph=args.cuda_graph,
                       seed=args.seed)
     best_top5 = 93.0     # only checkpoint "best" models above 93 % top-5 (reference :175)
     if args.resume:

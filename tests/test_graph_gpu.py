@@ -1,0 +1,111 @@
+"""Whole-step CUDA-graph replay must reproduce the eager step sequence (device-side step counter + learning rate)."""
+import pytest
+import torch
+
+import layerwise_b200  # noqa: F401
+
+pytestmark = pytest.mark.gpu
+
+
+class _MLP(torch.nn.Module):
+    """GEMM-only network (deterministic kernels) fed with an image-shaped batch."""
+
+    def __init__(self, d_in, hidden, classes):
+        super().__init__()
+        from layerwise_b200.ops import nn as lnn
+        self.f1 = lnn.Linear(d_in, hidden)
+        self.f2 = lnn.Linear(hidden, hidden)
+        self.f3 = lnn.Linear(hidden, classes)
+
+    def forward(self, x):
+        x = x.flatten(1)
+        return self.f3(torch.relu(self.f2(torch.relu(self.f1(x)))))
+
+
+def _trainer(method, ratio):
+    from layerwise_b200.parallel.exchange import CompressionConfig
+    from layerwise_b200.train.imagenet import Trainer
+    torch.manual_seed(0)
+    cfg = CompressionConfig(compress="layerwise", method=method, ratio=ratio, error_feedback=True)
+    return Trainer(model=_MLP(3 * 16 * 16, 256, 16), dtype="bf16", cfg=cfg, lr=0.01, momentum=0.9, weight_decay=1e-4,
+                   device="cuda:0", overlap=True, engine="fused", no_bn_wd=False)
+
+
+def _batches(n):
+    g = torch.Generator().manual_seed(3)
+    return [(torch.randint(0, 256, (64, 3, 16, 16), dtype=torch.uint8, generator=g).cuda(),
+             torch.randint(0, 16, (64,), generator=g).cuda()) for _ in range(n)]
+
+
+@pytest.mark.parametrize("method,ratio", [("Topk", 0.05), ("Randomk", 0.1), ("TernGrad", 1.0)])
+def test_graph_replay_matches_eager(method, ratio):
+    data = _batches(6)
+    lrs = [0.01, 0.01, 0.01, 0.02, 0.005, 0.01, 0.03, 0.01]
+    # eager: 3 steps on batch 0 (what capture_graph's warm-up does), then batches 1..5 with a changing lr
+    a = _trainer(method, ratio)
+    la = []
+    for i in range(3):
+        a.optimizer.set_lr(lrs[i])
+        a.train_step(*data[0])
+    for i in range(1, 6):
+        a.optimizer.set_lr(lrs[2 + i])
+        la.append(float(a.train_step(*data[i])[1].detach()))
+    # graph: capture on batch 0, replay batches 1..5
+    b = _trainer(method, ratio)
+    b.optimizer.set_lr(lrs[0])
+    b.capture_graph(*data[0], warmup=3)
+    lb = []
+    for i in range(1, 6):
+        b.optimizer.set_lr(lrs[2 + i])
+        lb.append(float(b.train_step(*data[i])[1].detach()))
+    # an eager step with another batch shape next to the live graph, then a replay again
+    half = (data[0][0][:32].contiguous(), data[0][1][:32].contiguous())
+    for t in (a, b):
+        t.train_step(*half)
+        la.append(float(t.train_step(*data[2])[1])) if t is a else lb.append(float(t.train_step(*data[2])[1]))
+    torch.cuda.synchronize()
+    assert b._graph is not None and b._graph_launches > 0
+    assert a.exchanger.engine.step == b.exchanger.engine.step == 10
+    assert a.steps == b.steps == 10
+    assert b.exchanger.engine.stats()["timeouts"] == 0
+    assert la == pytest.approx(lb, rel=1e-5, abs=1e-6), (la, lb)
+    for pa, pb in zip(a.master_params, b.master_params):
+        assert torch.equal(pa, pb)
+
+
+def test_graph_replay_resnet_learns():
+    from layerwise_b200.parallel.exchange import CompressionConfig
+    from layerwise_b200.train.imagenet import Trainer
+    torch.manual_seed(0)
+    cfg = CompressionConfig(compress="layerwise", method="Topk", ratio=0.1, error_feedback=True)
+    tr = Trainer(arch="resnet50", num_classes=16, dtype="bf16", cfg=cfg, lr=0.02, momentum=0.9, weight_decay=1e-4,
+                 device="cuda:0", overlap=True, init_bn0=False)
+    g = torch.Generator().manual_seed(1)
+    x = torch.randint(0, 256, (32, 3, 64, 64), dtype=torch.uint8, generator=g).cuda()
+    y = torch.randint(0, 16, (32,), generator=g).cuda()
+    first = float(tr.train_step(x, y)[1])
+    tr.capture_graph(x, y, warmup=3)
+    losses = [float(tr.train_step(x, y)[1]) for _ in range(56)]
+    assert all(l == l for l in losses)
+    assert losses[-1] < 0.7 * first, (first, losses[::8])
+    assert tr.exchanger.engine.stats()["timeouts"] == 0
+
+
+def test_auto_graph_mode_matches_eager():
+    """Trainer(cuda_graph=True): three eager steps per batch shape, then capture + replay, transparently."""
+    data = _batches(7)
+    half = (data[0][0][:32].contiguous(), data[0][1][:32].contiguous())
+    seq = [data[0], data[1], data[2], data[3], data[4], half, data[5], data[6]]
+    a = _trainer("Topk", 0.05)
+    b = _trainer("Topk", 0.05)
+    b.cuda_graph = True
+    la, lb = [], []
+    for i, (x, y) in enumerate(seq):
+        for t, out in ((a, la), (b, lb)):
+            t.optimizer.set_lr(0.01 * (1 + i % 3))
+            out.append(float(t.train_step(x, y)[1].detach()))
+    torch.cuda.synchronize()
+    assert b._graph is not None and a._graph is None
+    assert la == pytest.approx(lb, rel=1e-5, abs=1e-6), (la, lb)
+    for pa, pb in zip(a.master_params, b.master_params):
+        assert torch.equal(pa, pb)

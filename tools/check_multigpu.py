@@ -86,6 +86,24 @@ def main():
             results[name] = {"nvls": bool(getattr(ex.engine, "nvls", False)), "ok": bool(flag.item()), "ms_per_exchange": round(float(ms.item()), 4), "stats": st}
             ok = ok and bool(flag.item())
             ex.engine.close()
+    # two small heaps alive at once: the driver may carve them out of one block, whose IPC handle maps the BLOCK --
+    # every rank writes a tag into its neighbour's copy of each heap and each must land in the right one
+    from layerwise_b200.parallel.peer import DeviceBuffer, PeerHeap
+    heaps = [PeerHeap(4096), PeerHeap(4096)]
+    dev = torch.device("cuda", local)
+    for k, h in enumerate(heaps):
+        DeviceBuffer(h.ptrs[(rank + 1) % world], 4096, dev, False).view(torch.int32, 1024).fill_(100 * rank + k + 1)
+    torch.cuda.synchronize()
+    dist.barrier(device_ids=[local])
+    good = all(bool((h.local.view(torch.int32, 1024) == 100 * ((rank - 1) % world) + k + 1).all().item())
+               for k, h in enumerate(heaps))
+    flag = torch.tensor([1.0 if good else 0.0], device="cuda")
+    dist.all_reduce(flag, op=dist.ReduceOp.MIN)
+    results["two_small_heaps"] = {"ok": bool(flag.item())}
+    ok = ok and bool(flag.item())
+    dist.barrier(device_ids=[local])
+    for h in heaps:
+        h.close()
     if rank == 0:
         print(json.dumps({"world": world, "ok": ok, "numel": sum(sizes), "results": results}, indent=1))
     dist.destroy_process_group()
