@@ -246,6 +246,7 @@ def main():
         dtype, par = args.ref_dtype, f"dp{world}"
     else:
         tr = build_ours(args, world, rank)
+        args.graph = args.graph and hasattr(tr.exchanger.engine, "enable_graph_mode")
         if args.graph:
             tr.capture_graph(dev_x[0], dev_y[0], warmup=3)
         step_dev = lambda i: tr.train_step(dev_x[i % nbuf], dev_y[i % nbuf])[1]     # noqa: E731
