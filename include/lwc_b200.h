@@ -107,15 +107,7 @@ int lwc_plan_set_random(LwcPlan* plan, const void* const* rand_dev);
  * store into every rank's slot, release flags.  step must increase by 1 per call. */
 int lwc_plan_send(LwcPlan* plan, uint64_t step, void* stream);
 /* Receiver side: acquire the flags of step, scatter-add / dequantise all sources in rank
- * order, scale by 1/world, write out_dev[].  With sgd != NULL the averaged gradient is
- * consumed by a fused SGD update instead (see LwcSgdArgs). */
-typedef struct {
-    float lr, momentum, dampening, weight_decay, grad_scale;
-    int32_t nesterov, first_step;
-    void* const*  param_dev;      /* fp32 master weights per tensor */
-    void* const*  mom_dev;        /* fp32 momentum buffers per tensor (or NULL when momentum==0) */
-    void* const*  model_dev;      /* optional low-precision copies (out_dtype), NULL entries allowed */
-} LwcSgdArgs;
+ * order, scale by 1/world, write out_dev[].  The optimiser step is a separate launch (lwc_sgd_step). */
 int lwc_plan_recv(LwcPlan* plan, uint64_t step, void* stream);
 /* counters: [0]=entries sent last step, [1]=entries dropped by capacity clamp,
  * [2]=flag wait timeouts, [3]=payload bytes stored per destination */
@@ -214,6 +206,20 @@ int lwc_bn_forward(const void* x, void* y, const void* res, const float* gamma, 
 int lwc_bn_backward(const void* dy, const void* x, const void* y, void* dx, void* dres, const float* gamma,
                     const float* beta, const float* mean, const float* invstd, float* dgamma, float* dbeta,
                     float* workspace, long long M, int C, int dtype, int relu, void* stream);
+
+/* Persistent tcgen05 implicit-GEMM convolution, bf16 NHWC, stride 1, kh in {1, 3} ("same" padding), Cin % 64 == 0,
+ * Cout % 64 == 0 (stands in for the cuDNN convolutions under IMAGENET/training/resnet.py:28-31 and
+ * CIFAR10/dawn.py:34-41).  wt is [Cout][kh*kh][Cin] (b_mn = 0) or, for 1x1 data gradients, the forward weight
+ * [Cin_fwd][Cout_fwd] read MN-major (b_mn = 1).  bias (fp32 per Cout) and relu are optional epilogue stages;
+ * stats, when non-NULL, receives per-M-tile partial batch-norm sums: [tiles_m][2][Cout] floats with tiles_m from
+ * lwc_conv_tiles_m (which also reports the rows covered by one tile). */
+int lwc_conv_tiles_m(int Nimg, int H, int W, int kh, int* rows_per_tile_out);
+int lwc_conv_forward(const void* x, const void* wt, void* y, int Nimg, int H, int W, int Cin, int Cout, int kh,
+                     int b_mn, const float* bias, int relu, float* stats, void* stream);
+/* 1x1 only: Y = conv(X) + addend (bf16, shape of Y), the addend tile prefetched by TMA: the data gradient at a
+ * residual fork, dX = dY * W + d_identity, in one kernel. */
+int lwc_conv1x1_add(const void* x, const void* wt, const void* addend, void* y, int Nimg, int H, int W, int Cin,
+                    int Cout, int b_mn, void* stream);
 
 /* Max pooling, NHWC, byte argmax forward + gather backward (CIFAR10/dawn.py:51,:70; resnet.py:104). */
 int lwc_maxpool_forward(const void* x, void* y, void* idx, int N, int H, int W, int C, int k, int stride,
