@@ -1,7 +1,7 @@
 // Fused batch normalisation for channels-last activations ([M = N*H*W, C] row-major).
 //
 // Training forward : k_bn_stats (per-block partial sum / sum-of-squares, fp32)
-//                    k_bn_finalize (deterministic Chan combination in double -> mean, invstd,
+//                    k_bn_finalize (deterministic Chan combination of the partials -> mean, invstd,
 //                                   running-stat update)
 //                    k_bn_apply   y = relu?( (x-mean)*invstd*gamma + beta (+ residual) )
 // Training backward: k_bn_bwd_reduce (sum dy', sum dy'*xhat with dy' = dy * [y > 0] when ReLU is fused)
@@ -221,61 +221,81 @@ __global__ void __launch_bounds__(THREADS) k_bn_stats(Params p) {
     }
 }
 
-// ---- forward: combine partials (one warp per channel, fixed-order -> deterministic) -------------------
-__device__ __forceinline__ double warp_sum_d(double v) {
+// ---- forward: combine partials (fixed order -> deterministic) ------------------------------------------
+constexpr int MAX_PART_PER_LANE = 20;     // plan_grid keeps nblk <= 32 * 20
+constexpr int FIN_THREADS = 256;
+
+// A CTA finalises 8 adjacent channels.  Lane = (partial row r = lane / 8, channel = lane % 8): a warp load reads
+// four full 32-byte sectors of the [nblk][2][C] partial array (a warp-per-channel mapping touches a different
+// sector per lane and fetches every sector eight times).  Thread (warp w, row r) owns partials b = 4 w + r (mod 32);
+// its <= 40 loads are independent.  Everything is fp32 and index arithmetic 32-bit: with one CTA per 8 channels the
+// kernel is a short dependent chain, and ncu showed the earlier fp64 / 64-bit version issue-bound (1.4 k
+// instructions per warp, 13 us for C = 256).
+__device__ __forceinline__ float fin_reduce(float (*sh)[8], int w, int lane, float v) {
+    v += __shfl_xor_sync(0xffffffffu, v, 8);
+    v += __shfl_xor_sync(0xffffffffu, v, 16);
+    __syncthreads();
+    if (lane < 8) sh[w][lane] = v;
+    __syncthreads();
+    float t = 0.0f;
 #pragma unroll
-    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
-    return v;
+    for (int k = 0; k < 8; ++k) t += sh[k][lane & 7];
+    return t;
 }
 
-constexpr int MAX_PART_PER_LANE = 20;     // plan_grid keeps nblk <= 32 * 20
+template <int N>
+__device__ __forceinline__ float tree_sum(const float (&v)[N]) {
+    float t[4] = {0.0f, 0.0f, 0.0f, 0.0f};
+#pragma unroll
+    for (int i = 0; i < N; ++i) t[i & 3] += v[i];
+    return (t[0] + t[1]) + (t[2] + t[3]);
+}
 
-// All partials of a channel are fetched up front (<= 20 independent loads per lane), so the kernel pays
-// the memory latency once instead of once per loop iteration.
-__global__ void __launch_bounds__(256) k_bn_finalize(Params p) {
-    const int c = blockIdx.x * 8 + (threadIdx.x >> 5);
-    const int l = threadIdx.x & 31;
-    if (c >= p.C) return;
-    const float* part = p.partial + c;
-    const size_t stride = (size_t)2 * p.C;
+__device__ __forceinline__ void fin_load(const Params& p, int b0, int c, float (&sv)[MAX_PART_PER_LANE],
+                                         float (&qv)[MAX_PART_PER_LANE]) {
+    const int stride = 2 * p.C;
+    const float* part = p.partial + c + b0 * stride;
+#pragma unroll
+    for (int i = 0; i < MAX_PART_PER_LANE; ++i) {
+        const bool ok = b0 + 32 * i < p.nblk;
+        sv[i] = ok ? part[i * 32 * stride] : 0.0f;
+        qv[i] = ok ? part[i * 32 * stride + p.C] : 0.0f;
+    }
+}
+
+__global__ void __launch_bounds__(FIN_THREADS) k_bn_finalize(Params p) {
+    __shared__ float sh[8][8];
+    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+    const int c = blockIdx.x * 8 + (lane & 7);          // C % 8 == 0: always a live channel
+    const int b0 = w * 4 + (lane >> 3);
     float sv[MAX_PART_PER_LANE], qv[MAX_PART_PER_LANE];
-#pragma unroll
-    for (int i = 0; i < MAX_PART_PER_LANE; ++i) {
-        const int b = l + 32 * i;
-        sv[i] = b < p.nblk ? part[(size_t)b * stride] : 0.0f;
-        qv[i] = b < p.nblk ? part[(size_t)b * stride + p.C] : 0.0f;
-    }
-    double s = 0.0;
-#pragma unroll
-    for (int i = 0; i < MAX_PART_PER_LANE; ++i) s += (double)sv[i];
-    s = warp_sum_d(s);
-    const double n = (double)p.M;
-    const double mean = s / n;
+    fin_load(p, b0, c, sv, qv);
+    const float s = fin_reduce(sh, w, lane, tree_sum(sv));
+    const float n = (float)p.M;
+    const float mean = s / n;
     // M2 = sum_b [ M2_b + n_b * (mean_b - mean)^2 ]   (Chan's combination against the global mean)
-    double m2 = 0.0;
-    const float fmean = (float)mean;
+    const float n_full = (float)p.rows_per_blk, n_last = (float)(p.M - (long long)(p.nblk - 1) * p.rows_per_blk);
+    const float i_full = 1.0f / n_full, i_last = 1.0f / n_last;
+    float m2v[MAX_PART_PER_LANE];
 #pragma unroll
     for (int i = 0; i < MAX_PART_PER_LANE; ++i) {
-        const int b = l + 32 * i;
-        if (b < p.nblk) {
-            long long r0 = (long long)b * p.rows_per_blk, r1 = r0 + p.rows_per_blk;
-            if (r1 > p.M) r1 = p.M;
-            const float nb = (float)(r1 - r0);
-            const float mb = sv[i] / nb;
-            const float m2b = fmaxf(qv[i] - sv[i] * mb, 0.0f);
-            const float d = mb - fmean;
-            m2 += (double)(m2b + nb * d * d);
-        }
+        const int b = b0 + 32 * i;
+        const bool last = b == p.nblk - 1;
+        const float nb = last ? n_last : n_full;
+        const float mb = sv[i] * (last ? i_last : i_full);
+        const float m2b = fmaxf(qv[i] - sv[i] * mb, 0.0f);
+        const float d = mb - mean;
+        m2v[i] = b < p.nblk ? m2b + nb * d * d : 0.0f;
     }
-    m2 = warp_sum_d(m2);
-    if (l == 0) {
-        const double var = m2 / n;
-        p.mean[c] = (float)mean;
-        p.invstd[c] = (float)(1.0 / sqrt(var + (double)p.eps));
+    const float m2 = fin_reduce(sh, w, lane, tree_sum(m2v));
+    if (threadIdx.x < 8) {
+        const float var = m2 / n;
+        p.mean[c] = mean;
+        p.invstd[c] = 1.0f / sqrtf(var + p.eps);
         if (p.running_mean) {
-            const double unb = n > 1 ? m2 / (n - 1.0) : var;
-            p.running_mean[c] = (float)((1.0 - p.momentum) * p.running_mean[c] + p.momentum * mean);
-            p.running_var[c] = (float)((1.0 - p.momentum) * p.running_var[c] + p.momentum * unb);
+            const float unb = p.M > 1 ? m2 / (n - 1.0f) : var;
+            p.running_mean[c] = (1.0f - p.momentum) * p.running_mean[c] + p.momentum * mean;
+            p.running_var[c] = (1.0f - p.momentum) * p.running_var[c] + p.momentum * unb;
         }
     }
 }
@@ -389,27 +409,17 @@ __global__ void __launch_bounds__(THREADS) k_bn_bwd_reduce(Params p) {
     }
 }
 
-__global__ void __launch_bounds__(256) k_bn_bwd_finalize(Params p) {
-    const int c = blockIdx.x * 8 + (threadIdx.x >> 5);
-    const int l = threadIdx.x & 31;
-    if (c >= p.C) return;
-    const float* part = p.partial + c;
-    const size_t stride = (size_t)2 * p.C;
+__global__ void __launch_bounds__(FIN_THREADS) k_bn_bwd_finalize(Params p) {
+    __shared__ float sh[8][8];
+    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+    const int c = blockIdx.x * 8 + (lane & 7);
     float sv[MAX_PART_PER_LANE], qv[MAX_PART_PER_LANE];
-#pragma unroll
-    for (int i = 0; i < MAX_PART_PER_LANE; ++i) {
-        const int b = l + 32 * i;
-        sv[i] = b < p.nblk ? part[(size_t)b * stride] : 0.0f;
-        qv[i] = b < p.nblk ? part[(size_t)b * stride + p.C] : 0.0f;
-    }
-    double sd = 0.0, sx = 0.0;
-#pragma unroll
-    for (int i = 0; i < MAX_PART_PER_LANE; ++i) { sd += (double)sv[i]; sx += (double)qv[i]; }
-    sd = warp_sum_d(sd);
-    sx = warp_sum_d(sx);
-    if (l == 0) {
-        p.dbeta[c] = (float)sd;
-        p.dgamma[c] = (float)((double)p.invstd[c] * (sx - (double)p.mean[c] * sd));
+    fin_load(p, w * 4 + (lane >> 3), c, sv, qv);
+    const float sd = fin_reduce(sh, w, lane, tree_sum(sv));
+    const float sx = fin_reduce(sh, w, lane, tree_sum(qv));
+    if (threadIdx.x < 8) {
+        p.dbeta[c] = sd;
+        p.dgamma[c] = p.invstd[c] * (sx - p.mean[c] * sd);
     }
 }
 
@@ -529,7 +539,7 @@ extern "C" int lwc_bn_forward(const void* x, void* y, const void* res, const flo
         // the pure-read statistics pass (50 registers) likes 4 CTAs per SM; the apply pass 2
         plan_grid(M, C, &p.nblk, &p.rows_per_blk, &grid, 4);
         LWC_BN_DISPATCH(dtype, k_bn_stats<T><<<grid, THREADS, 0, st>>>(p));
-        k_bn_finalize<<<(C + 7) / 8, 256, 0, st>>>(p);
+        k_bn_finalize<<<C / 8, FIN_THREADS, 0, st>>>(p);
     }
     plan_grid(M, C, &p.nblk, &p.rows_per_blk, &grid, 2);
     LWC_BN_DISPATCH(dtype, k_bn_apply<T><<<grid, THREADS, 0, st>>>(p, training ? 0 : 1));
@@ -554,7 +564,7 @@ extern "C" int lwc_bn_backward(const void* dy, const void* x, const void* y, voi
     dim3 grid;
     plan_grid(M, C, &p.nblk, &p.rows_per_blk, &grid);
     LWC_BN_DISPATCH(dtype, k_bn_bwd_reduce<T><<<grid, THREADS, 0, st>>>(p));
-    k_bn_bwd_finalize<<<(C + 7) / 8, 256, 0, st>>>(p);
+    k_bn_bwd_finalize<<<C / 8, FIN_THREADS, 0, st>>>(p);
     LWC_BN_DISPATCH(dtype, k_bn_bwd_apply<T><<<grid, THREADS, 0, st>>>(p));
     return (int)cudaGetLastError();
 }
