@@ -203,6 +203,12 @@ size_t lwc_bn_workspace_bytes(long long M, int C);
 int lwc_bn_forward(const void* x, void* y, const void* res, const float* gamma, const float* beta,
                    float* mean, float* invstd, float* running_mean, float* running_var, float* workspace,
                    long long M, int C, int dtype, int training, int relu, float eps, float momentum, void* stream);
+/* same, and in training mode also increments *num_batches_tracked (int64 device scalar, nullable) inside the
+ * statistics-finalize kernel, so nn.BatchNorm2d's counter costs no launch of its own */
+int lwc_bn_forward_ex(const void* x, void* y, const void* res, const float* gamma, const float* beta,
+                      float* mean, float* invstd, float* running_mean, float* running_var, float* workspace,
+                      long long M, int C, int dtype, int training, int relu, float eps, float momentum,
+                      long long* num_batches_tracked, void* stream);
 int lwc_bn_backward(const void* dy, const void* x, const void* y, void* dx, void* dres, const float* gamma,
                     const float* beta, const float* mean, const float* invstd, float* dgamma, float* dbeta,
                     float* workspace, long long M, int C, int dtype, int relu, void* stream);

@@ -87,6 +87,8 @@ def declare(lib: C.CDLL):
     sig("lwc_bn_workspace_bytes", sz, C.c_longlong, C.c_int)
     sig("lwc_bn_forward", C.c_int, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, C.c_longlong, C.c_int, C.c_int, C.c_int,
         C.c_int, C.c_float, C.c_float, vp)
+    sig("lwc_bn_forward_ex", C.c_int, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, C.c_longlong, C.c_int, C.c_int, C.c_int,
+        C.c_int, C.c_float, C.c_float, vp, vp)
     sig("lwc_bn_backward", C.c_int, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, C.c_longlong, C.c_int, C.c_int,
         C.c_int, vp)
     sig("lwc_maxpool_forward", C.c_int, vp, vp, vp, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int,

@@ -45,6 +45,7 @@ struct Params {
     float* dgamma;
     float* dbeta;
     float* partial;       // [nblk][2][C]
+    long long* num_batches;   // nn.BatchNorm2d.num_batches_tracked, bumped by the finalize kernel (nullable)
     long long M;
     int C;
     int nblk;
@@ -288,6 +289,7 @@ __global__ void __launch_bounds__(FIN_THREADS) k_bn_finalize(Params p) {
         m2v[i] = b < p.nblk ? m2b + nb * d * d : 0.0f;
     }
     const float m2 = fin_reduce(sh, w, lane, tree_sum(m2v));
+    if (p.num_batches && blockIdx.x == 0 && threadIdx.x == 0) *p.num_batches += 1;
     if (threadIdx.x < 8) {
         const float var = m2 / n;
         p.mean[c] = mean;
@@ -521,10 +523,25 @@ extern "C" size_t lwc_bn_workspace_bytes(long long M, int C) {
 
 // Training (training=1): batch statistics are computed, saved in mean/invstd and folded into the running stats.
 // Eval (training=0): running statistics are used.  res may be NULL; relu in {0,1}.
+extern "C" int lwc_bn_forward_ex(const void* x, void* y, const void* res, const float* gamma, const float* beta,
+                                 float* mean, float* invstd, float* running_mean, float* running_var, float* workspace,
+                                 long long M, int C, int dtype, int training, int relu, float eps, float momentum,
+                                 long long* num_batches_tracked, void* stream);
+
 extern "C" int lwc_bn_forward(const void* x, void* y, const void* res, const float* gamma, const float* beta,
                               float* mean, float* invstd, float* running_mean, float* running_var, float* workspace,
                               long long M, int C, int dtype, int training, int relu, float eps, float momentum,
                               void* stream) {
+    return lwc_bn_forward_ex(x, y, res, gamma, beta, mean, invstd, running_mean, running_var, workspace, M, C, dtype,
+                             training, relu, eps, momentum, nullptr, stream);
+}
+
+// num_batches_tracked (int64 device scalar, nullable): incremented by one in training mode inside the finalize
+// kernel -- the module's counter costs no launch of its own.
+extern "C" int lwc_bn_forward_ex(const void* x, void* y, const void* res, const float* gamma, const float* beta,
+                                 float* mean, float* invstd, float* running_mean, float* running_var, float* workspace,
+                                 long long M, int C, int dtype, int training, int relu, float eps, float momentum,
+                                 long long* num_batches_tracked, void* stream) {
     if (!x || !y || M <= 0 || C <= 0 || (C % VEC)) return LWC_EINVAL;
     if (training && (!mean || !invstd || !workspace)) return LWC_EINVAL;
     if (!training && (!running_mean || !running_var)) return LWC_EINVAL;
@@ -534,6 +551,7 @@ extern "C" int lwc_bn_forward(const void* x, void* y, const void* res, const flo
     p.x = x; p.y = y; p.res = res; p.gamma = gamma; p.beta = beta; p.mean = mean; p.invstd = invstd;
     p.running_mean = running_mean; p.running_var = running_var; p.partial = workspace;
     p.M = M; p.C = C; p.relu = relu; p.eps = eps; p.momentum = momentum;
+    p.num_batches = training ? num_batches_tracked : nullptr;
     dim3 grid;
     if (training) {
         // the pure-read statistics pass (50 registers) likes 4 CTAs per SM; the apply pass 2

@@ -70,13 +70,12 @@ class Bottleneck(nn.Module):
         return self.bn3
 
     def forward(self, x):
-        if self.downsample is None:
-            # the block input forks into conv1 and the skip connection: fused backward (ops/conv.py)
-            from ..ops.conv import fork_conv1x1
-            out, identity = fork_conv1x1(self.conv1, x)
-        else:
-            identity = self.downsample(x)
-            out = self.conv1(x)
+        # the block input forks into conv1 and the skip connection (plain or through the downsample convolution):
+        # conv1's data gradient runs on the tcgen05 kernel whose epilogue adds the skip gradient (ops/conv.py)
+        from ..ops.conv import fork_conv1x1
+        out, identity = fork_conv1x1(self.conv1, x)
+        if self.downsample is not None:
+            identity = self.downsample(identity)
         out = self.bn1(out, relu=True)
         out = self.bn2(self.conv2(out), relu=True)
         return self.bn3(self.conv3(out), residual=identity, relu=True)

@@ -59,7 +59,8 @@ def _ptr(t):
 
 class _BatchNormAct(torch.autograd.Function):
     @staticmethod
-    def forward(ctx, x, weight, bias, running_mean, running_var, residual, training, momentum, eps, relu):
+    def forward(ctx, x, weight, bias, running_mean, running_var, residual, training, momentum, eps, relu,
+                num_batches_tracked=None):
         lib = _native.lib()
         M, Cc = _rows_channels(x)
         y = torch.empty_like(x)       # preserves the channels-last strides
@@ -70,11 +71,11 @@ class _BatchNormAct(torch.autograd.Function):
             mean = torch.empty(Cc, dtype=torch.float32, device=x.device)
             invstd = torch.empty(Cc, dtype=torch.float32, device=x.device)
             ws_ptr = _workspace(int(lib.lwc_bn_workspace_bytes(M, Cc)), x.device).data_ptr()
-        rc = lib.lwc_bn_forward(x.data_ptr(), y.data_ptr(), _ptr(residual), _ptr(weight), _ptr(bias), _ptr(mean),
-                                _ptr(invstd), _ptr(running_mean), _ptr(running_var), ws_ptr, M, Cc,
-                                abi.dtype_code(x.dtype), int(training), int(relu), float(eps), float(momentum),
-                                C.c_void_p(st))
-        abi.check(rc, "lwc_bn_forward")
+        rc = lib.lwc_bn_forward_ex(x.data_ptr(), y.data_ptr(), _ptr(residual), _ptr(weight), _ptr(bias), _ptr(mean),
+                                   _ptr(invstd), _ptr(running_mean), _ptr(running_var), ws_ptr, M, Cc,
+                                   abi.dtype_code(x.dtype), int(training), int(relu), float(eps), float(momentum),
+                                   _ptr(num_batches_tracked), C.c_void_p(st))
+        abi.check(rc, "lwc_bn_forward_ex")
         _native.counters.add(3 if training else 1)
         ctx.training, ctx.relu, ctx.has_res = training, relu, residual is not None
         ctx.eps = eps
@@ -102,7 +103,7 @@ class _BatchNormAct(torch.autograd.Function):
             xhat = (x.float() - mean.view(shape)) * torch.rsqrt(invstd + ctx.eps).view(shape)
             dims = (0, 2, 3) if x.dim() == 4 else (0,)
             return (dx, (g.float() * xhat).sum(dims), g.float().sum(dims), None, None,
-                    g if ctx.has_res else None, None, None, None, None)
+                    g if ctx.has_res else None, None, None, None, None, None)
         dx = torch.empty_like(x)
         dres = torch.empty_like(x) if ctx.has_res else None
         dgamma = torch.empty(Cc, dtype=torch.float32, device=x.device)
@@ -115,13 +116,15 @@ class _BatchNormAct(torch.autograd.Function):
         abi.check(rc, "lwc_bn_backward")
         _native.counters.add(3)
         return (dx, dgamma if weight is not None else None, dbeta if weight is not None else None, None, None,
-                dres, None, None, None, None)
+                dres, None, None, None, None, None)
 
 
 def batch_norm_act(x, weight, bias, running_mean, running_var, residual=None, training=True,
-                   momentum=0.1, eps=1e-5, relu=False):
-    """``relu?(batch_norm(x) + residual?)`` in one fused pass structure (see module docstring)."""
-    return _BatchNormAct.apply(x, weight, bias, running_mean, running_var, residual, training, momentum, eps, relu)
+                   momentum=0.1, eps=1e-5, relu=False, num_batches_tracked=None):
+    """``relu?(batch_norm(x) + residual?)`` in one fused pass structure (see module docstring).
+    ``num_batches_tracked`` (int64 CUDA scalar) is incremented inside the statistics-finalize kernel."""
+    return _BatchNormAct.apply(x, weight, bias, running_mean, running_var, residual, training, momentum, eps, relu,
+                               num_batches_tracked)
 
 
 def maybe_batch_norm(module, x, residual=None, relu=False):
@@ -131,7 +134,11 @@ def maybe_batch_norm(module, x, residual=None, relu=False):
     if not supported(x, module.weight, module.bias, residual):
         return None
     training = module.training or module.running_mean is None
+    nbt = None
     if training and module.track_running_stats and module.num_batches_tracked is not None:
-        module.num_batches_tracked.add_(1)
+        nbt = module.num_batches_tracked
+        if not (nbt.is_cuda and nbt.dtype == torch.int64):
+            nbt.add_(1)
+            nbt = None
     return batch_norm_act(x, module.weight, module.bias, module.running_mean, module.running_var,
-                          residual, training, module.momentum, module.eps, relu)
+                          residual, training, module.momentum, module.eps, relu, nbt)

@@ -79,3 +79,15 @@ def test_module_matches_torch_module_in_training():
     assert _native.counters.kernels == 3
     assert torch.allclose(ya, yb, atol=1e-4)
     assert torch.allclose(a.running_var, b.running_var, atol=1e-5) and int(a.num_batches_tracked) == 1
+
+
+def test_num_batches_tracked_is_bumped_by_the_finalize_kernel():
+    from layerwise_b200.ops import nn as lnn
+    bn = lnn.BatchNorm2d(64).cuda()
+    x = torch.randn(8, 64, 6, 6, device="cuda").contiguous(memory_format=torch.channels_last)
+    for _ in range(3):
+        bn(x, relu=True)
+    bn.eval()
+    bn(x)
+    torch.cuda.synchronize()
+    assert int(bn.num_batches_tracked) == 3
