@@ -150,6 +150,138 @@ __global__ void __launch_bounds__(256) k_maxpool_bwd(Params p) {
     }
 }
 
+// Raw 8-element vectors: loaded without conversion so that several loads can be in flight before the first use.
+template <typename T> struct Raw8 { uint4 v; };
+template <> struct Raw8<float> { float4 a, b; };
+template <typename T>
+__device__ __forceinline__ void ldraw(const T* p, Raw8<T>& r) { r.v = *reinterpret_cast<const uint4*>(p); }
+template <>
+__device__ __forceinline__ void ldraw<float>(const float* p, Raw8<float>& r) {
+    r.a = *reinterpret_cast<const float4*>(p);
+    r.b = *reinterpret_cast<const float4*>(p + 4);
+}
+__device__ __forceinline__ void unpack(const Raw8<__nv_bfloat16>& r, float v[8]) {
+    const uint32_t w[4] = {r.v.x, r.v.y, r.v.z, r.v.w};
+#pragma unroll
+    for (int i = 0; i < 4; ++i) { v[2 * i] = __uint_as_float(w[i] << 16); v[2 * i + 1] = __uint_as_float(w[i] & 0xffff0000u); }
+}
+__device__ __forceinline__ void unpack(const Raw8<__half>& r, float v[8]) {
+    const uint32_t w[4] = {r.v.x, r.v.y, r.v.z, r.v.w};
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+        const __half2 h = *reinterpret_cast<const __half2*>(&w[i]);
+        v[2 * i] = __low2float(h); v[2 * i + 1] = __high2float(h);
+    }
+}
+__device__ __forceinline__ void unpack(const Raw8<float>& r, float v[8]) {
+    v[0] = r.a.x; v[1] = r.a.y; v[2] = r.a.z; v[3] = r.a.w; v[4] = r.b.x; v[5] = r.b.y; v[6] = r.b.z; v[7] = r.b.w;
+}
+
+// ---- 3x3 / stride 2 / pad 1 (the ResNet stem pool) specialisations ------------------------------------------
+// Forward: the nine 16-byte loads of a window are issued back to back (compile-time window, 32-bit indexing).
+template <typename T>
+__global__ void __launch_bounds__(256) k_maxpool_fwd_k3s2(Params p) {
+    const int ncg = p.C >> 3;
+    const int total = p.N * p.OH * p.OW * ncg;
+    for (int id = blockIdx.x * blockDim.x + threadIdx.x; id < total; id += gridDim.x * blockDim.x) {
+        const int cg = id % ncg;
+        int pix = id / ncg;
+        const int ow = pix % p.OW; pix /= p.OW;
+        const int oh = pix % p.OH;
+        const int n = pix / p.OH;
+        const int h0 = 2 * oh - 1, w0 = 2 * ow - 1;
+        const T* xb = reinterpret_cast<const T*>(p.x) + (size_t)n * p.H * p.W * p.C + cg * 8;
+        Raw8<T> raw[9];
+        bool ok[9];
+#pragma unroll
+        for (int t = 0; t < 9; ++t) {
+            const int h = h0 + t / 3, w = w0 + t % 3;
+            ok[t] = h >= 0 && h < p.H && w >= 0 && w < p.W;
+            // out-of-range taps re-read the (always valid) centre tap: no branch, no effect on the maximum
+            const int hh = ok[t] ? h : h0 + 1, ww = ok[t] ? w : w0 + 1;
+            ldraw<T>(xb + (size_t)(hh * p.W + ww) * p.C, raw[t]);
+        }
+        float best[8];
+        unsigned arg[8];
+#pragma unroll
+        for (int c = 0; c < 8; ++c) { best[c] = -INFINITY; arg[c] = 0; }
+#pragma unroll
+        for (int t = 0; t < 9; ++t) {
+            float v[8];
+            unpack(raw[t], v);
+#pragma unroll
+            for (int c = 0; c < 8; ++c)
+                if (ok[t] && v[c] > best[c]) { best[c] = v[c]; arg[c] = t; }
+        }
+        const size_t o = (size_t)id * 8;                  // == ((n*OH + oh)*OW + ow)*C + cg*8
+        V8<T>::st(reinterpret_cast<T*>(p.y) + o, best);
+        if (p.idx) {
+            uint2 packed;
+            packed.x = arg[0] | (arg[1] << 8) | (arg[2] << 16) | (arg[3] << 24);
+            packed.y = arg[4] | (arg[5] << 8) | (arg[6] << 16) | (arg[7] << 24);
+            *reinterpret_cast<uint2*>(p.idx + o) = packed;
+        }
+    }
+}
+
+// Backward: a thread owns a 2x2 block of input pixels (rows 2i, 2i+1; columns 2j, 2j+1).  Only the four windows
+// (i..i+1, j..j+1) can point into it, so their dy / argmax vectors are loaded once (4 x 24 bytes) for four outputs;
+// the per-pixel gather needs nine window loads for the same block.  H and W even.
+template <typename T>
+__global__ void __launch_bounds__(256) k_maxpool_bwd_k3s2(Params p) {
+    const int ncg = p.C >> 3;
+    const int HB = p.H >> 1, WB = p.W >> 1;
+    const int total = p.N * HB * WB * ncg;
+    for (int id = blockIdx.x * blockDim.x + threadIdx.x; id < total; id += gridDim.x * blockDim.x) {
+        const int cg = id % ncg;
+        int blk = id / ncg;
+        const int j = blk % WB; blk /= WB;
+        const int i = blk % HB;
+        const int n = blk / HB;
+        Raw8<T> draw[4];
+        uint2 a[4];
+        bool ok[4];
+#pragma unroll
+        for (int t = 0; t < 4; ++t) {
+            const int oh = i + (t >> 1), ow = j + (t & 1);
+            ok[t] = oh < p.OH && ow < p.OW;
+            const size_t o = (((size_t)n * p.OH + (ok[t] ? oh : i)) * p.OW + (ok[t] ? ow : j)) * p.C + cg * 8;
+            a[t] = *reinterpret_cast<const uint2*>(p.idx + o);
+            ldraw<T>(reinterpret_cast<const T*>(p.dy) + o, draw[t]);
+        }
+        // window t = (dh, dw) relative to (i, j); the input pixel (2i + a_, 2j + b_) sits at kernel offset
+        // kh = a_ + 1 - 2 dh, kw = b_ + 1 - 2 dw of that window (valid when 0 <= kh, kw <= 2)
+        float acc[4][8];
+#pragma unroll
+        for (int q = 0; q < 4; ++q)
+#pragma unroll
+            for (int c = 0; c < 8; ++c) acc[q][c] = 0.0f;
+#pragma unroll
+        for (int t = 0; t < 4; ++t) {
+            if (!ok[t]) continue;
+            const int dh = t >> 1, dw = t & 1;
+            float dv[8];
+            unpack(draw[t], dv);
+#pragma unroll
+            for (int q = 0; q < 4; ++q) {
+                const int kh = (q >> 1) + 1 - 2 * dh, kw = (q & 1) + 1 - 2 * dw;
+                if (kh < 0 || kh > 2 || kw < 0 || kw > 2) continue;      // compile-time after unrolling
+                const unsigned code = kh * 3 + kw;
+#pragma unroll
+                for (int c = 0; c < 8; ++c) {
+                    const unsigned ac = ((c < 4 ? a[t].x : a[t].y) >> (8 * (c & 3))) & 0xffu;
+                    if (ac == code) acc[q][c] += dv[c];
+                }
+            }
+        }
+        T* dx = reinterpret_cast<T*>(p.dx) + (((size_t)n * p.H + 2 * i) * p.W + 2 * j) * p.C + cg * 8;
+        V8<T>::st(dx, acc[0]);
+        V8<T>::st(dx + p.C, acc[1]);
+        V8<T>::st(dx + (size_t)p.W * p.C, acc[2]);
+        V8<T>::st(dx + (size_t)p.W * p.C + p.C, acc[3]);
+    }
+}
+
 }  // namespace pool
 }  // namespace lwc
 
@@ -182,6 +314,10 @@ extern "C" int lwc_maxpool_forward(const void* x, void* y, void* idx, int N, int
     p.OW = (W + 2 * pad - k) / stride + 1;
     if (p.OH < 1 || p.OW < 1) return LWC_EINVAL;
     const long long total = (long long)N * p.OH * p.OW * (C >> 3);
+    if (k == 3 && stride == 2 && pad == 1 && (long long)N * H * W * C < (1LL << 31)) {
+        LWC_POOL_DISPATCH(dtype, k_maxpool_fwd_k3s2<T><<<grid_for(total), 256, 0, (cudaStream_t)stream>>>(p));
+        return (int)cudaGetLastError();
+    }
     LWC_POOL_DISPATCH(dtype, k_maxpool_fwd<T><<<grid_for(total), 256, 0, (cudaStream_t)stream>>>(p));
     return (int)cudaGetLastError();
 }
@@ -196,6 +332,10 @@ extern "C" int lwc_maxpool_backward(const void* dy, const void* idx, void* dx, i
     p.OH = (H + 2 * pad - k) / stride + 1;
     p.OW = (W + 2 * pad - k) / stride + 1;
     const long long total = (long long)N * H * W * (C >> 3);
+    if (k == 3 && stride == 2 && pad == 1 && !(H & 1) && !(W & 1) && (long long)N * H * W * C < (1LL << 31)) {
+        LWC_POOL_DISPATCH(dtype, k_maxpool_bwd_k3s2<T><<<grid_for(total / 4), 256, 0, (cudaStream_t)stream>>>(p));
+        return (int)cudaGetLastError();
+    }
     LWC_POOL_DISPATCH(dtype, k_maxpool_bwd<T><<<grid_for(total), 256, 0, (cudaStream_t)stream>>>(p));
     return (int)cudaGetLastError();
 }

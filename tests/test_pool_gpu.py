@@ -9,7 +9,8 @@ pytestmark = pytest.mark.gpu
 
 @pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float32])
 @pytest.mark.parametrize("k,s,p,shape", [(3, 2, 1, (4, 64, 37, 41)), (2, 2, 0, (8, 128, 16, 16)),
-                                        (4, 4, 0, (8, 512, 4, 4)), (3, 2, 1, (2, 64, 112, 112)), (3, 1, 1, (2, 8, 9, 7))])
+                                        (4, 4, 0, (8, 512, 4, 4)), (3, 2, 1, (2, 64, 112, 112)), (3, 1, 1, (2, 8, 9, 7)),
+                                        (3, 2, 1, (3, 16, 6, 10)), (3, 2, 1, (2, 8, 2, 2))])
 def test_maxpool_matches_torch(dtype, k, s, p, shape):
     from layerwise_b200.ops import nn as lnn
     torch.manual_seed(0)
