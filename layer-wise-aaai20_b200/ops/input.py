@@ -33,35 +33,76 @@ def s2d_stem_weight(w7: torch.Tensor) -> torch.Tensor:
     return F.pad(w, (0, 0, 0, 0, 0, 4))
 
 
+_WS = {}
+
+
+def stem_wgrad_native_ok(oh: int, ow: int, dtype, cout: int = 64) -> bool:
+    """Can ``csrc/stem.cu`` compute the stem's weight gradient for this output size?"""
+    return (_native.available() and dtype == torch.bfloat16 and cout == 64 and oh % 2 == 0 and ow % 16 == 0
+            and 16 <= ow <= 144)
+
+
+def stem_wgrad(dy: torch.Tensor, xs: torch.Tensor, out_dtype=torch.bfloat16, scale: float = 1.0) -> torch.Tensor:
+    """Weight gradient [64,3,7,7] (channels-last) of the 7x7/2 stem from ``dy`` [N,64,OH,OW] (channels-last bf16) and
+    the space-to-depth input ``xs`` [N,16,OH+3,OW+3] (channels-last bf16): one tcgen05 kernel + a tiny reduction."""
+    n, co, oh, ow = dy.shape
+    assert co == 64 and tuple(xs.shape) == (n, 16, oh + 3, ow + 3)
+    assert dy.dtype == torch.bfloat16 and xs.dtype == torch.bfloat16
+    if not dy.is_contiguous(memory_format=torch.channels_last):
+        dy = dy.contiguous(memory_format=torch.channels_last)
+    assert xs.is_contiguous(memory_format=torch.channels_last)
+    lib = _native.lib()
+    nbytes = int(lib.lwc_stem_wgrad_workspace_bytes(n, oh))
+    key = (dy.device.index, torch.cuda.current_stream(dy.device).cuda_stream)
+    ws = _WS.get(key)
+    if ws is None or ws.numel() * 4 < nbytes:
+        ws = _WS[key] = torch.empty(nbytes // 4, dtype=torch.float32, device=dy.device)
+    gw = torch.empty((64, 3, 7, 7), dtype=out_dtype, device=dy.device, memory_format=torch.channels_last)
+    st = torch.cuda.current_stream().cuda_stream
+    abi.check(lib.lwc_stem_wgrad(dy.data_ptr(), xs.data_ptr(), gw.data_ptr(), ws.data_ptr(), n, oh, ow,
+                                 abi.dtype_code(out_dtype), float(scale), C.c_void_p(st)), "lwc_stem_wgrad")
+    _native.counters.add(2)
+    return gw
+
+
 class _StemS2D(torch.autograd.Function):
-    """Stem convolution: forward on the space-to-depth input (dense 4x4/1, K = 256), weight gradient in the
-    original 7x7/2 formulation on the plain 3-channel input (cuDNN's wgrad for the 16-channel 4x4 form is
-    ~2x slower than its 7x7 one on B200).  No input gradient: the stem consumes data."""
+    """Stem convolution: forward on the space-to-depth input (dense 4x4/1, K = 256).  Weight gradient: the tcgen05
+    kernel of ``csrc/stem.cu`` straight from the space-to-depth input, or (``x3`` given: shapes the kernel does not
+    take) cuDNN's wgrad in the original 7x7/2 formulation on a plain 3-channel copy -- its wgrad for the 16-channel
+    4x4 form is ~2x slower than its 7x7 one on B200.  No input gradient: the stem consumes data."""
 
     @staticmethod
     def forward(ctx, xs, x3, w7):
         w = s2d_stem_weight(w7)
         if xs.is_contiguous(memory_format=torch.channels_last):
             w = w.contiguous(memory_format=torch.channels_last)
-        ctx.save_for_backward(x3, w7)
+        ctx.native = x3 is None
+        ctx.save_for_backward(xs if x3 is None else x3, w7)
         return F.conv2d(xs, w, None, stride=1, padding=0)
 
     @staticmethod
     def backward(ctx, dy):
-        x3, w7 = ctx.saved_tensors
-        gw = torch.ops.aten.convolution_backward(dy, x3, w7, None, [2, 2], [3, 3], [1, 1], False, [0, 0], 1,
+        x, w7 = ctx.saved_tensors
+        if ctx.native:
+            return None, None, stem_wgrad(dy, x, w7.dtype)
+        gw = torch.ops.aten.convolution_backward(dy, x, w7, None, [2, 2], [3, 3], [1, 1], False, [0, 0], 1,
                                                  [False, True, False])[1]
         return None, None, gw
 
 
 def stem_s2d(xs: torch.Tensor, w7: torch.Tensor) -> torch.Tensor:
     x3 = getattr(xs, "plain3", None)
-    if x3 is None or not w7.requires_grad or not torch.is_grad_enabled():
-        w = s2d_stem_weight(w7)
-        if xs.is_contiguous(memory_format=torch.channels_last):
-            w = w.contiguous(memory_format=torch.channels_last)
-        return F.conv2d(xs, w, None, stride=1, padding=0)
-    return _StemS2D.apply(xs, x3, w7)
+    if w7.requires_grad and torch.is_grad_enabled():
+        if (xs.is_cuda and xs.dtype == torch.bfloat16 and w7.dtype == torch.bfloat16 and tuple(w7.shape) == (64, 3, 7, 7)
+                and xs.shape[1] == 16 and xs.is_contiguous(memory_format=torch.channels_last)
+                and stem_wgrad_native_ok(xs.shape[2] - 3, xs.shape[3] - 3, xs.dtype, w7.shape[0])):
+            return _StemS2D.apply(xs, None, w7)
+        if x3 is not None:
+            return _StemS2D.apply(xs, x3, w7)
+    w = s2d_stem_weight(w7)
+    if xs.is_contiguous(memory_format=torch.channels_last):
+        w = w.contiguous(memory_format=torch.channels_last)
+    return F.conv2d(xs, w, None, stride=1, padding=0)
 
 
 def normalize_u8(x: torch.Tensor, dtype=torch.bfloat16, s2d: bool = False, mean=IMAGENET_MEAN, std=IMAGENET_STD,
@@ -80,8 +121,9 @@ def normalize_u8(x: torch.Tensor, dtype=torch.bfloat16, s2d: bool = False, mean=
                                                  abi.dtype_code(dtype), C.c_void_p(st)), "lwc_normalize_u8")
         _native.counters.add(1)
         res = out.permute(0, 3, 1, 2)           # logical NCHW view of NHWC storage (= channels_last)
-        if keep_plain:
-            # the stem's weight gradient is cheaper in the original 7x7 formulation: keep a 3-channel copy too
+        if keep_plain and not stem_wgrad_native_ok(h // 2, w // 2, dtype):
+            # shapes csrc/stem.cu does not take: cuDNN's weight gradient is cheaper in the original 7x7 formulation,
+            # which needs a plain 3-channel copy
             plain = torch.empty((n, h, w, 3), dtype=dtype, device=x.device)
             abi.check(_native.lib().lwc_normalize_u8(x.data_ptr(), plain.data_ptr(), n, h, w, 3, 0, m, s,
                                                      abi.dtype_code(dtype), C.c_void_p(st)), "lwc_normalize_u8")
