@@ -227,6 +227,14 @@ int lwc_conv_forward(const void* x, const void* wt, void* y, int Nimg, int H, in
 int lwc_conv1x1_add(const void* x, const void* wt, const void* addend, void* y, int Nimg, int H, int W, int Cin,
                     int Cout, int b_mn, void* stream);
 
+/* Weight gradient of the ResNet stem (7x7/2 pad 3, 3 -> 64 channels; IMAGENET/training/resnet.py:100) on tcgen05:
+ * dy [N][OH][OW][64] bf16, xs = the 2x2 space-to-depth input [N][OH+3][OW+3][16] bf16 written by lwc_normalize_u8
+ * (mode 1); out [64][7][7][3] (channels-last [64,3,7,7]) in out_dtype (LWC_F32 / LWC_BF16) = scale * dW.
+ * OH even, OW % 16 == 0, OW <= 144.  workspace: lwc_stem_wgrad_workspace_bytes(N, OH) bytes of device memory. */
+size_t lwc_stem_wgrad_workspace_bytes(int N, int OH);
+int lwc_stem_wgrad(const void* dy, const void* xs, void* out, float* workspace, int N, int OH, int OW, int out_dtype,
+                   float scale, void* stream);
+
 /* Max pooling, NHWC, byte argmax forward + gather backward (CIFAR10/dawn.py:51,:70; resnet.py:104). */
 int lwc_maxpool_forward(const void* x, void* y, void* idx, int N, int H, int W, int C, int k, int stride,
                         int pad, int dtype, void* stream);
