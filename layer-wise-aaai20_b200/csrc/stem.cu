@@ -102,6 +102,37 @@ __device__ __forceinline__ void umma(uint32_t tmem_d, uint64_t da, uint64_t db, 
         "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}"
         ::"r"(tmem_d), "l"(da), "l"(db), "r"(kIdesc), "r"(accumulate) : "memory");
 }
+// All MMAs of one input row in ONE asm block: up to three (A tile, accumulator) uses x ksteps K-steps, descriptors
+// advanced by 2048 bytes (16 k-rows) per step inside the block.  Issued one by one from C++, every tcgen05.mma costs
+// ~120 cycles of operand shuffling into uniform registers (R2UR) against 32 cycles of tensor-pipe time; here the
+// operands enter uniform registers once per row.
+__device__ __forceinline__ void umma_row(uint32_t t0, uint32_t t1, uint32_t t2, uint64_t da0, uint64_t da1, uint64_t da2,
+                                         uint64_t db, uint32_t use_mask, uint32_t acc_mask, uint32_t ksteps) {
+    asm volatile(
+        "{\n\t"
+        ".reg .pred u0, u1, u2, a0, a1, a2, lp;\n\t"
+        ".reg .b64 x0, x1, x2, xb;\n\t"
+        ".reg .b32 i, t;\n\t"
+        "and.b32 t, %7, 1;\n\t setp.ne.b32 u0, t, 0;\n\t"
+        "and.b32 t, %7, 2;\n\t setp.ne.b32 u1, t, 0;\n\t"
+        "and.b32 t, %7, 4;\n\t setp.ne.b32 u2, t, 0;\n\t"
+        "and.b32 t, %8, 1;\n\t setp.ne.b32 a0, t, 0;\n\t"
+        "and.b32 t, %8, 2;\n\t setp.ne.b32 a1, t, 0;\n\t"
+        "and.b32 t, %8, 4;\n\t setp.ne.b32 a2, t, 0;\n\t"
+        "mov.b64 x0, %3;\n\t mov.b64 x1, %4;\n\t mov.b64 x2, %5;\n\t mov.b64 xb, %6;\n\t mov.u32 i, 0;\n\t"
+        "ROW_LOOP:\n\t"
+        "@u0 tcgen05.mma.cta_group::1.kind::f16 [%0], x0, xb, %10, a0;\n\t"
+        "@u1 tcgen05.mma.cta_group::1.kind::f16 [%1], x1, xb, %10, a1;\n\t"
+        "@u2 tcgen05.mma.cta_group::1.kind::f16 [%2], x2, xb, %10, a2;\n\t"
+        "add.u64 x0, x0, 128;\n\t add.u64 x1, x1, 128;\n\t add.u64 x2, x2, 128;\n\t add.u64 xb, xb, 128;\n\t"
+        "setp.eq.u32 a0, i, i;\n\t setp.eq.u32 a1, i, i;\n\t setp.eq.u32 a2, i, i;\n\t"
+        "add.u32 i, i, 1;\n\t"
+        "setp.lt.u32 lp, i, %9;\n\t"
+        "@lp bra ROW_LOOP;\n\t"
+        "}"
+        ::"r"(t0), "r"(t1), "r"(t2), "l"(da0), "l"(da1), "l"(da2), "l"(db), "r"(use_mask), "r"(acc_mask), "r"(ksteps), "r"(kIdesc)
+        : "memory");
+}
 __device__ __forceinline__ void umma_commit(uint64_t* bar) {
     asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar)) : "memory");
 }
@@ -267,7 +298,7 @@ __global__ void __launch_bounds__(THREADS, 1) k_stem_wgrad(const __grid_constant
         uint32_t started = 0;
         long long tw_b = 0, tw_p = 0, t_iss = 0, t_com = 0;
         for (int R = R0, i = 0; R < R1; ++R, ++i) {
-            const long long c0 = clock64();
+            const long long c0 = stamps ? clock64() : 0;
             if (R != R0 && r == 0) seq.new_image();
             if (seq.introduces(r, J)) ++seq.q_next;
             // the (at most three) uses of this row, kept in scalar registers: use k reads pair j - k
@@ -275,7 +306,7 @@ __global__ void __launch_bounds__(THREADS, 1) k_stem_wgrad(const __grid_constant
             const bool odd = r & 1;
             const int s = i % NB;
             mbar_wait(&b_full[s], (i / NB) & 1);
-            const long long c1 = clock64();
+            const long long c1 = stamps ? clock64() : 0;
             // descriptor of the A tile of pair pj (0 = not used by this row); everything stays in scalar registers
             auto prep = [&](int pj, bool wanted) -> uint64_t {
                 if (!wanted || pj < 0 || pj >= J) return 0ull;
@@ -288,25 +319,16 @@ __global__ void __launch_bounds__(THREADS, 1) k_stem_wgrad(const __grid_constant
             };
             const uint64_t da0 = prep(j, true), da1 = prep(j - 1, true), da2 = prep(j - 2, !odd);
             const uint32_t acc0 = odd ? ACC_A : ACC_D, acc1 = odd ? ACC_B : ACC_C, acc2 = ACC_E;
-            const long long c2 = clock64();
+            const long long c2 = stamps ? clock64() : 0;
             tcgen05_fence_after();
             const uint64_t db = make_desc(smem_u32(bst + s * slot_bytes), 8192, 1024);
-            auto issue = [&](uint64_t da, uint32_t acc, uint64_t step, bool dup) {
-                if (da == 0ull) return;
-                const uint32_t slot = (dup && acc <= ACC_C) ? NACC + acc : acc;
-                if (leader && !(p.debug & 1)) umma(tmem_base + slot * 64, da + step, db + step, (started >> slot) & 1u);
-                started |= 1u << slot;
-            };
-            for (int ks = 0; ks < ksteps; ++ks) {
-                const uint64_t step = (uint64_t)(ks * (2048 >> 4));      // 16 k-rows of 128 bytes, in descriptor units
-                // back-to-back MMAs into one accumulator are latency-bound at N = 64: odd k-steps of the fully used
-                // accumulators A, B, C go to duplicates (columns 320..511) that the epilogue adds back
-                const bool dup = ks & 1;
-                issue(da0, acc0, step, dup);
-                issue(da1, acc1, step, dup);
-                issue(da2, acc2, step, dup);
-            }
-            const long long c3 = clock64();
+            const uint32_t use_mask = (da0 ? 1u : 0u) | (da1 ? 2u : 0u) | (da2 ? 4u : 0u);
+            const uint32_t acc_mask = ((started >> acc0) & 1u) | (((started >> acc1) & 1u) << 1) | (((started >> acc2) & 1u) << 2);
+            if (leader && !(p.debug & 1))
+                umma_row(tmem_base + acc0 * 64, tmem_base + acc1 * 64, tmem_base + acc2 * 64, da0, da1, da2, db, use_mask, acc_mask,
+                         (uint32_t)ksteps);
+            started |= (da0 ? 1u << acc0 : 0u) | (da1 ? 1u << acc1 : 0u) | (da2 ? 1u << acc2 : 0u);
+            const long long c3 = stamps ? clock64() : 0;
             if (leader) umma_commit(&b_empty[s]);
             // pair j-2 of an even row is used for the last time here
             if (!(r & 1)) {
@@ -314,7 +336,7 @@ __global__ void __launch_bounds__(THREADS, 1) k_stem_wgrad(const __grid_constant
                 if (leader && jl >= 0 && jl < J) umma_commit(&pair_empty[seq.q_of(jl) % PAIR_SLOTS]);
             }
             if (++r == p.HB) { r = 0; ++n; }
-            const long long c4 = clock64();
+            const long long c4 = stamps ? clock64() : 0;
             tw_b += c1 - c0; tw_p += c2 - c1; t_iss += c3 - c2; t_com += c4 - c3;
         }
         if (leader) umma_commit(done);
@@ -328,11 +350,10 @@ __global__ void __launch_bounds__(THREADS, 1) k_stem_wgrad(const __grid_constant
         uint32_t started = 0;
         {
             int n = R0 / p.HB, r = R0 - n * p.HB;
-            for (int R = R0; R < R1 && started != 255u; ++R) {
+            for (int R = R0; R < R1 && started != 31u; ++R) {
                 const RowUses u = row_uses(r, J);
                 for (int k = 0; k < u.n; ++k) {
                     started |= 1u << u.acc[k];
-                    if (u.acc[k] <= ACC_C && ksteps > 1) started |= 1u << (NACC + u.acc[k]);
                 }
                 if (++r == p.HB) r = 0;
             }
