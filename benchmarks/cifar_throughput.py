@@ -58,6 +58,11 @@ def ours(network, args, world):
     y = torch.randint(0, 10, (args.batch,), device="cuda")
     model.train()
 
+    if args.graph and hasattr(ex.engine, "enable_graph_mode"):
+        from layerwise_b200.train.cifar import GraphedTrainStep
+        graphed = GraphedTrainStep(model, ex, opt)
+        return lambda: graphed({"input": x, "target": y})
+
     def step():
         out = model({"input": x, "target": y})
         out["loss"].sum().backward()
@@ -115,6 +120,7 @@ def main():
     ap.add_argument("--compress", default="layerwise")
     ap.add_argument("--method", default="Topk")
     ap.add_argument("--ratio", type=float, default=0.01)
+    ap.add_argument("--graph", action="store_true", help="ours: replay the step as one CUDA graph")
     ap.add_argument("--out", default="gpurun_out/cifar_throughput.json")
     args = ap.parse_args()
     world, rank, local = int(os.environ.get("WORLD_SIZE", 1)), int(os.environ.get("RANK", 0)), int(os.environ.get("LOCAL_RANK", 0))

@@ -163,6 +163,8 @@ typedef struct {
     float lr, momentum, dampening, weight_decay, grad_scale;
     int32_t nesterov, first_step;
     const float* lr_dev;     /* optional: learning rate read from device memory (CUDA-graph replay) */
+    int32_t param_dtype;     /* LWC_F32 (default): fp32 weights + momentum.  LWC_BF16 / LWC_F16: weights, momentum and
+                              * gradients all in that type (training without fp32 masters); model copies unused */
 } LwcSgdDesc;
 /* table_dev: device array of num_tensors LwcSgdTensor; chunk table built by lwc_sgd_plan */
 typedef struct { void* param; const void* grad; void* mom; void* model; int64_t n; } LwcSgdTensor;

@@ -24,7 +24,7 @@ class LwcSgdDesc(C.Structure):
         ("num_tensors", C.c_int32), ("grad_dtype", C.c_int32), ("model_dtype", C.c_int32),
         ("lr", C.c_float), ("momentum", C.c_float), ("dampening", C.c_float),
         ("weight_decay", C.c_float), ("grad_scale", C.c_float),
-        ("nesterov", C.c_int32), ("first_step", C.c_int32), ("lr_dev", C.c_void_p),
+        ("nesterov", C.c_int32), ("first_step", C.c_int32), ("lr_dev", C.c_void_p), ("param_dtype", C.c_int32),
     ]
 
 

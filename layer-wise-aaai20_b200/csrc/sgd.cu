@@ -50,6 +50,40 @@ __global__ void __launch_bounds__(kThreads) k_sgd(const LwcSgdTensor* __restrict
         if (md) store_quad<ModelT>(md, j, c.len, dv, wq);
     }
 }
+// Pure low-precision training (no fp32 masters: the CIFAR recipes with --dtype bf16): weights, momentum and gradients
+// all in T; the arithmetic is fp32, the results are rounded once.
+template <typename T>
+__global__ void __launch_bounds__(kThreads) k_sgd_lowp(const LwcSgdTensor* __restrict__ tensors,
+                                                       const SgdChunk* __restrict__ chunks, LwcSgdDesc d) {
+    const SgdChunk c = chunks[blockIdx.x];
+    const LwcSgdTensor t = tensors[c.tensor];
+    T* w = reinterpret_cast<T*>(t.param) + c.start;
+    const T* g = reinterpret_cast<const T*>(t.grad) + c.start;
+    T* m = t.mom ? reinterpret_cast<T*>(t.mom) + c.start : nullptr;
+    const bool wv = vec_ok(w), gv = vec_ok(g), mv = m && vec_ok(m);
+    const int tid = threadIdx.x;
+    const float lr = d.lr_dev ? *d.lr_dev : d.lr;
+#pragma unroll 2
+    for (int it = 0; it < kQuadsPerThread; ++it) {
+        const int j = (it * kThreads + tid) * 4;
+        if (j >= c.len) break;
+        float wq[4], gq[4], mq[4] = {0.f, 0.f, 0.f, 0.f};
+        load_quad<T>(w, j, c.len, wv, wq);
+        load_quad<T>(g, j, c.len, gv, gq);
+        if (m && !d.first_step) load_quad<T>(m, j, c.len, mv, mq);
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+            float dd = fmaf(d.weight_decay, wq[k], gq[k] * d.grad_scale);
+            if (m) {
+                mq[k] = d.first_step ? dd : fmaf(d.momentum, mq[k], (1.0f - d.dampening) * dd);
+                dd = d.nesterov ? fmaf(d.momentum, mq[k], dd) : mq[k];
+            }
+            wq[k] = fmaf(-lr, dd, wq[k]);
+        }
+        store_quad<T>(w, j, c.len, wv, wq);
+        if (m) store_quad<T>(m, j, c.len, mv, mq);
+    }
+}
 }  // namespace lwc
 
 using namespace lwc;
@@ -113,6 +147,16 @@ extern "C" int lwc_sgd_step(LwcSgdPlan* P, const LwcSgdDesc* d, void* stream) {
     if (P->num_chunks == 0) return 0;
     cudaStream_t st = (cudaStream_t)stream;
     int rc;
+    if (d->param_dtype != LWC_F32) {
+        // weights, momentum and gradients share one 16-bit type
+        if (d->grad_dtype != d->param_dtype) return LWC_EINVAL;
+        const LwcSgdTensor* t = (const LwcSgdTensor*)P->d_tensors;
+        const SgdChunk* c = (const SgdChunk*)P->d_chunks;
+        if (d->param_dtype == LWC_BF16) k_sgd_lowp<__nv_bfloat16><<<P->num_chunks, kThreads, 0, st>>>(t, c, *d);
+        else if (d->param_dtype == LWC_F16) k_sgd_lowp<__half><<<P->num_chunks, kThreads, 0, st>>>(t, c, *d);
+        else return LWC_EINVAL;
+        return (int)cudaGetLastError();
+    }
     switch (d->grad_dtype) {
         case LWC_F32: rc = launch_sgd<float>(P, *d, st); break;
         case LWC_BF16: rc = launch_sgd<__nv_bfloat16>(P, *d, st); break;

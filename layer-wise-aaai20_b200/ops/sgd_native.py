@@ -46,11 +46,14 @@ def step_group(opt, gi, group, params):
     # split by (param dtype must be fp32), grad dtype
     subsets = {}
     for p in params:
-        if p.dtype != torch.float32 or not _same_dense_layout(p, p.grad):
+        lowp = p.dtype in (torch.bfloat16, torch.float16) and p.grad.dtype == p.dtype \
+            and opt._model_copy.get(id(p)) is None
+        if not (p.dtype == torch.float32 or lowp) or not _same_dense_layout(p, p.grad):
             opt._step_reference(group, [p])
             continue
-        subsets.setdefault(p.grad.dtype, []).append(p)
-    for gdt, ps in subsets.items():
+        # key: (grad dtype, param dtype) -- 16-bit weights without fp32 masters take the low-precision kernel
+        subsets.setdefault((p.grad.dtype, p.dtype), []).append(p)
+    for (gdt, pdt), ps in subsets.items():
         first = False
         bufs = None
         if mu != 0:
@@ -60,19 +63,22 @@ def step_group(opt, gi, group, params):
                 if "momentum_buffer" not in st or st["momentum_buffer"] is None:
                     st["momentum_buffer"] = torch.zeros_like(p, memory_format=torch.preserve_format)
                     first = True
+                if st["momentum_buffer"].dtype != p.dtype:        # e.g. a checkpoint written by another precision mode
+                    st["momentum_buffer"] = st["momentum_buffer"].to(p.dtype)
                 bufs.append(st["momentum_buffer"])
-        key = (gi, gdt) + tuple(p.data_ptr() for p in ps) + tuple(p.grad.data_ptr() for p in ps) + \
+        key = (gi, gdt, pdt) + tuple(p.data_ptr() for p in ps) + tuple(p.grad.data_ptr() for p in ps) + \
             (tuple(b.data_ptr() for b in bufs) if bufs else ())
-        plan = opt._plans.get((gi, gdt))
+        plan = opt._plans.get((gi, gdt, pdt))
         if plan is None or plan.key != key:
             if plan is not None:
                 lib.lwc_sgd_plan_destroy(plan.handle)
             handle, mdt = _build(opt, ps, bufs)
             plan = _Plan(key, handle, gdt, mdt)
-            opt._plans[(gi, gdt)] = plan
+            opt._plans[(gi, gdt, pdt)] = plan
         d = abi.LwcSgdDesc()
         d.num_tensors = len(ps)
         d.grad_dtype = abi.dtype_code(gdt)
+        d.param_dtype = abi.dtype_code(pdt)
         d.model_dtype = abi.dtype_code(plan.model_dtype) if plan.model_dtype is not None else abi.LWC_F32
         d.lr, d.momentum, d.dampening = float(group["lr"]), float(mu), float(group["dampening"])
         d.weight_decay, d.grad_scale = float(group["weight_decay"]), float(opt.grad_scale)

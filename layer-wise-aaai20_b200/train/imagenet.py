@@ -148,6 +148,7 @@ class Trainer:
         self.cuda_graph = bool(cuda_graph) and self.device.type == "cuda" and self.wrapper is None \
             and hasattr(self.exchanger.engine, "enable_graph_mode")
         self._shape_key, self._shape_run = None, 0
+        self._side = None
 
     def _model_in_group_order(self, groups):
         by_master = {id(m): p for m, p in zip(self.master_params, self.model_params)}
@@ -234,6 +235,19 @@ class Trainer:
             if self._shape_run > 3:
                 self.capture_graph(images, target, warmup=0)
                 return self._replay(images, target)
+            # steps that precede a capture run on a side stream: autograd state created on the legacy default stream
+            # makes the capture fail ("legacy stream depend on a capturing blocking stream")
+            if self._side is None:
+                self._side = torch.cuda.Stream(device=self.device)
+            cur = torch.cuda.current_stream()
+            self._side.wait_stream(cur)
+            with torch.cuda.stream(self._side):
+                if images.device != self.device:
+                    images = images.to(self.device, non_blocking=True)
+                    target = target.to(self.device, non_blocking=True)
+                res = self._step_body(images, target)
+            cur.wait_stream(self._side)
+            return res
         if images.device != self.device:
             images = images.to(self.device, non_blocking=True)
             target = target.to(self.device, non_blocking=True)

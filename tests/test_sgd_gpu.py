@@ -42,3 +42,31 @@ def test_fused_sgd_bf16_model_copy_and_grads():
     exp = ref - 0.05 * (d + 0.9 * d)
     assert torch.allclose(master[0], exp, atol=1e-5)
     assert torch.equal(model[0], master[0].detach().to(torch.bfloat16))
+
+
+@pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float16])
+def test_fused_sgd_low_precision_weights(dtype):
+    """16-bit weights without fp32 masters (dawn.py --dtype bf16): fp32 arithmetic, one rounding per step."""
+    from layerwise_b200 import _native
+    torch.manual_seed(0)
+    shapes = [(64,), (130, 33), (8193,), (3, 3, 64, 128)]
+    a = [torch.randn(s, device="cuda").to(dtype).requires_grad_(True) for s in shapes]
+    w = [t.detach().float() for t in a]                    # fp32 emulation of the same update
+    m = [None] * len(a)
+    opt = FusedSGD(a, lr=0.1, momentum=0.9, nesterov=True, weight_decay=5e-4)
+    n0 = _native.counters.kernels
+    for step in range(3):
+        for i, x in enumerate(a):
+            g = torch.randn_like(x)
+            x.grad = g.clone()
+            d = g.float() + 5e-4 * w[i]
+            m[i] = d if m[i] is None else 0.9 * m[i] + d
+            m[i] = m[i].to(dtype).float()                  # the momentum buffer is stored in `dtype`
+            w[i] = (w[i] - 0.1 * (d + 0.9 * m[i])).to(dtype).float()
+        opt.step()
+    assert _native.counters.kernels - n0 == 3              # one fused launch per step, no per-tensor fallback
+    tol = 2e-2 if dtype == torch.bfloat16 else 3e-3
+    for x, y in zip(a, w):
+        assert x.dtype == dtype
+        assert torch.allclose(x.float(), y, atol=tol, rtol=tol)
+    assert opt.state[a[0]]["momentum_buffer"].dtype == dtype
