@@ -19,23 +19,27 @@ def test_dawn_cli_on_gpu(tmp_path, network, extra):
     import dawn
     from layerwise_b200 import _native
     _native.counters.reset()
+    graph = ["--cuda_graph", "--max_batches", "6"] if network == "resnet9" else []      # capture after 3 eager batches
     summary = dawn.main(["--synthetic", "--epochs", "1", "--max_batches", "3", "--batch_size", "128", "--world_size", "1",
-                         "--network", network, "--dtype", "bf16", "--momentum", "0.9", "--log_dir", str(tmp_path)] + extra)
+                         "--network", network, "--dtype", "bf16", "--momentum", "0.9", "--log_dir", str(tmp_path)] + extra
+                        + graph)
     assert summary["epoch"] == 1 and summary["train loss"] == summary["train loss"]
     assert _native.counters.kernels > 0          # the native library really ran
 
 
-def test_imagenet_cli_on_gpu(tmp_path):
+@pytest.mark.parametrize("graph", [False, True])
+def test_imagenet_cli_on_gpu(tmp_path, graph):
     from layerwise_b200.train.imagenet_main import main
-    phases = json.dumps([{"ep": 0, "sz": 64, "bs": 16}, {"ep": [0, 1], "lr": [0.05, 0.1]}])
+    phases = json.dumps([{"ep": 0, "sz": 64, "bs": 16 if not graph else 8}, {"ep": [0, 1], "lr": [0.05, 0.1]}])
     cwd = os.getcwd()
     os.chdir(tmp_path)
     try:
         top1, top5 = main(["x", "--synthetic", "64", "--arch", "resnet50", "--phases", phases, "-j", "0", "--bf16",
                            "--logdir", str(tmp_path / "log"), "--compress", "layerwise", "--method", "Topk", "-K", "0.01",
-                           "--error_feedback", "--epochs", "1", "--no-bn-wd", "--init-bn0"])
-        assert 0.0 <= top1 <= 100.0 and os.path.exists(tmp_path / "sz16_checkpoint.path.tar")
-        ck = torch.load(tmp_path / "sz16_checkpoint.path.tar", weights_only=False)
+                           "--error_feedback", "--epochs", "1", "--no-bn-wd", "--init-bn0"] + (["--cuda-graph"] if graph else []))
+        name = "sz8_checkpoint.path.tar" if graph else "sz16_checkpoint.path.tar"
+        assert 0.0 <= top1 <= 100.0 and os.path.exists(tmp_path / name)
+        ck = torch.load(tmp_path / name, weights_only=False)
         assert ck["masters"] is not None and ck["ef_residual"] is not None
     finally:
         os.chdir(cwd)
