@@ -33,6 +33,7 @@ constexpr int BK = 64;
 constexpr int STAGES = 4;
 constexpr int THREADS = 192;
 constexpr int UMMA_K = 16;
+constexpr int NCBUF = 3;             // output / addend staging buffers: the addend of tile t+2 is in flight while t is written
 
 struct Params {
     int M, N, Kc, taps, kw, pad;     // rows (2-D mode), out channels, in channels per tap, taps, kernel width, padding
@@ -153,7 +154,7 @@ struct Smem {
     static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
     static constexpr int C_BYTES = BM * BN * 2;                 // one staging buffer (BN/64 swizzled 128x64 sub-tiles)
     static constexpr int C_OFF = STAGES * STAGE_BYTES;
-    static constexpr int BAR_OFF = C_OFF + 2 * C_BYTES;
+    static constexpr int BAR_OFF = C_OFF + NCBUF * C_BYTES;
     static constexpr int TOTAL = BAR_OFF + 256 + 1024;
 };
 
@@ -185,8 +186,8 @@ __global__ void __launch_bounds__(THREADS, 1) k_conv(const __grid_constant__ CUt
     uint64_t* empty = full + STAGES;
     uint64_t* tmem_full = empty + STAGES;      // [2]
     uint64_t* tmem_empty = tmem_full + 2;      // [2]
-    uint64_t* add_full = tmem_empty + 2;       // [2] addend tile landed in the staging buffer
-    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(add_full + 2);
+    uint64_t* add_full = tmem_empty + 2;       // [NCBUF] addend tile landed in the staging buffer
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(add_full + NCBUF);
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int num_tiles = p.tiles_m * p.tiles_n;
@@ -199,7 +200,8 @@ __global__ void __launch_bounds__(THREADS, 1) k_conv(const __grid_constant__ CUt
         asm volatile("prefetch.tensormap [%0];" ::"l"(&tmB) : "memory");
         asm volatile("prefetch.tensormap [%0];" ::"l"(&tmC) : "memory");
         for (int s = 0; s < STAGES; ++s) { mbar_init(&full[s], 1); mbar_init(&empty[s], 1); }
-        for (int a = 0; a < 2; ++a) { mbar_init(&tmem_full[a], 1); mbar_init(&tmem_empty[a], 4); mbar_init(&add_full[a], 1); }
+        for (int a = 0; a < 2; ++a) { mbar_init(&tmem_full[a], 1); mbar_init(&tmem_empty[a], 4); }
+        for (int a = 0; a < NCBUF; ++a) mbar_init(&add_full[a], 1);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     if (warp == 1) {
@@ -281,19 +283,23 @@ __global__ void __launch_bounds__(THREADS, 1) k_conv(const __grid_constant__ CUt
 #pragma unroll
             for (int h = 0; h < BN / 64; ++h) tma_load_2d(dst + h * (BM * 128), &tmD, &add_full[buf], tt.nt * BN + h * 64, tt.m0);
         };
-        if (has_add && leader && (int)blockIdx.x < num_tiles) prefetch_addend(blockIdx.x, 0);
+        if (has_add && leader) {               // two tiles ahead: the HBM latency of an addend tile exceeds one epilogue
+            if ((int)blockIdx.x < num_tiles) prefetch_addend(blockIdx.x, 0);
+            if ((int)(blockIdx.x + gridDim.x) < num_tiles) prefetch_addend(blockIdx.x + gridDim.x, 1);
+        }
         uint32_t tcount = 0;
         for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++tcount) {
             const TileCoord t = tile_coord(p, tile);
             const int co0 = t.nt * BN;
             const uint32_t as = tcount & 1, aph = (tcount >> 1) & 1;
-            uint8_t* cst = smem + S::C_OFF + (tcount & 1) * S::C_BYTES;
+            const uint32_t cbuf = tcount % NCBUF, cph = (tcount / NCBUF) & 1;
+            uint8_t* cst = smem + S::C_OFF + cbuf * S::C_BYTES;
             mbar_wait(&tmem_full[as], aph);
             tcgen05_fence_after();
             if (has_add) {
-                mbar_wait(&add_full[tcount & 1], aph);        // this tile's addend is in cst (its prefetch also guarded reuse)
+                mbar_wait(&add_full[cbuf], cph);              // this tile's addend is in cst (its prefetch also guarded reuse)
             } else {
-                if (leader) asm volatile("cp.async.bulk.wait_group.read 1;" ::: "memory");     // staging buffer free again
+                if (leader) asm volatile("cp.async.bulk.wait_group.read 2;" ::: "memory");     // staging buffer free again
                 epi_bar_sync();
             }
 #pragma unroll 1
@@ -391,10 +397,10 @@ __global__ void __launch_bounds__(THREADS, 1) k_conv(const __grid_constant__ CUt
                     else tma_store_2d(&tmC, cst + h * (BM * 128), co0 + h * 64, t.m0);
                 }
                 asm volatile("cp.async.bulk.commit_group;" ::: "memory");
-                if (has_add && tile + (int)gridDim.x < num_tiles) {
+                if (has_add && tile + 2 * (int)gridDim.x < num_tiles) {
                     // the other buffer was last read by the store issued one tile ago: wait for it, then refill it
                     asm volatile("cp.async.bulk.wait_group.read 1;" ::: "memory");
-                    prefetch_addend(tile + gridDim.x, (tcount + 1) & 1);
+                    prefetch_addend(tile + 2 * gridDim.x, (tcount + 2) % NCBUF);
                 }
             }
         }
