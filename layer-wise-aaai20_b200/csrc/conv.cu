@@ -145,6 +145,29 @@ __device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t r[32]) {
         : "r"(taddr) : "memory");
     asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
 }
+// Issue without waiting (several loads in flight); tmem_ld_wait() + use_after_wait() before the registers are read.
+__device__ __forceinline__ void tmem_ld32_issue(uint32_t taddr, uint32_t r[32]) {
+    asm volatile(
+        "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+        "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
+        "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
+        : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]),
+          "=r"(r[8]), "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15]),
+          "=r"(r[16]), "=r"(r[17]), "=r"(r[18]), "=r"(r[19]), "=r"(r[20]), "=r"(r[21]), "=r"(r[22]), "=r"(r[23]),
+          "=r"(r[24]), "=r"(r[25]), "=r"(r[26]), "=r"(r[27]), "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
+        : "r"(taddr) : "memory");
+}
+__device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
+// Ties the loaded registers to a point after the wait: without a data dependency the compiler may schedule
+// arithmetic on them above the wait.
+__device__ __forceinline__ void use_after_wait(uint32_t r[32]) {
+    asm volatile(""
+                 : "+r"(r[0]), "+r"(r[1]), "+r"(r[2]), "+r"(r[3]), "+r"(r[4]), "+r"(r[5]), "+r"(r[6]), "+r"(r[7]),
+                   "+r"(r[8]), "+r"(r[9]), "+r"(r[10]), "+r"(r[11]), "+r"(r[12]), "+r"(r[13]), "+r"(r[14]), "+r"(r[15]),
+                   "+r"(r[16]), "+r"(r[17]), "+r"(r[18]), "+r"(r[19]), "+r"(r[20]), "+r"(r[21]), "+r"(r[22]), "+r"(r[23]),
+                   "+r"(r[24]), "+r"(r[25]), "+r"(r[26]), "+r"(r[27]), "+r"(r[28]), "+r"(r[29]), "+r"(r[30]), "+r"(r[31])
+                 :: "memory");
+}
 __device__ __forceinline__ void epi_bar_sync() { asm volatile("bar.sync 1, 128;" ::: "memory"); }
 
 template <int BN>
@@ -302,10 +325,20 @@ __global__ void __launch_bounds__(THREADS, 1) k_conv(const __grid_constant__ CUt
                 if (leader) asm volatile("cp.async.bulk.wait_group.read 2;" ::: "memory");     // staging buffer free again
                 epi_bar_sync();
             }
-#pragma unroll 1
-            for (int c = 0; c < BN; c += 32) {
-                uint32_t v[32];
-                tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16) + as * BN + (uint32_t)c, v);
+            // all BN/32 accumulator chunks of this thread's row are requested back to back, one wait
+            uint32_t vall[BN / 32][32];
+#pragma unroll
+            for (int cc = 0; cc < BN / 32; ++cc)
+                tmem_ld32_issue(tmem_base + ((uint32_t)(q * 32) << 16) + as * BN + (uint32_t)(cc * 32), vall[cc]);
+            tmem_ld_wait();
+            tcgen05_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&tmem_empty[as]);                   // the row is in registers: accumulator may be overwritten
+#pragma unroll
+            for (int cc = 0; cc < BN / 32; ++cc) {
+                const int c = cc * 32;
+                uint32_t* v = vall[cc];
+                use_after_wait(v);
                 if (has_add) {
                     const uint8_t* asub = cst + (c / 64) * (BM * 128) + r * 128;
                     const int achunk0 = (c % 64) / 8;
@@ -337,9 +370,6 @@ __global__ void __launch_bounds__(THREADS, 1) k_conv(const __grid_constant__ CUt
                     *reinterpret_cast<uint4*>(sub + chunk * 16) = make_uint4(w[0], w[1], w[2], w[3]);
                 }
             }
-            tcgen05_fence_before();
-            __syncwarp();
-            if (lane == 0) mbar_arrive(&tmem_empty[as]);                   // accumulator may be overwritten
             asm volatile("fence.proxy.async.shared::cta;" ::: "memory");   // generic-proxy writes -> visible to TMA
             epi_bar_sync();
             if (p.stats) {
