@@ -206,11 +206,16 @@ int lwc_bn_forward(const void* x, void* y, const void* res, const float* gamma, 
                    float* mean, float* invstd, float* running_mean, float* running_var, float* workspace,
                    long long M, int C, int dtype, int training, int relu, float eps, float momentum, void* stream);
 /* same, and in training mode also increments *num_batches_tracked (int64 device scalar, nullable) inside the
- * statistics-finalize kernel, so nn.BatchNorm2d's counter costs no launch of its own */
+ * statistics-finalize kernel, so nn.BatchNorm2d's counter costs no launch of its own.  relu_mask (M*C/8 bytes,
+ * nullable): one bit per output element, set where the pre-activation is positive -- lwc_bn_backward_ex reads it
+ * instead of the saved output y (1/16 of the bytes; needed only when a residual was fused). */
 int lwc_bn_forward_ex(const void* x, void* y, const void* res, const float* gamma, const float* beta,
                       float* mean, float* invstd, float* running_mean, float* running_var, float* workspace,
                       long long M, int C, int dtype, int training, int relu, float eps, float momentum,
-                      long long* num_batches_tracked, void* stream);
+                      long long* num_batches_tracked, void* relu_mask, void* stream);
+int lwc_bn_backward_ex(const void* dy, const void* x, const void* y, void* dx, void* dres, const float* gamma,
+                       const float* beta, const float* mean, const float* invstd, float* dgamma, float* dbeta,
+                       float* workspace, long long M, int C, int dtype, int relu, const void* relu_mask, void* stream);
 int lwc_bn_backward(const void* dy, const void* x, const void* y, void* dx, void* dres, const float* gamma,
                     const float* beta, const float* mean, const float* invstd, float* dgamma, float* dbeta,
                     float* workspace, long long M, int C, int dtype, int relu, void* stream);

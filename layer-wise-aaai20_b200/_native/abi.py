@@ -88,7 +88,9 @@ def declare(lib: C.CDLL):
     sig("lwc_bn_forward", C.c_int, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, C.c_longlong, C.c_int, C.c_int, C.c_int,
         C.c_int, C.c_float, C.c_float, vp)
     sig("lwc_bn_forward_ex", C.c_int, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, C.c_longlong, C.c_int, C.c_int, C.c_int,
-        C.c_int, C.c_float, C.c_float, vp, vp)
+        C.c_int, C.c_float, C.c_float, vp, vp, vp)
+    sig("lwc_bn_backward_ex", C.c_int, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, C.c_longlong, C.c_int, C.c_int,
+        C.c_int, vp, vp)
     sig("lwc_bn_backward", C.c_int, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, C.c_longlong, C.c_int, C.c_int,
         C.c_int, vp)
     sig("lwc_maxpool_forward", C.c_int, vp, vp, vp, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int,

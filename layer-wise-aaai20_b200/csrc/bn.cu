@@ -46,6 +46,8 @@ struct Params {
     float* dbeta;
     float* partial;       // [nblk][2][C]
     long long* num_batches;   // nn.BatchNorm2d.num_batches_tracked, bumped by the finalize kernel (nullable)
+    unsigned char* mask;      // ReLU mask, one bit per element ([M][C/8] bytes): written by the forward apply when
+                              // non-NULL, read by the backward kernels instead of the saved output y (1/16 of its bytes)
     long long M;
     int C;
     int nblk;
@@ -339,12 +341,16 @@ __global__ void __launch_bounds__(THREADS) k_bn_apply(Params p, int use_running)
             unpack(xr[u], v);
             if (rs) unpack(rr[u], w);
 #pragma unroll
+            unsigned bits = 0;
+#pragma unroll
             for (int k = 0; k < 8; ++k) {
                 float o = fmaf(v[k], a[k], b[k]);
                 if (rs) o += w[k];
+                bits |= (o > 0.0f ? 1u : 0u) << k;
                 v[k] = p.relu ? fmaxf(o, 0.0f) : o;
             }
             st8<T>(y + (size_t)ru * p.C, v);
+            if (p.mask) p.mask[(size_t)ru * (p.C >> 3) + m.cg] = (unsigned char)bits;
         }
     }
 }
@@ -360,8 +366,11 @@ __global__ void __launch_bounds__(THREADS) k_bn_bwd_reduce(Params p) {
     float sd[8] = {0, 0, 0, 0, 0, 0, 0, 0}, sx[8] = {0, 0, 0, 0, 0, 0, 0, 0};
     if (m.active) {
         const int c0 = m.cg * VEC;
-        const bool have_y = p.y != nullptr;
-        const bool recompute = p.relu && !have_y;
+        const bool have_mask = p.mask != nullptr;
+        const bool have_y = !have_mask && p.y != nullptr;
+        const bool recompute = p.relu && !have_y && !have_mask;
+        const unsigned char* mk = have_mask ? p.mask + m.cg : nullptr;
+        const size_t mstride = (size_t)(p.C >> 3);
         float fa[8], fb[8];
 #pragma unroll
         for (int k = 0; k < 8; ++k) {
@@ -373,6 +382,7 @@ __global__ void __launch_bounds__(THREADS) k_bn_bwd_reduce(Params p) {
         const T* y = reinterpret_cast<const T*>(p.y) + c0;
         for (long long r = m.row0 + m.ry; r < m.row1; r += (long long)ROWS * m.rpp) {
             Raw<T> xr[ROWS], dr[ROWS], yr[ROWS];
+            unsigned mb[ROWS];
 #pragma unroll
             for (int u = 0; u < ROWS; ++u) {
                 const long long ru = r + (long long)u * m.rpp;
@@ -380,6 +390,7 @@ __global__ void __launch_bounds__(THREADS) k_bn_bwd_reduce(Params p) {
                     ldraw<T>(x + (size_t)ru * p.C, xr[u]);
                     ldraw<T>(dy + (size_t)ru * p.C, dr[u]);
                     if (p.relu && have_y) ldraw<T>(y + (size_t)ru * p.C, yr[u]);
+                    if (p.relu && have_mask) mb[u] = mk[(size_t)ru * mstride];
                 }
             }
 #pragma unroll
@@ -394,8 +405,12 @@ __global__ void __launch_bounds__(THREADS) k_bn_bwd_reduce(Params p) {
                 for (int k = 0; k < 8; ++k) {
                     float d = dv[k];
                     if (p.relu) {
-                        const float yy = recompute ? fmaf(xv[k], fa[k], fb[k]) : yv[k];
-                        if (!(yy > 0.0f)) d = 0.0f;
+                        if (have_mask) {
+                            if (!((mb[u] >> k) & 1u)) d = 0.0f;
+                        } else {
+                            const float yy = recompute ? fmaf(xv[k], fa[k], fb[k]) : yv[k];
+                            if (!(yy > 0.0f)) d = 0.0f;
+                        }
                     }
                     sd[k] += d;
                     sx[k] = fmaf(d, xv[k], sx[k]);
@@ -431,8 +446,11 @@ __global__ void __launch_bounds__(THREADS) k_bn_bwd_apply(Params p) {
     const Map m = make_map(p);
     if (!m.active) return;
     const int c0 = m.cg * VEC;
-    const bool have_y = p.y != nullptr;
-    const bool recompute = p.relu && !have_y;
+    const bool have_mask = p.mask != nullptr;
+    const bool have_y = !have_mask && p.y != nullptr;
+    const bool recompute = p.relu && !have_y && !have_mask;
+    const unsigned char* mk = have_mask ? p.mask + m.cg : nullptr;
+    const size_t mstride = (size_t)(p.C >> 3);
     float A[8], B[8], Cc[8], fb[8];
     const float invM = 1.0f / (float)p.M;
 #pragma unroll
@@ -450,6 +468,7 @@ __global__ void __launch_bounds__(THREADS) k_bn_bwd_apply(Params p) {
     T* dr = p.dres ? reinterpret_cast<T*>(p.dres) + c0 : nullptr;
     for (long long r = m.row0 + m.ry; r < m.row1; r += (long long)ROWS * m.rpp) {
         Raw<T> xr[ROWS], gr[ROWS], yr[ROWS];
+        unsigned mb[ROWS];
 #pragma unroll
         for (int u = 0; u < ROWS; ++u) {
             const long long ru = r + (long long)u * m.rpp;
@@ -457,6 +476,7 @@ __global__ void __launch_bounds__(THREADS) k_bn_bwd_apply(Params p) {
                 ldraw<T>(x + (size_t)ru * p.C, xr[u]);
                 ldraw<T>(dy + (size_t)ru * p.C, gr[u]);
                 if (p.relu && have_y) ldraw<T>(y + (size_t)ru * p.C, yr[u]);
+                if (p.relu && have_mask) mb[u] = mk[(size_t)ru * mstride];
             }
         }
 #pragma unroll
@@ -471,8 +491,12 @@ __global__ void __launch_bounds__(THREADS) k_bn_bwd_apply(Params p) {
             for (int k = 0; k < 8; ++k) {
                 float d = dv[k];
                 if (p.relu) {
-                    const float yy = recompute ? fmaf(xv[k], A[k], fb[k]) : yv[k];
-                    if (!(yy > 0.0f)) d = 0.0f;
+                    if (have_mask) {
+                        if (!((mb[u] >> k) & 1u)) d = 0.0f;
+                    } else {
+                        const float yy = recompute ? fmaf(xv[k], A[k], fb[k]) : yv[k];
+                        if (!(yy > 0.0f)) d = 0.0f;
+                    }
                 }
                 dv[k] = d;
                 xv[k] = fmaf(A[k], d, fmaf(B[k], xv[k], Cc[k]));
@@ -526,22 +550,25 @@ extern "C" size_t lwc_bn_workspace_bytes(long long M, int C) {
 extern "C" int lwc_bn_forward_ex(const void* x, void* y, const void* res, const float* gamma, const float* beta,
                                  float* mean, float* invstd, float* running_mean, float* running_var, float* workspace,
                                  long long M, int C, int dtype, int training, int relu, float eps, float momentum,
-                                 long long* num_batches_tracked, void* stream);
+                                 long long* num_batches_tracked, void* relu_mask, void* stream);
 
 extern "C" int lwc_bn_forward(const void* x, void* y, const void* res, const float* gamma, const float* beta,
                               float* mean, float* invstd, float* running_mean, float* running_var, float* workspace,
                               long long M, int C, int dtype, int training, int relu, float eps, float momentum,
                               void* stream) {
     return lwc_bn_forward_ex(x, y, res, gamma, beta, mean, invstd, running_mean, running_var, workspace, M, C, dtype,
-                             training, relu, eps, momentum, nullptr, stream);
+                             training, relu, eps, momentum, nullptr, nullptr, stream);
 }
 
 // num_batches_tracked (int64 device scalar, nullable): incremented by one in training mode inside the finalize
 // kernel -- the module's counter costs no launch of its own.
+// relu_mask (M * C / 8 bytes, nullable): one bit per output element, set where the pre-activation is positive; hand it
+// to lwc_bn_backward_ex instead of y and the backward kernels read 1/16 of the bytes (matters when a residual was
+// fused: without one the mask is recomputed from x and neither y nor a mask is needed).
 extern "C" int lwc_bn_forward_ex(const void* x, void* y, const void* res, const float* gamma, const float* beta,
                                  float* mean, float* invstd, float* running_mean, float* running_var, float* workspace,
                                  long long M, int C, int dtype, int training, int relu, float eps, float momentum,
-                                 long long* num_batches_tracked, void* stream) {
+                                 long long* num_batches_tracked, void* relu_mask, void* stream) {
     if (!x || !y || M <= 0 || C <= 0 || (C % VEC)) return LWC_EINVAL;
     if (training && (!mean || !invstd || !workspace)) return LWC_EINVAL;
     if (!training && (!running_mean || !running_var)) return LWC_EINVAL;
@@ -552,6 +579,7 @@ extern "C" int lwc_bn_forward_ex(const void* x, void* y, const void* res, const 
     p.running_mean = running_mean; p.running_var = running_var; p.partial = workspace;
     p.M = M; p.C = C; p.relu = relu; p.eps = eps; p.momentum = momentum;
     p.num_batches = training ? num_batches_tracked : nullptr;
+    p.mask = reinterpret_cast<unsigned char*>(relu_mask);
     dim3 grid;
     if (training) {
         // the pure-read statistics pass (50 registers) likes 4 CTAs per SM; the apply pass 2
@@ -566,11 +594,23 @@ extern "C" int lwc_bn_forward_ex(const void* x, void* y, const void* res, const 
 
 // y: the forward output (needed only when relu=1 and a residual was fused; NULL -> the ReLU mask is recomputed
 // from x, gamma, beta); dres: gradient of the fused residual input (nullable).
+extern "C" int lwc_bn_backward_ex(const void* dy, const void* x, const void* y, void* dx, void* dres, const float* gamma,
+                                  const float* beta, const float* mean, const float* invstd, float* dgamma, float* dbeta,
+                                  float* workspace, long long M, int C, int dtype, int relu, const void* relu_mask, void* stream);
+
 extern "C" int lwc_bn_backward(const void* dy, const void* x, const void* y, void* dx, void* dres, const float* gamma,
                                const float* beta, const float* mean, const float* invstd, float* dgamma, float* dbeta, float* workspace,
                                long long M, int C, int dtype, int relu, void* stream) {
+    return lwc_bn_backward_ex(dy, x, y, dx, dres, gamma, beta, mean, invstd, dgamma, dbeta, workspace, M, C, dtype, relu, nullptr,
+                              stream);
+}
+
+// relu_mask: the bit mask written by lwc_bn_forward_ex (takes precedence over y).
+extern "C" int lwc_bn_backward_ex(const void* dy, const void* x, const void* y, void* dx, void* dres, const float* gamma,
+                                  const float* beta, const float* mean, const float* invstd, float* dgamma, float* dbeta,
+                                  float* workspace, long long M, int C, int dtype, int relu, const void* relu_mask, void* stream) {
     if (!dy || !x || !dx || !mean || !invstd || !dgamma || !dbeta || !workspace) return LWC_EINVAL;
-    if (relu && !y && dres) return LWC_EINVAL;    // with a fused residual the mask needs the saved output
+    if (relu && !y && !relu_mask && dres) return LWC_EINVAL;    // with a fused residual the mask needs y or the bit mask
     if (M <= 0 || C <= 0 || (C % VEC)) return LWC_EINVAL;
     cudaStream_t st = (cudaStream_t)stream;
     Params p;
@@ -579,6 +619,7 @@ extern "C" int lwc_bn_backward(const void* dy, const void* x, const void* y, voi
     p.mean = const_cast<float*>(mean); p.invstd = const_cast<float*>(invstd);
     p.dgamma = dgamma; p.dbeta = dbeta; p.partial = workspace;
     p.M = M; p.C = C; p.relu = relu;
+    p.mask = reinterpret_cast<unsigned char*>(const_cast<void*>(relu_mask));
     dim3 grid;
     plan_grid(M, C, &p.nblk, &p.rows_per_blk, &grid);
     LWC_BN_DISPATCH(dtype, k_bn_bwd_reduce<T><<<grid, THREADS, 0, st>>>(p));

@@ -71,26 +71,30 @@ class _BatchNormAct(torch.autograd.Function):
             mean = torch.empty(Cc, dtype=torch.float32, device=x.device)
             invstd = torch.empty(Cc, dtype=torch.float32, device=x.device)
             ws_ptr = _workspace(int(lib.lwc_bn_workspace_bytes(M, Cc)), x.device).data_ptr()
+        # a fused residual makes the ReLU mask depend on the output: keep it as one bit per element instead of re-reading y
+        mask = None
+        if training and relu and residual is not None:
+            mask = torch.empty(M * Cc // 8, dtype=torch.uint8, device=x.device)
         rc = lib.lwc_bn_forward_ex(x.data_ptr(), y.data_ptr(), _ptr(residual), _ptr(weight), _ptr(bias), _ptr(mean),
                                    _ptr(invstd), _ptr(running_mean), _ptr(running_var), ws_ptr, M, Cc,
                                    abi.dtype_code(x.dtype), int(training), int(relu), float(eps), float(momentum),
-                                   _ptr(num_batches_tracked), C.c_void_p(st))
+                                   _ptr(num_batches_tracked), _ptr(mask), C.c_void_p(st))
         abi.check(rc, "lwc_bn_forward_ex")
         _native.counters.add(3 if training else 1)
         ctx.training, ctx.relu, ctx.has_res = training, relu, residual is not None
         ctx.eps = eps
         # the ReLU mask is recomputed from x unless a residual was fused (then it depends on y)
-        need_y = relu and (residual is not None or not training)
+        need_y = relu and (residual is not None or not training) and mask is None
         if training:
-            ctx.save_for_backward(x, y if need_y else None, weight, mean, invstd, bias)
+            ctx.save_for_backward(x, y if need_y else None, weight, mean, invstd, bias, mask)
         else:
-            ctx.save_for_backward(x, y if need_y else None, weight, running_mean, running_var, bias)
+            ctx.save_for_backward(x, y if need_y else None, weight, running_mean, running_var, bias, None)
         return y
 
     @staticmethod
     def backward(ctx, dy):
         lib = _native.lib()
-        x, y, weight, mean, invstd, bias = ctx.saved_tensors
+        x, y, weight, mean, invstd, bias, mask = ctx.saved_tensors
         M, Cc = _rows_channels(x)
         if _rows_channels(dy) is None or dy.stride() != x.stride():
             dy = dy.contiguous(memory_format=torch.channels_last) if x.dim() == 4 else dy.contiguous()
@@ -110,10 +114,10 @@ class _BatchNormAct(torch.autograd.Function):
         dbeta = torch.empty(Cc, dtype=torch.float32, device=x.device)
         ws_ptr = _workspace(int(lib.lwc_bn_workspace_bytes(M, Cc)), x.device).data_ptr()
         st = torch.cuda.current_stream().cuda_stream
-        rc = lib.lwc_bn_backward(dy.data_ptr(), x.data_ptr(), _ptr(y), dx.data_ptr(), _ptr(dres), _ptr(weight),
-                                 _ptr(bias), mean.data_ptr(), invstd.data_ptr(), dgamma.data_ptr(), dbeta.data_ptr(), ws_ptr,
-                                 M, Cc, abi.dtype_code(x.dtype), int(ctx.relu), C.c_void_p(st))
-        abi.check(rc, "lwc_bn_backward")
+        rc = lib.lwc_bn_backward_ex(dy.data_ptr(), x.data_ptr(), _ptr(y), dx.data_ptr(), _ptr(dres), _ptr(weight),
+                                    _ptr(bias), mean.data_ptr(), invstd.data_ptr(), dgamma.data_ptr(), dbeta.data_ptr(), ws_ptr,
+                                    M, Cc, abi.dtype_code(x.dtype), int(ctx.relu), _ptr(mask), C.c_void_p(st))
+        abi.check(rc, "lwc_bn_backward_ex")
         _native.counters.add(3)
         return (dx, dgamma if weight is not None else None, dbeta if weight is not None else None, None, None,
                 dres, None, None, None, None, None)

@@ -91,3 +91,22 @@ def test_num_batches_tracked_is_bumped_by_the_finalize_kernel():
     bn(x)
     torch.cuda.synchronize()
     assert int(bn.num_batches_tracked) == 3
+
+
+def test_relu_bitmask_replaces_saved_output():
+    """With a fused residual the backward reads a 1-bit-per-element mask written by the forward, not y."""
+    from layerwise_b200.ops import bn as bnops
+    torch.manual_seed(0)
+    x = torch.randn(6, 64, 9, 7, device="cuda").to(torch.bfloat16).contiguous(memory_format=torch.channels_last).requires_grad_(True)
+    r = torch.randn_like(x).requires_grad_(True)
+    w = torch.rand(64, device="cuda").add_(0.5).requires_grad_(True)
+    b = torch.randn(64, device="cuda").requires_grad_(True)
+    y = bnops.batch_norm_act(x, w, b, torch.zeros(64, device="cuda"), torch.ones(64, device="cuda"), r, True, 0.1, 1e-5, True)
+    saved = y.grad_fn.saved_tensors
+    assert saved[1] is None and saved[6] is not None and saved[6].dtype == torch.uint8      # no y, a mask
+    mask = saved[6].view(6 * 9 * 7, 8)
+    bits = torch.stack([(mask >> k) & 1 for k in range(8)], dim=-1).reshape(6, 9, 7, 64).permute(0, 3, 1, 2).bool()
+    assert torch.equal(bits, y > 0)
+    dy = torch.randn_like(y)
+    y.backward(dy)
+    assert torch.equal(r.grad, dy * (y > 0))
