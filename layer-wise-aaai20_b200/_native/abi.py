@@ -104,6 +104,7 @@ def declare(lib: C.CDLL):
     sig("lwc_conv_forward", C.c_int, vp, vp, vp, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, vp,
         C.c_int, vp, vp)
     sig("lwc_conv1x1_add", C.c_int, vp, vp, vp, vp, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, vp)
+    sig("lwc_conv1x1_add_mask", C.c_int, vp, vp, vp, vp, vp, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, vp)
     sig("lwc_stem_wgrad_workspace_bytes", C.c_size_t, C.c_int, C.c_int)
     sig("lwc_stem_wgrad", C.c_int, vp, vp, vp, vp, C.c_int, C.c_int, C.c_int, C.c_int, C.c_float, vp)
     sig("lwc_sgd_plan_create", C.c_int, c_void_pp, C.POINTER(LwcSgdTensor), i32)

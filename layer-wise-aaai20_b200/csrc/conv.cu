@@ -44,6 +44,7 @@ struct Params {
     const float* bias;
     float* stats;                    // [tiles_m][2][N] per-tile column sums / sums of squares, or NULL
     const __nv_bfloat16* addend;     // optional [M][N] tensor added in the epilogue (2-D mode): Y = conv(X) + addend
+    const unsigned char* mask;       // optional [M][N/8] bit mask (2-D mode, N % 128 == 0): outputs whose bit is 0 are zeroed
 };
 
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
@@ -325,6 +326,20 @@ __global__ void __launch_bounds__(THREADS, 1) k_conv(const __grid_constant__ CUt
                 if (leader) asm volatile("cp.async.bulk.wait_group.read 2;" ::: "memory");     // staging buffer free again
                 epi_bar_sync();
             }
+            // ReLU bit mask of this thread's output row (BN/8 bytes), requested before the accumulator wait
+            uint32_t mbits[BN / 32];
+            const bool has_mask = p.mask != nullptr && !p.mode4d;
+            if (has_mask) {
+                const bool in = t.m0 + r < p.M;
+                const unsigned char* mp = p.mask + (size_t)(in ? t.m0 + r : 0) * (p.N >> 3) + (co0 >> 3);
+                if constexpr (BN == 128) {
+                    const uint4 mv = *reinterpret_cast<const uint4*>(mp);
+                    mbits[0] = mv.x; mbits[1] = mv.y; mbits[2] = mv.z; mbits[3] = mv.w;
+                } else {
+                    const uint2 mv = *reinterpret_cast<const uint2*>(mp);
+                    mbits[0] = mv.x; mbits[1] = mv.y;
+                }
+            }
             // all BN/32 accumulator chunks of this thread's row are requested back to back, one wait
             uint32_t vall[BN / 32][32];
 #pragma unroll
@@ -352,6 +367,11 @@ __global__ void __launch_bounds__(THREADS, 1) k_conv(const __grid_constant__ CUt
                             v[j * 8 + 2 * e + 1] = __float_as_uint(__uint_as_float(v[j * 8 + 2 * e + 1]) + __uint_as_float(aw[e] & 0xffff0000u));
                         }
                     }
+                }
+                if (has_mask) {                                           // bit j of mbits[cc] <-> column c + j
+#pragma unroll
+                    for (int j = 0; j < 32; ++j)
+                        if (!((mbits[cc] >> j) & 1u)) v[j] = 0u;
                 }
                 uint8_t* sub = cst + (c / 64) * (BM * 128) + r * 128;     // 128x64 sub-tile, 128-byte rows
                 const int chunk0 = (c % 64) / 8;
@@ -510,29 +530,41 @@ extern "C" int lwc_conv_tiles_m(int Nimg, int H, int W, int kh, int* rows_per_ti
 //              used un-transposed for the data gradient dX = dY * W)
 // stats (optional): [tiles_m][2][Cout] fp32 per-tile sums / sums of squares of the bf16 outputs.
 static int conv_forward_impl(const void* x, const void* wt, void* y, int Nimg, int H, int W, int Cin, int Cout, int kh,
-                             int b_mn, const float* bias, int relu, float* stats, const void* addend, void* stream);
+                             int b_mn, const float* bias, int relu, float* stats, const void* addend, const void* mask,
+                             void* stream);
 
 extern "C" int lwc_conv_forward(const void* x, const void* wt, void* y, int Nimg, int H, int W, int Cin, int Cout, int kh,
                                 int b_mn, const float* bias, int relu, float* stats, void* stream) {
-    return conv_forward_impl(x, wt, y, Nimg, H, W, Cin, Cout, kh, b_mn, bias, relu, stats, nullptr, stream);
+    return conv_forward_impl(x, wt, y, Nimg, H, W, Cin, Cout, kh, b_mn, bias, relu, stats, nullptr, nullptr, stream);
 }
 
 // 1x1 only: Y = conv(X) + addend, addend bf16 with the shape of Y (used for dX = dY * W + d_identity at residual forks).
 extern "C" int lwc_conv1x1_add(const void* x, const void* wt, const void* addend, void* y, int Nimg, int H, int W, int Cin,
                                int Cout, int b_mn, void* stream) {
     if (!addend) return LWC_EINVAL;
-    return conv_forward_impl(x, wt, y, Nimg, H, W, Cin, Cout, 1, b_mn, nullptr, 0, nullptr, addend, stream);
+    return conv_forward_impl(x, wt, y, Nimg, H, W, Cin, Cout, 1, b_mn, nullptr, 0, nullptr, addend, nullptr, stream);
+}
+
+// Same, and outputs whose bit in relu_mask ([M][Cout/8] bytes, bit j of byte b <-> channel 8 b + j; the layout written by
+// lwc_bn_forward_ex) is 0 are zeroed: Y = (conv(X) + addend) * mask.  The data gradient at a residual fork arrives at the
+// producing block already multiplied with that block's ReLU mask, so its batch-norm backward neither reads a mask nor
+// writes a separate residual gradient.  addend may be NULL.  Cout % 128 == 0.
+extern "C" int lwc_conv1x1_add_mask(const void* x, const void* wt, const void* addend, const void* relu_mask, void* y, int Nimg,
+                                    int H, int W, int Cin, int Cout, int b_mn, void* stream) {
+    if (!relu_mask || (Cout % 128)) return LWC_EINVAL;
+    return conv_forward_impl(x, wt, y, Nimg, H, W, Cin, Cout, 1, b_mn, nullptr, 0, nullptr, addend, relu_mask, stream);
 }
 
 static int conv_forward_impl(const void* x, const void* wt, void* y, int Nimg, int H, int W, int Cin, int Cout, int kh,
-                             int b_mn, const float* bias, int relu, float* stats, const void* addend, void* stream) {
+                             int b_mn, const float* bias, int relu, float* stats, const void* addend, const void* mask,
+                             void* stream) {
     if (!x || !wt || !y || Nimg <= 0 || H <= 0 || W <= 0) return LWC_EINVAL;
     if ((Cin % 64) || (Cout % 64) || (kh != 1 && kh != 3) || (b_mn && kh != 1)) return LWC_EINVAL;
     ensure_context();
     cudaStream_t st = (cudaStream_t)stream;
     Params p;
     memset(&p, 0, sizeof(p));
-    p.N = Cout; p.Kc = Cin; p.taps = kh * kh; p.kw = kh; p.pad = kh / 2; p.relu = relu; p.bias = bias; p.stats = stats; p.addend = (const __nv_bfloat16*)addend;
+    p.N = Cout; p.Kc = Cin; p.taps = kh * kh; p.kw = kh; p.pad = kh / 2; p.relu = relu; p.bias = bias; p.stats = stats; p.addend = (const __nv_bfloat16*)addend; p.mask = (const unsigned char*)mask;
     p.H = H; p.W = W; p.Nimg = Nimg;
     const int BN = (Cout % 128 == 0) ? 128 : 64;
     p.tiles_n = Cout / BN;

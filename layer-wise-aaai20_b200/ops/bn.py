@@ -58,6 +58,8 @@ def _ptr(t):
 
 
 class _BatchNormAct(torch.autograd.Function):
+    last_mask = (None, None)      # (bit mask, taken-flag) of the most recent forward, picked up by batch_norm_act
+
     @staticmethod
     def forward(ctx, x, weight, bias, running_mean, running_var, residual, training, momentum, eps, relu,
                 num_batches_tracked=None):
@@ -85,6 +87,9 @@ class _BatchNormAct(torch.autograd.Function):
         ctx.eps = eps
         # the ReLU mask is recomputed from x unless a residual was fused (then it depends on y)
         need_y = relu and (residual is not None or not training) and mask is None
+        # a consumer (ops.conv.fork_conv1x1) may take over the masking of the incoming gradient: it flips taken[0]
+        ctx.mask_taken = [False] if mask is not None else None
+        _BatchNormAct.last_mask = (mask, ctx.mask_taken)
         if training:
             ctx.save_for_backward(x, y if need_y else None, weight, mean, invstd, bias, mask)
         else:
@@ -109,15 +114,24 @@ class _BatchNormAct(torch.autograd.Function):
             return (dx, (g.float() * xhat).sum(dims), g.float().sum(dims), None, None,
                     g if ctx.has_res else None, None, None, None, None, None)
         dx = torch.empty_like(x)
-        dres = torch.empty_like(x) if ctx.has_res else None
+        premasked = ctx.mask_taken is not None and ctx.mask_taken[0]
+        if premasked:
+            # the consumer's backward already multiplied dy with this layer's ReLU mask: no mask to read, and the
+            # gradient of the residual branch IS dy -- nothing to write
+            mask, y, relu_flag, dres = None, None, 0, None
+        else:
+            relu_flag = int(ctx.relu)
+            dres = torch.empty_like(x) if ctx.has_res else None
         dgamma = torch.empty(Cc, dtype=torch.float32, device=x.device)
         dbeta = torch.empty(Cc, dtype=torch.float32, device=x.device)
         ws_ptr = _workspace(int(lib.lwc_bn_workspace_bytes(M, Cc)), x.device).data_ptr()
         st = torch.cuda.current_stream().cuda_stream
         rc = lib.lwc_bn_backward_ex(dy.data_ptr(), x.data_ptr(), _ptr(y), dx.data_ptr(), _ptr(dres), _ptr(weight),
                                     _ptr(bias), mean.data_ptr(), invstd.data_ptr(), dgamma.data_ptr(), dbeta.data_ptr(), ws_ptr,
-                                    M, Cc, abi.dtype_code(x.dtype), int(ctx.relu), _ptr(mask), C.c_void_p(st))
+                                    M, Cc, abi.dtype_code(x.dtype), relu_flag, _ptr(mask), C.c_void_p(st))
         abi.check(rc, "lwc_bn_backward_ex")
+        if premasked and ctx.has_res:
+            dres = dy
         _native.counters.add(3)
         return (dx, dgamma if weight is not None else None, dbeta if weight is not None else None, None, None,
                 dres, None, None, None, None, None)
@@ -127,8 +141,14 @@ def batch_norm_act(x, weight, bias, running_mean, running_var, residual=None, tr
                    momentum=0.1, eps=1e-5, relu=False, num_batches_tracked=None):
     """``relu?(batch_norm(x) + residual?)`` in one fused pass structure (see module docstring).
     ``num_batches_tracked`` (int64 CUDA scalar) is incremented inside the statistics-finalize kernel."""
-    return _BatchNormAct.apply(x, weight, bias, running_mean, running_var, residual, training, momentum, eps, relu,
-                               num_batches_tracked)
+    _BatchNormAct.last_mask = (None, None)
+    y = _BatchNormAct.apply(x, weight, bias, running_mean, running_var, residual, training, momentum, eps, relu,
+                            num_batches_tracked)
+    mask, taken = _BatchNormAct.last_mask
+    if mask is not None:
+        y.relu_mask, y.relu_mask_taken = mask, taken       # see ops.conv.fork_conv1x1
+        _BatchNormAct.last_mask = (None, None)
+    return y
 
 
 def maybe_batch_norm(module, x, residual=None, relu=False):

@@ -11,6 +11,7 @@ CIFAR10/dawn.py:23-35).
 from __future__ import annotations
 
 import ctypes as C
+import os
 from typing import Optional, Tuple
 
 import torch
@@ -134,18 +135,33 @@ def maybe_conv2d(module, x):
 
 
 # ---- residual fork: conv1x1(x) and the identity branch share one fused backward --------------------------------
-def conv1x1_dgrad_add(dy: torch.Tensor, weight: torch.Tensor, addend: torch.Tensor) -> torch.Tensor:
-    """``dX = dY * W + addend`` in one pass of the native kernel (W = forward weight ``[Cout, Cin, 1, 1]``)."""
+def conv1x1_dgrad_add(dy: torch.Tensor, weight: torch.Tensor, addend: torch.Tensor,
+                      relu_mask: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """``dX = dY * W + addend`` in one pass of the native kernel (W = forward weight ``[Cout, Cin, 1, 1]``); with
+    ``relu_mask`` (the bit mask a fused batch-norm wrote for the tensor ``X``) also ``dX *= mask``."""
     lib = _native.lib()
     n, co, h, w = dy.shape
     ci = weight.shape[1]
     dx = torch.empty((n, ci, h, w), dtype=dy.dtype, device=dy.device, memory_format=torch.channels_last)
     st = torch.cuda.current_stream().cuda_stream
-    rc = lib.lwc_conv1x1_add(dy.data_ptr(), weight.data_ptr(), addend.data_ptr(), dx.data_ptr(), n, h, w, co, ci, 1,
-                             C.c_void_p(st))
-    abi.check(rc, "lwc_conv1x1_add")
+    if relu_mask is not None:
+        rc = lib.lwc_conv1x1_add_mask(dy.data_ptr(), weight.data_ptr(), addend.data_ptr(), relu_mask.data_ptr(), dx.data_ptr(),
+                                      n, h, w, co, ci, 1, C.c_void_p(st))
+        abi.check(rc, "lwc_conv1x1_add_mask")
+    else:
+        rc = lib.lwc_conv1x1_add(dy.data_ptr(), weight.data_ptr(), addend.data_ptr(), dx.data_ptr(), n, h, w, co, ci, 1,
+                                 C.c_void_p(st))
+        abi.check(rc, "lwc_conv1x1_add")
     _native.counters.add(1)
     return dx
+
+
+def apply_bitmask(t: torch.Tensor, mask: torch.Tensor) -> torch.Tensor:
+    """``t * mask`` for a channels-last ``t`` [N,C,H,W] and a bit mask [N*H*W*C/8] bytes (bit j of byte b <-> channel
+    8 b + j of the same pixel): the plain-op counterpart of the kernel epilogue."""
+    n, c, h, w = t.shape
+    bits = torch.stack([(mask >> k) & 1 for k in range(8)], dim=-1).reshape(n, h, w, c).permute(0, 3, 1, 2)
+    return t * bits.to(t.dtype)
 
 
 class _ForkConv1x1(torch.autograd.Function):
@@ -154,32 +170,39 @@ class _ForkConv1x1(torch.autograd.Function):
     gradient runs on the tcgen05 kernel whose epilogue adds the skip-connection gradient on the way out."""
 
     @staticmethod
-    def forward(ctx, x, weight):
-        ctx.save_for_backward(x, weight)
+    def forward(ctx, x, weight, relu_mask=None):
+        ctx.save_for_backward(x, weight, relu_mask)
         y = torch.nn.functional.conv2d(x, weight)
         return y, x.view_as(x)
 
     @staticmethod
     def backward(ctx, dy, d_identity):
-        x, weight = ctx.saved_tensors
+        x, weight, relu_mask = ctx.saved_tensors
         dx = dw = None
         if not _nhwc(dy):
             dy = dy.contiguous(memory_format=torch.channels_last)
         if ctx.needs_input_grad[0]:
             if d_identity is not None and _nhwc(d_identity) and d_identity.dtype == dy.dtype:
-                dx = conv1x1_dgrad_add(dy, weight, d_identity)
+                dx = conv1x1_dgrad_add(dy, weight, d_identity, relu_mask)
             else:
                 dx, _ = conv_forward(dy, weight, b_mn=True, out_channels=weight.shape[1])
                 if d_identity is not None:
                     dx = dx + d_identity
+                if relu_mask is not None:           # this function promised the producer a masked gradient
+                    dx = apply_bitmask(dx, relu_mask)
         if ctx.needs_input_grad[1]:
             dw = torch.ops.aten.convolution_backward(dy, x, weight, None, [1, 1], [0, 0], [1, 1], False, [0, 0], 1,
                                                      [False, True, False])[1]
-        return dx, dw
+        return dx, dw, None
 
 
 def fork_conv1x1(module, x):
-    """``(module(x), x)`` with the fused backward when the layer qualifies; plain ops otherwise."""
+    """``(module(x), x)`` with the fused backward when the layer qualifies; plain ops otherwise.
+
+    If ``x`` is the output of a fused batch-norm + residual + ReLU (it then carries ``relu_mask`` / ``relu_mask_taken``,
+    see ``ops/bn.py``) and ``x`` has no consumer other than this fork, the fork also multiplies its input gradient with
+    that ReLU mask in the kernel epilogue and tells the batch-norm so: its backward then neither applies the mask nor
+    writes a separate gradient for the residual branch (it hands the incoming gradient on as is)."""
     w = module.weight
     ok = (x.is_cuda and _native.available() and torch.is_grad_enabled() and x.requires_grad and module.bias is None
           and tuple(module.kernel_size) == (1, 1) and tuple(module.stride) == (1, 1) and tuple(module.padding) == (0, 0)
@@ -187,4 +210,9 @@ def fork_conv1x1(module, x):
           and w.shape[0] % 64 == 0 and w.shape[1] % 64 == 0)
     if not ok:
         return module(x), x
+    mask = getattr(x, "relu_mask", None)
+    taken = getattr(x, "relu_mask_taken", None)
+    if mask is not None and taken is not None and w.shape[1] % 128 == 0 and not os.environ.get("LWC_NO_PREMASK"):
+        taken[0] = True
+        return _ForkConv1x1.apply(x, w, mask)
     return _ForkConv1x1.apply(x, w)

@@ -1,4 +1,6 @@
 """Persistent tcgen05 implicit-GEMM convolution vs an fp32 PyTorch reference."""
+import os
+
 import pytest
 import torch
 import torch.nn.functional as F
@@ -76,3 +78,62 @@ def test_fork_conv1x1_fused_residual_gradient():
     assert (y.float() - y2).abs().max() <= 2e-2 * y2.abs().max()
     assert (x1.grad.float() - x2.grad).abs().max() <= 2e-2 * x2.grad.abs().max()
     assert (gw1.float() - w2.grad).abs().max() <= 3e-2 * w2.grad.abs().max()
+
+
+def test_fork_premasks_gradient_for_the_producing_batchnorm():
+    """Two bottlenecks in a row: the second block's fork multiplies its input gradient with the first block's ReLU mask
+    (kernel epilogue) and the first block's bn3 backward hands dy on without masking or writing a residual gradient.
+    Gradients must match the stock-op pipeline."""
+    import copy
+    from layerwise_b200.models import resnet as zoo
+    from layerwise_b200.ops import nn as lnn
+    torch.manual_seed(0)
+    blocks = torch.nn.Sequential(zoo.Bottleneck(256, 64), zoo.Bottleneck(256, 64), zoo.Bottleneck(256, 64)).cuda()
+    blocks = blocks.to(memory_format=torch.channels_last).to(torch.bfloat16)
+    for m in blocks.modules():
+        if isinstance(m, torch.nn.modules.batchnorm._BatchNorm):
+            m.float()
+            torch.nn.init.uniform_(m.weight, 0.5, 1.5)
+            torch.nn.init.normal_(m.bias, 0.0, 0.5)
+    ref = copy.deepcopy(blocks)
+    x0 = torch.randn(8, 256, 12, 12, device="cuda").to(torch.bfloat16).contiguous(memory_format=torch.channels_last)
+    g = torch.randn(8, 256, 12, 12, device="cuda").to(torch.bfloat16).contiguous(memory_format=torch.channels_last)
+
+    def run(net, native):
+        lnn.set_backend("auto" if native else "torch")
+        try:
+            x = x0.clone().requires_grad_(True)
+            y1 = net[0](x)
+            if native:
+                assert y1.relu_mask_taken[0] is False
+            y2 = net[1](y1)
+            if native and not os.environ.get("LWC_NO_PREMASK"):
+                assert y1.relu_mask_taken[0] is True and y2.relu_mask_taken[0] is False
+            y3 = net[2](y2)
+            (y3 * g).sum().backward()
+            return x.grad.float(), [p.grad.float() for p in net.parameters()]
+        finally:
+            lnn.set_backend("auto")
+
+    # (1) pre-masking is an exact re-association of the same arithmetic: bit-identical to the path that masks inside
+    #     the batch-norm backward and writes a separate residual gradient
+    gx_a, gp_a = run(blocks, True)
+    os.environ["LWC_NO_PREMASK"] = "1"
+    try:
+        for p_ in blocks.parameters():
+            p_.grad = None
+        gx_c, gp_c = run(blocks, True)
+    finally:
+        del os.environ["LWC_NO_PREMASK"]
+    assert torch.equal(gx_a, gx_c)
+    for a, c in zip(gp_a, gp_c):
+        assert torch.equal(a, c)
+    # (2) against the stock-op pipeline: a ReLU whose bf16 pre-activation rounds to the other side of zero flips a whole
+    #     gradient path, so compare in relative L2 and loosely (nine batch-norms deep, bf16)
+    gx_b, gp_b = run(ref, False)
+
+    def rel(a, b):
+        return float((a - b).norm() / (b.norm() + 1e-12))
+    assert rel(gx_a, gx_b) < 0.25, rel(gx_a, gx_b)
+    for a, b in zip(gp_a, gp_b):
+        assert rel(a, b) < 0.25, (a.shape, rel(a, b))
