@@ -233,6 +233,12 @@ int lwc_conv_forward(const void* x, const void* wt, void* y, int Nimg, int H, in
  * residual fork, dX = dY * W + d_identity, in one kernel. */
 int lwc_conv1x1_add(const void* x, const void* wt, const void* addend, void* y, int Nimg, int H, int W, int Cin,
                     int Cout, int b_mn, void* stream);
+/* Same, and outputs whose bit in relu_mask ([M][Cout/8] bytes, the layout lwc_bn_forward_ex writes) is 0 are zeroed:
+ * Y = (conv(X) + addend) * mask.  The gradient then reaches the producing block already multiplied with that block's
+ * ReLU mask, so its batch-norm backward neither reads a mask nor writes a residual gradient of its own.
+ * addend may be NULL; Cout % 128 == 0. */
+int lwc_conv1x1_add_mask(const void* x, const void* wt, const void* addend, const void* relu_mask, void* y, int Nimg,
+                         int H, int W, int Cin, int Cout, int b_mn, void* stream);
 
 /* Weight gradient of the ResNet stem (7x7/2 pad 3, 3 -> 64 channels; IMAGENET/training/resnet.py:100) on tcgen05:
  * dy [N][OH][OW][64] bf16, xs = the 2x2 space-to-depth input [N][OH+3][OW+3][16] bf16 written by lwc_normalize_u8
