@@ -149,6 +149,8 @@ class Trainer:
             and hasattr(self.exchanger.engine, "enable_graph_mode")
         self._shape_key, self._shape_run = None, 0
         self._side = None
+        self._graphable = self.device.type == "cuda" and self.wrapper is None \
+            and hasattr(self.exchanger.engine, "enable_graph_mode")
 
     def _model_in_group_order(self, groups):
         by_master = {id(m): p for m, p in zip(self.master_params, self.model_params)}
@@ -182,7 +184,9 @@ class Trainer:
         self.optimizer.enable_device_lr(self.device)
         self.net.train()
         self.normalize.train()
-        side = torch.cuda.Stream(device=self.device)
+        if self._side is None:
+            self._side = torch.cuda.Stream(device=self.device)
+        side = self._side
         side.wait_stream(torch.cuda.current_stream())
         with torch.cuda.stream(side):
             for _ in range(warmup):
@@ -235,8 +239,10 @@ class Trainer:
             if self._shape_run > 3:
                 self.capture_graph(images, target, warmup=0)
                 return self._replay(images, target)
-            # steps that precede a capture run on a side stream: autograd state created on the legacy default stream
-            # makes the capture fail ("legacy stream depend on a capturing blocking stream")
+        if self._graphable:
+            # Eager steps of a trainer that may be captured later run on a stream of its own: autograd state created on
+            # the legacy default stream (gradient accumulators kept alive by a loss the caller still holds) makes a
+            # later capture fail with "legacy stream depend on a capturing blocking stream".
             if self._side is None:
                 self._side = torch.cuda.Stream(device=self.device)
             cur = torch.cuda.current_stream()
