@@ -207,13 +207,23 @@ __global__ void __launch_bounds__(THREADS) k_bn_stats(Params p) {
                 for (int k = 0; k < 8; ++k) { s[k] += v[k]; q[k] = fmaf(v[k], v[k], q[k]); }
             }
         }
-        for (; r < m.row1; r += m.rpp) {
-            Raw<T> raw;
-            ldraw<T>(x + (size_t)r * p.C, raw);
-            float v[8];
-            unpack(raw, v);
+        if (r < m.row1) {
+            // fewer than U rows left: ONE batch of predicated loads (rows past the end re-read row r and are not
+            // counted) instead of a serial one-load-per-round-trip tail of up to U - 1 iterations
+            Raw<T> raw[U];
 #pragma unroll
-            for (int k = 0; k < 8; ++k) { s[k] += v[k]; q[k] = fmaf(v[k], v[k], q[k]); }
+            for (int u = 0; u < U; ++u) {
+                const long long ru = r + (long long)u * m.rpp;
+                ldraw<T>(x + (size_t)(ru < m.row1 ? ru : r) * p.C, raw[u]);
+            }
+#pragma unroll
+            for (int u = 0; u < U; ++u) {
+                if (r + (long long)u * m.rpp >= m.row1) break;
+                float v[8];
+                unpack(raw[u], v);
+#pragma unroll
+                for (int k = 0; k < 8; ++k) { s[k] += v[k]; q[k] = fmaf(v[k], v[k], q[k]); }
+            }
         }
     }
     reduce_rows(m, s, q, sh);
