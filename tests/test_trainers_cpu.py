@@ -48,3 +48,35 @@ def test_trainer_bf16_masters_cpu():
     assert out.dtype == torch.bfloat16 and torch.isfinite(loss)
     assert not torch.equal(w0, tr.master_params[0])
     assert torch.equal(tr.model_params[0].detach(), tr.master_params[0].detach().to(torch.bfloat16))
+
+
+def test_graphed_train_step_falls_back_to_eager_on_cpu():
+    """``dawn.py --cuda_graph`` on a machine without the fused engine: same loop, stepped eagerly."""
+    import torch
+    from layerwise_b200.models import build_cifar_model, trainable_params
+    from layerwise_b200.ops.sgd import SGD
+    from layerwise_b200.parallel.exchange import CompressionConfig, GradientExchanger
+    from layerwise_b200.train.cifar import GraphedTrainStep, run_batches
+    torch.manual_seed(0)
+    model = build_cifar_model("resnet9")
+    ex = GradientExchanger(trainable_params(model), CompressionConfig(compress="layerwise", method="Topk", ratio=0.1))
+    opt = SGD(trainable_params(model), lr=lambda s: 0.01, momentum=0.9, weight_decay=5e-4, nesterov=True)
+    step = GraphedTrainStep(model, ex, opt)
+    assert not step.ok                                   # torch engine on CPU: nothing to capture
+    batches = [{"input": torch.randn(8, 3, 32, 32), "target": torch.randint(0, 10, (8,))} for _ in range(3)]
+    stats = run_batches(model, batches, True, ex, opt.step, graphed=step)
+    assert opt.step_number == 3 and step.graph is None
+    assert stats.mean("loss") == stats.mean("loss")
+
+
+def test_apply_bitmask_matches_manual_mask():
+    import torch
+    from layerwise_b200.ops.conv import apply_bitmask
+    torch.manual_seed(0)
+    n, c, h, w = 2, 16, 3, 5
+    keep = torch.rand(n, h, w, c) > 0.5                  # channels-last pixel order
+    bits = keep.reshape(-1, 8).to(torch.uint8)
+    mask = sum(bits[:, k] << k for k in range(8)).to(torch.uint8)
+    t = torch.randn(n, c, h, w).contiguous(memory_format=torch.channels_last)
+    out = apply_bitmask(t, mask)
+    assert torch.equal(out, t * keep.permute(0, 3, 1, 2).to(t.dtype))
