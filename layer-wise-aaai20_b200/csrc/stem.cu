@@ -18,7 +18,7 @@
 //                pair j-2 -> acc E (lo: unused, hi: bh 3)
 // Five fp32 accumulators of 64 columns live in tensor memory for the whole kernel; the CTA (one per SM, each
 // owning a contiguous range of input rows) dumps them once at the end and a small second kernel sums the
-// per-CTA partials in a fixed order and scatters them into the 7x7 layout.  dy pairs stay in a 4-slot ring
+// per-CTA partials in a fixed order and scatters them into the 7x7 layout.  dy pairs stay in a 5-slot ring
 // (each is used by five consecutive input rows and requested two rows early), xs rows go through a ring of up
 // to 8 stages: 100+ KB of loads in flight per SM.
 //
