@@ -220,6 +220,7 @@ class GradientExchanger:
         self.params = [p for p in params if p.requires_grad]
         self.cfg = cfg
         self.group = group
+        self._seen_timeouts = 0
         use_fused = False
         if engine in ("auto", "fused") and self.params and self.params[0].is_cuda:
             from .. import _native
@@ -257,6 +258,24 @@ class GradientExchanger:
 
     def load_state_dict(self, sd):
         self.engine.load_state_dict(sd)
+
+    def check_health(self, raise_on_timeout: bool = True) -> Dict[str, int]:
+        """Failure detection for the peer-memory engines: their receivers wait for the other ranks' flags with a bound
+        (``lwc_set_flag_timeout_ms``) and count every wait that ran out -- a stalled or dead rank then shows up as a
+        growing ``timeouts`` counter instead of a hang.  Call at a point that may synchronise (the trainers do at
+        their logging interval); returns the engine's counters and raises once new time-outs appeared.  Entries
+        dropped by the capacity clamp are reported in ``dropped`` (not an error: they stay in the error-feedback
+        residual)."""
+        stats = getattr(self.engine, "stats", None)
+        if stats is None:
+            return {}
+        st = stats()
+        new = st.get("timeouts", 0) - self._seen_timeouts
+        self._seen_timeouts = st.get("timeouts", 0)
+        if new > 0 and raise_on_timeout:
+            raise RuntimeError(f"gradient exchange: {new} peer flag wait(s) timed out since the last check "
+                               f"(rank {comm.rank(self.group)} of {comm.world_size(self.group)}): a peer is stalled or gone")
+        return st
 
     @property
     def step(self):

@@ -182,6 +182,7 @@ def train(model, optimizer, train_batches, test_batches, epochs, master_address=
     for epoch in range(epochs):
         stats = train_epoch(model, train_batches, test_batches, optimizer.step, timer, exchanger,
                             test_time_in_total=test_time_in_total, max_batches=max_batches, graphed=graphed)
+        exchanger.check_health()             # a peer whose flags stopped arriving raises here instead of hanging the job
         lr = optimizer.param_values()["lr"] * train_batches.batch_size \
             if hasattr(optimizer, "param_values") else optimizer.param_groups[0]["lr"]
         summary = union({"epoch": epoch + 1, "lr": lr}, stats)

@@ -373,6 +373,9 @@ def train_epoch(trainer: Trainer, loader, scheduler: PhaseScheduler, epoch: int,
         if (i + 1) % print_freq == 0 or i + 1 == n or (short_epoch and i == 10):
             tot, lsum, s1, s5 = comm.sum_tensor(acc).tolist()       # the only host sync of the loop
             acc.zero_()
+            health = trainer.exchanger.check_health()               # raises when a peer's flags stopped arriving
+            if tb is not None and health:
+                tb.log("net/exchange_dropped", health.get("dropped", 0))
             tot = max(tot, 1.0)
             losses.update(lsum / tot, tot)
             top1.update(100.0 * s1 / tot, tot)

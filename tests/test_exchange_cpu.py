@@ -96,3 +96,27 @@ def test_resnet9_topk_ef_two_ranks_plumbing():
     for a, b in zip(r0["w"], r1["w"]):
         assert torch.equal(a, b)  # replicas stay in lock-step although inputs differ
     assert r0["loss"] == r0["loss"]  # finite
+
+
+def test_check_health_reports_new_timeouts():
+    import pytest
+    import torch
+    from layerwise_b200.parallel.exchange import CompressionConfig, GradientExchanger
+    p = torch.nn.Parameter(torch.zeros(8))
+    ex = GradientExchanger([p], CompressionConfig())
+    assert ex.check_health() == {} or "timeouts" in ex.check_health()       # the torch engine keeps no counters
+
+    class _Eng:                                                            # an engine with counters
+        def __init__(self):
+            self.n = 0
+
+        def stats(self):
+            return {"sent": 5, "dropped": 1, "timeouts": self.n, "bytes": 40}
+    ex.engine = _Eng()
+    assert ex.check_health()["dropped"] == 1
+    ex.engine.n = 2
+    with pytest.raises(RuntimeError, match="2 peer flag wait"):
+        ex.check_health()
+    assert ex.check_health()["timeouts"] == 2                              # already reported: no second raise
+    ex.engine.n = 3
+    assert ex.check_health(raise_on_timeout=False)["timeouts"] == 3
