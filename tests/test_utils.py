@@ -120,3 +120,18 @@ def test_misc_helpers():
     assert run_parallel(lambda v: v * v, [1, 2, 3]) == [1, 4, 9]
     t = utils.Timer()
     assert t() >= 0 and t.total_time >= 0
+
+
+def test_minimal_api_example_runs_and_learns():
+    import importlib.util
+    import os
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    spec = importlib.util.spec_from_file_location("ex_min", os.path.join(root, "examples", "compressed_ddp_minimal.py"))
+    mod = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(mod)
+    import torch
+    if torch.cuda.is_available():
+        import pytest
+        pytest.skip("CPU example test")
+    first, last = mod.main(["--steps", "25", "--method", "Topk", "--ratio", "0.1"])
+    assert last < first
