@@ -99,6 +99,8 @@ class Trainer:
         self.device = torch.device(device or ("cuda" if torch.cuda.is_available() else "cpu"))
         if self.device.type == "cuda":
             torch.backends.cudnn.benchmark = True     # as the reference does (train_imagenet_nv.py:95): autotune conv algos
+            if os.environ.get("LWC_CUDNN_BENCH_LIMIT") is not None:      # 0 = try every algorithm (default: the first 10)
+                torch.backends.cudnn.benchmark_limit = int(os.environ["LWC_CUDNN_BENCH_LIMIT"])
         self.dtype = {"fp32": torch.float32, "bf16": torch.bfloat16, "fp16": torch.float16}[dtype]
         self.loss_scale = loss_scale if self.dtype == torch.float16 else 1.0
         torch.manual_seed(seed)          # identical initial replicas (reference :117-118)
