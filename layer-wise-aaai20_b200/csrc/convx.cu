@@ -1,0 +1,490 @@
+// Tap-table implicit-GEMM convolution on tcgen05 / TMEM / TMA: every convolution of the model zoo, forward,
+// data gradient and weight gradient, channels-last bf16.
+//
+// Forward-like kernel k_fx (forward, data gradient, strided variants, small-Cin first layers, the 7x7/2 stem):
+//
+//   Y[p, co] = sum_{t < ntaps} sum_{c < Kc} A[(p * s + d_t), a_c0[t] + c] * B[co, b_k0[t] + c]
+//
+//   * the output tile is a Wb x Hb x Nb patch of pixels (<= 128 rows); each (tap, 64-channel chunk) of the K loop is
+//     ONE 4-D TMA box load of that patch of the input shifted by the tap offset d_t -- out-of-bounds rows, columns
+//     and channels are zero-filled by the TMA unit, which is the padding (also the channel padding of 3- / 8- /
+//     16-channel inputs: the K chunk is padded in the descriptor, not in memory);
+//   * stride 2 is the tensor map's traversal stride (elementStrides), the kernel only scales the start coordinate;
+//   * 1x1 stride-1 layers are the same code with the pixels flattened into one axis;
+//   * the data gradient of a stride-2 layer is four launches, one per output parity class, each with its own tap
+//     subset and a strided output map; the 7x7/2 stem is four row-taps over overlapping 128-byte windows of the
+//     space-to-depth input;
+//   * BN in {64, 128, 256}: Cout <= 256 layers read the activation exactly once and write whole output rows;
+//   * persistent CTAs (static tile schedule), accumulator double-buffered in tensor memory, epilogue
+//     TMEM -> registers -> (bias, ReLU) -> swizzled shared memory -> TMA store through a ring of 64-column staging
+//     buffers; optional per-channel sum / sum-of-squares of the rounded outputs accumulated per CTA in shared
+//     memory in a fixed order (batch-norm statistics without a pass over the output).
+//
+// Weight-gradient kernel k_wx:   dW[co, t, ci] = sum_p dY[p, co] * X[p * s + d_t, ci]
+//   D[(tap, ci) : 128][co : BN] accumulators in tensor memory (up to 512 columns = several (tap, ci-pair) slices
+//   per CTA), both operands MN-major straight from the channels-last tensors (4-D TMA boxes of the same pixel patch,
+//   the X box shifted by the tap), split over pixel patches across CTAs, fp32 partials reduced in a fixed order.
+//
+// All TMA loads here read this GPU's own activations and weights; none is a cluster-multicast load.
+//
+// Reference ops: nn.Conv2d forward / backward through cuDNN -- IMAGENET/training/resnet.py:18-21,59-66,100-101,122-126;
+// CIFAR10/dawn.py:23-35; CIFAR10/alexnet.py:15-27; CIFAR10/vgg16.py:69-82.
+#include <cuda.h>
+#include <cuda_bf16.h>
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdio.h>
+#include <stdlib.h>
+#include <string.h>
+
+#include "common.cuh"
+#include "tc.cuh"
+
+namespace lwc {
+namespace convx {
+
+using namespace lwc::tc;
+
+constexpr int BM = 128;
+constexpr int BK = 64;
+constexpr int THREADS = 192;
+constexpr int MAXT = 16;
+constexpr int SUB_BYTES = BM * 128;          // one 128-row x 64-column bf16 staging sub-tile
+constexpr int SMEM_BUDGET = 227 * 1024;
+
+struct FxParams {
+    int N;                                   // output channels
+    int ntaps, kchunks;                      // K loop = ntaps * kchunks iterations of 64 channels
+    int Wb, Hb, Nb, tiles_w, tiles_h;        // output patch and tile grid (tiles_m = tiles_w * tiles_h * tiles_nimg)
+    int sw, sh;                              // input start coordinate = output coordinate * s + d
+    int OW, OH, ON;                          // output extent (rows of a patch beyond it are neither stored nor counted)
+    int tiles_m, tiles_n, rows_per_tile;
+    int relu;
+    int stages, ncs;                         // operand ring depth, staging ring depth
+    int c_off, stat_off, bar_off;            // shared-memory offsets
+    const float* bias;
+    float* stats;                            // [gridDim.x][2][N] per-CTA sums / sums of squares, or NULL
+    short dw[MAXT], dh[MAXT];
+    int a_c0[MAXT], b_k0[MAXT];
+};
+
+struct TileCoord { int mt, nt, w0, h0, n0; };
+__device__ __forceinline__ TileCoord tile_coord(const FxParams& p, int tile) {
+    TileCoord t;
+    t.mt = tile / p.tiles_n;
+    t.nt = tile - t.mt * p.tiles_n;
+    const int tw = t.mt % p.tiles_w;
+    const int r = t.mt / p.tiles_w;
+    const int th = r % p.tiles_h;
+    t.w0 = tw * p.Wb; t.h0 = th * p.Hb; t.n0 = (r / p.tiles_h) * p.Nb;
+    return t;
+}
+
+template <int BN, bool B_MN>
+__global__ void __launch_bounds__(THREADS, 1) k_fx(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
+                                                   const __grid_constant__ CUtensorMap tmC, const FxParams p) {
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+    constexpr int A_BYTES = BM * BK * 2;
+    constexpr int B_BYTES = BN * BK * 2;
+    constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
+    constexpr int MAXS = 8;
+    uint64_t* full = reinterpret_cast<uint64_t*>(smem + p.bar_off);
+    uint64_t* empty = full + MAXS;
+    uint64_t* tmem_full = empty + MAXS;        // [2]
+    uint64_t* tmem_empty = tmem_full + 2;      // [2]
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_empty + 2);
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int num_tiles = p.tiles_m * p.tiles_n;
+    const int kiters = p.ntaps * p.kchunks;
+    const int stages = p.stages;
+    const uint32_t a_bytes = (uint32_t)p.rows_per_tile * (BK * 2);
+
+    if (threadIdx.x == 0) {
+        prefetch_tensormap(&tmA); prefetch_tensormap(&tmB); prefetch_tensormap(&tmC);
+        for (int s = 0; s < stages; ++s) { mbar_init(&full[s], 1); mbar_init(&empty[s], 1); }
+        for (int a = 0; a < 2; ++a) { mbar_init(&tmem_full[a], 1); mbar_init(&tmem_empty[a], 4); }
+        fence_barrier_init();
+    }
+    if (warp == 1) tmem_alloc<2 * BN>(tmem_slot);
+    if (p.stats) {                                          // per-CTA statistics accumulators start at zero
+        float* acc0 = reinterpret_cast<float*>(smem + p.stat_off);
+        for (int i = threadIdx.x; i < 2 * p.N; i += THREADS) acc0[i] = 0.0f;
+    }
+    fence_before();
+    __syncthreads();
+    fence_after();
+    const uint32_t tmem_base = *tmem_slot;
+
+    if (warp == 0 && lane == 0) {
+        // ---------------- TMA producer ----------------
+        uint32_t s = 0, ph = 0;
+        for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+            const TileCoord t = tile_coord(p, tile);
+            const int co0 = t.nt * BN;
+            const int wi = t.w0 * p.sw, hi = t.h0 * p.sh;
+            for (int tap = 0; tap < p.ntaps; ++tap) {
+                const int aw = wi + p.dw[tap], ah = hi + p.dh[tap], ac = p.a_c0[tap], bk = p.b_k0[tap];
+                for (int ch = 0; ch < p.kchunks; ++ch) {
+                    mbar_wait(&empty[s], ph ^ 1);
+                    uint8_t* a = smem + s * STAGE_BYTES;
+                    uint8_t* b = a + A_BYTES;
+                    mbar_expect_tx(&full[s], a_bytes + B_BYTES);
+                    tma_load_4d(a, &tmA, &full[s], ac + ch * BK, aw, ah, t.n0);
+                    if (B_MN) {
+#pragma unroll
+                        for (int h = 0; h < BN / 64; ++h) tma_load_2d(b + h * 8192, &tmB, &full[s], co0 + h * 64, bk + ch * BK);
+                    } else {
+                        tma_load_2d(b, &tmB, &full[s], bk + ch * BK, co0);
+                    }
+                    if (++s == (uint32_t)stages) { s = 0; ph ^= 1; }
+                }
+            }
+        }
+    } else if (warp == 1 && lane == 0) {
+        // ---------------- MMA issuer ----------------
+        constexpr uint32_t idesc = make_idesc(BN, false, B_MN);
+        uint32_t s = 0, ph = 0, tcount = 0;
+        for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++tcount) {
+            const uint32_t as = tcount & 1, aph = (tcount >> 1) & 1;
+            mbar_wait(&tmem_empty[as], aph ^ 1);
+            fence_after();
+            const uint32_t tacc = tmem_base + as * BN;
+            for (int kk = 0; kk < kiters; ++kk) {
+                mbar_wait(&full[s], ph);
+                fence_after();
+                const uint32_t a = smem_u32(smem + s * STAGE_BYTES);
+                const uint32_t b = a + A_BYTES;
+                const uint64_t da = make_desc(a, 16, 1024);
+                const uint64_t db = B_MN ? make_desc(b, 8192, 1024) : make_desc(b, 16, 1024);
+                umma_x4<2, (B_MN ? 128 : 2)>(tacc, da, db, idesc, kk > 0 ? 1u : 0u);
+                umma_commit(&empty[s]);
+                if (++s == (uint32_t)stages) { s = 0; ph ^= 1; }
+            }
+            umma_commit(&tmem_full[as]);
+        }
+    } else if (warp >= 2) {
+        // ---------------- epilogue ----------------
+        const int q = warp & 3;
+        const int r = q * 32 + lane;
+        const int et = threadIdx.x - 64;               // 0..127
+        const bool leader = et == 0;
+        const int r_w = r % p.Wb, r_h = (r / p.Wb) % p.Hb, r_n = r / (p.Wb * p.Hb);
+        float* acc = reinterpret_cast<float*>(smem + p.stat_off);
+        float* scratch = acc + 2 * p.N;                // [4 warps][2][64]
+        uint32_t tcount = 0, sub = 0;
+        for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++tcount) {
+            const TileCoord t = tile_coord(p, tile);
+            const int co0 = t.nt * BN;
+            const uint32_t as = tcount & 1, aph = (tcount >> 1) & 1;
+            // rows of the patch that are not output pixels are zeroed in the staging tile: the TMA store clips them
+            // anyway, and the statistics must not see them
+            const bool row_live = r < p.rows_per_tile && t.w0 + r_w < p.OW && t.h0 + r_h < p.OH && t.n0 + r_n < p.ON;
+            mbar_wait(&tmem_full[as], aph);
+            fence_after();
+#pragma unroll 1
+            for (int h = 0; h < BN / 64; ++h) {
+                uint8_t* cst = smem + p.c_off + sub * SUB_BYTES;
+                // the store that read this staging buffer `ncs` chunks ago must have finished reading it
+                if (leader) {
+                    if (p.ncs >= 4) tma_wait_group_read<3>(); else if (p.ncs == 3) tma_wait_group_read<2>(); else tma_wait_group_read<1>();
+                }
+                uint32_t v0[32], v1[32];
+                const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + as * BN + (uint32_t)(h * 64);
+                tmem_ld32_issue(taddr, v0);
+                tmem_ld32_issue(taddr + 32, v1);
+                tmem_ld_wait();
+                if (h == BN / 64 - 1) {                 // whole row is in registers: the accumulator may be overwritten
+                    fence_before();
+                    __syncwarp();
+                    if (lane == 0) mbar_arrive(&tmem_empty[as]);
+                }
+                epi_bar_sync();                         // staging buffer free (leader waited above)
+                use_after_wait(v0);
+                use_after_wait(v1);
+                uint8_t* rowp = cst + r * 128;
+#pragma unroll
+                for (int j = 0; j < 8; ++j) {           // eight 16-byte chunks (8 bf16 each)
+                    const uint32_t* v = j < 4 ? v0 : v1;
+                    const int jj = (j & 3) * 8;
+                    uint32_t w[4];
+#pragma unroll
+                    for (int e = 0; e < 4; ++e) {
+                        float x0 = __uint_as_float(v[jj + 2 * e]), x1 = __uint_as_float(v[jj + 2 * e + 1]);
+                        if (p.bias) {
+                            const int c = co0 + h * 64 + j * 8 + 2 * e;
+                            x0 += __ldg(p.bias + c); x1 += __ldg(p.bias + c + 1);
+                        }
+                        if (p.relu) { x0 = fmaxf(x0, 0.0f); x1 = fmaxf(x1, 0.0f); }
+                        if (!row_live) { x0 = 0.0f; x1 = 0.0f; }
+                        __nv_bfloat162 hb = __floats2bfloat162_rn(x0, x1);
+                        w[e] = *reinterpret_cast<uint32_t*>(&hb);
+                    }
+                    *reinterpret_cast<uint4*>(rowp + ((j ^ (r & 7)) * 16)) = make_uint4(w[0], w[1], w[2], w[3]);
+                }
+                fence_proxy_async_smem();
+                epi_bar_sync();
+                if (leader) {
+                    if (co0 + h * 64 < p.N) tma_store_4d(&tmC, cst, co0 + h * 64, t.w0, t.h0, t.n0);
+                    tma_commit_group();                 // one group per chunk keeps the count in step with the ring
+                }
+                if (p.stats) {
+                    // column sums of the rounded 128 x 64 sub-tile: thread = (row group of 8, 16-byte chunk)
+                    const int c = et & 7, rg = et >> 3;
+                    float s1[8], s2[8];
+#pragma unroll
+                    for (int k = 0; k < 8; ++k) { s1[k] = 0.0f; s2[k] = 0.0f; }
+#pragma unroll
+                    for (int i = 0; i < 8; ++i) {
+                        const uint4 u = *reinterpret_cast<const uint4*>(cst + (rg * 8 + i) * 128 + ((c ^ i) * 16));
+                        const uint32_t uw[4] = {u.x, u.y, u.z, u.w};
+#pragma unroll
+                        for (int e = 0; e < 4; ++e) {
+                            const float lo = __uint_as_float(uw[e] << 16), hi = __uint_as_float(uw[e] & 0xffff0000u);
+                            s1[2 * e] += lo; s2[2 * e] = fmaf(lo, lo, s2[2 * e]);
+                            s1[2 * e + 1] += hi; s2[2 * e + 1] = fmaf(hi, hi, s2[2 * e + 1]);
+                        }
+                    }
+#pragma unroll
+                    for (int k = 0; k < 8; ++k) {      // the four row groups of a warp: lanes l, l^8, l^16, l^24
+                        s1[k] += __shfl_xor_sync(0xffffffffu, s1[k], 8);
+                        s2[k] += __shfl_xor_sync(0xffffffffu, s2[k], 8);
+                        s1[k] += __shfl_xor_sync(0xffffffffu, s1[k], 16);
+                        s2[k] += __shfl_xor_sync(0xffffffffu, s2[k], 16);
+                    }
+                    if (lane < 8) {
+                        float* o = scratch + q * 128 + lane * 8;
+#pragma unroll
+                        for (int k = 0; k < 8; ++k) { o[k] = s1[k]; o[64 + k] = s2[k]; }
+                    }
+                    epi_bar_sync();
+                    {
+                        const int which = et >> 6, ch = et & 63;           // fixed order over the four warps
+                        const float tot = (scratch[0 * 128 + which * 64 + ch] + scratch[1 * 128 + which * 64 + ch]) +
+                                          (scratch[2 * 128 + which * 64 + ch] + scratch[3 * 128 + which * 64 + ch]);
+                        const int cg = co0 + h * 64 + ch;
+                        if (cg < p.N) acc[which * p.N + cg] += tot;
+                    }
+                }
+                if (++sub == (uint32_t)p.ncs) sub = 0;
+            }
+        }
+        if (leader) tma_wait_group<0>();
+        if (p.stats) {
+            epi_bar_sync();
+            float* o = p.stats + (size_t)blockIdx.x * 2 * p.N;
+            for (int i = et; i < 2 * p.N; i += 128) o[i] = acc[i];
+        }
+    }
+    fence_before();
+    __syncthreads();
+    if (warp == 1) {
+        __syncwarp();
+        tmem_dealloc<2 * BN>(tmem_base);
+    }
+}
+
+// ======================================================================================================
+// Weight gradient.  One CTA = (slice group g, pixel split z):
+//   * boxes are (tap, 64-input-channel chunk) pairs in tap-major order; a slice is two consecutive boxes (M = 128
+//     accumulator rows), a group is `nacc` consecutive slices that share the same BN output channels;
+//   * every pipeline stage holds one patch of PK pixels: the dY tile [PK][BN] (B operand, MN-major) and for each
+//     slice two X boxes [PK][64] shifted by their tap (A operand, MN-major);  nacc * PK / 16 MMAs per stage;
+//   * the CTA walks patches z, z + ksplit, ...; at the end the nacc accumulators go to the fp32 workspace
+//     [ksplit][nboxes][64][Cout], which k_wx_reduce sums over the splits in a fixed order and transposes into the
+//     channels-last weight layout [Cout][taps][Cin].
+// ======================================================================================================
+struct WxParams {
+    int Cout, Cin_pad;                       // Cin_pad = 64 * cchunks (channels past the tensor's extent read as zero)
+    int ntaps, cchunks, nboxes;              // nboxes = ntaps * cchunks
+    int nacc, groups_per_co;                 // slices per CTA, groups per output-channel tile
+    int PK;                                  // pixels per stage (multiple of 16)
+    int Wb, Hb, Nb, tiles_w, tiles_h, npatches;
+    int sw, sh;
+    int stages, stage_bytes, bar_off;
+    int ksplit;
+    float* ws;                               // [ksplit][nboxes][64][Cout]
+    short dw[MAXT], dh[MAXT];
+};
+
+template <int BN>
+__global__ void __launch_bounds__(THREADS, 1) k_wx(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ CUtensorMap tmDY,
+                                                   const WxParams p) {
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+    constexpr int MAXS = 8;
+    constexpr int TCOLS = 512;               // nacc * BN <= 512
+    uint64_t* full = reinterpret_cast<uint64_t*>(smem + p.bar_off);
+    uint64_t* empty = full + MAXS;
+    uint64_t* tmem_full = empty + MAXS;
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_full + 1);
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int g = blockIdx.x, z = blockIdx.y;
+    const int co_tile = g / p.groups_per_co;
+    const int box0 = (g % p.groups_per_co) * p.nacc * 2;
+    const int co0 = co_tile * BN;
+    int nslices = (p.nboxes - box0 + 1) / 2;
+    if (nslices > p.nacc) nslices = p.nacc;
+    if (nslices < 0) nslices = 0;
+    const int box_bytes = p.PK * 128;
+    const int b_bytes = (BN / 64) * box_bytes;
+    const int npat = z < p.npatches ? (p.npatches - z + p.ksplit - 1) / p.ksplit : 0;
+
+    if (threadIdx.x == 0) {
+        prefetch_tensormap(&tmX); prefetch_tensormap(&tmDY);
+        for (int s = 0; s < p.stages; ++s) { mbar_init(&full[s], 1); mbar_init(&empty[s], 1); }
+        mbar_init(tmem_full, 1);
+        fence_barrier_init();
+    }
+    if (warp == 1) tmem_alloc<TCOLS>(tmem_slot);
+    fence_before();
+    __syncthreads();
+    fence_after();
+    const uint32_t tmem_base = *tmem_slot;
+
+    if (warp == 0 && lane == 0) {
+        // ---------------- TMA producer ----------------
+        int nlive = p.nboxes - box0;                       // boxes of this group that exist
+        if (nlive > 2 * nslices) nlive = 2 * nslices;
+        uint32_t s = 0, ph = 0;
+        for (int i = 0; i < npat; ++i) {
+            const int pt = z + i * p.ksplit;
+            const int tw = pt % p.tiles_w;
+            const int rr = pt / p.tiles_w;
+            const int th = rr % p.tiles_h;
+            const int w0 = tw * p.Wb, h0 = th * p.Hb, n0 = (rr / p.tiles_h) * p.Nb;
+            mbar_wait(&empty[s], ph ^ 1);
+            uint8_t* b = smem + s * p.stage_bytes;
+            uint8_t* a = b + b_bytes;
+            mbar_expect_tx(&full[s], (uint32_t)(b_bytes + nlive * box_bytes));
+#pragma unroll
+            for (int h = 0; h < BN / 64; ++h) tma_load_4d(b + h * box_bytes, &tmDY, &full[s], co0 + h * 64, w0, h0, n0);
+            for (int j = 0; j < nlive; ++j) {
+                const int bx = box0 + j;
+                const int tap = bx / p.cchunks, cc = bx - tap * p.cchunks;
+                tma_load_4d(a + j * box_bytes, &tmX, &full[s], cc * 64, w0 * p.sw + p.dw[tap], h0 * p.sh + p.dh[tap], n0);
+            }
+            if (++s == (uint32_t)p.stages) { s = 0; ph ^= 1; }
+        }
+    } else if (warp == 1 && lane == 0) {
+        // ---------------- MMA issuer ----------------
+        constexpr uint32_t idesc = make_idesc(BN, true, true);
+        const int ksteps = p.PK / 16;
+        uint32_t s = 0, ph = 0;
+        for (int i = 0; i < npat; ++i) {
+            mbar_wait(&full[s], ph);
+            fence_after();
+            const uint32_t b = smem_u32(smem + s * p.stage_bytes);
+            const uint32_t a = b + b_bytes;
+            // MN-major operands: 64-wide MN atoms box_bytes apart (LBO), 8-pixel groups 1024 bytes apart (SBO),
+            // one K step = 16 pixels = 2048 bytes
+            const uint64_t db = make_desc(b, (uint32_t)box_bytes, 1024);
+            for (int j = 0; j < nslices; ++j) {
+                const uint64_t da = make_desc(a + j * 2 * box_bytes, (uint32_t)box_bytes, 1024);
+                for (int ks = 0; ks < ksteps; ++ks)
+                    umma(tmem_base + j * BN, da + (uint64_t)(ks * 128), db + (uint64_t)(ks * 128), idesc, (i > 0 || ks > 0) ? 1u : 0u);
+            }
+            umma_commit(&empty[s]);
+            if (++s == (uint32_t)p.stages) { s = 0; ph ^= 1; }
+        }
+        umma_commit(tmem_full);
+    } else if (warp >= 2) {
+        // ---------------- epilogue: accumulators -> fp32 partials ----------------
+        const int q = warp & 3;
+        const int r = q * 32 + lane;                       // accumulator row = (box parity, channel)
+        mbar_wait(tmem_full, 0);
+        fence_after();
+        for (int j = 0; j < nslices; ++j) {
+            const int bx = box0 + 2 * j + (r >> 6);
+            const bool live = bx < p.nboxes;
+            float* dst = p.ws + (((size_t)z * p.nboxes + (live ? bx : 0)) * 64 + (r & 63)) * p.Cout + co0;
+#pragma unroll 1
+            for (int c = 0; c < BN; c += 32) {
+                uint32_t v[32];
+                tmem_ld32_issue(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(j * BN + c), v);
+                tmem_ld_wait();
+                use_after_wait(v);
+                if (npat == 0) {
+#pragma unroll
+                    for (int e = 0; e < 32; ++e) v[e] = 0u;
+                }
+                if (live && co0 + c < p.Cout) {
+#pragma unroll
+                    for (int e = 0; e < 32; e += 4)
+                        *reinterpret_cast<float4*>(dst + c + e) = make_float4(__uint_as_float(v[e]), __uint_as_float(v[e + 1]),
+                                                                              __uint_as_float(v[e + 2]), __uint_as_float(v[e + 3]));
+                }
+            }
+        }
+    }
+    fence_before();
+    __syncthreads();
+    if (warp == 1) {
+        __syncwarp();
+        tmem_dealloc<TCOLS>(tmem_base);
+    }
+}
+
+// Sum the split partials in a fixed order and transpose [box = (tap, chunk)][64 ci][Cout] -> [Cout][tap][Cin].
+// grid = (nboxes, Cout / 64), block = (64, 4): a 64 x 64 tile per CTA through shared memory.
+template <typename OutT>
+__global__ void __launch_bounds__(256) k_wx_reduce(const float* __restrict__ ws, OutT* __restrict__ out, int ksplit, int nboxes,
+                                                   int cchunks, int Cout, int Cin, int ntaps, float scale) {
+    __shared__ float tile[64][65];
+    const int bx = blockIdx.x, co0 = blockIdx.y * 64;
+    const int tap = bx / cchunks, cc = bx - tap * cchunks;
+    const int tx = threadIdx.x, ty = threadIdx.y;
+    for (int i = ty; i < 64; i += 4) {                     // i = input channel within the box, tx = output channel
+        float s = 0.0f;
+        const float* src = ws + ((size_t)bx * 64 + i) * Cout + co0 + tx;
+        for (int zz = 0; zz < ksplit; ++zz) s += src[(size_t)zz * nboxes * 64 * Cout];
+        tile[i][tx] = s;
+    }
+    __syncthreads();
+    for (int o = ty; o < 64; o += 4) {                     // o = output channel, tx = input channel
+        const int ci = cc * 64 + tx;
+        if (ci < Cin) {
+            const float v = tile[tx][o] * scale;
+            OutT* dst = out + ((size_t)(co0 + o) * ntaps + tap) * Cin + ci;
+            if constexpr (sizeof(OutT) == 4) *dst = v; else *dst = __float2bfloat16_rn(v);
+        }
+    }
+}
+
+// Combine the per-CTA statistics of k_fx into batch-norm mean / inverse std (+ running statistics), one warp per
+// channel, fixed order, double accumulation (<= 148 partials per channel).
+__global__ void __launch_bounds__(256) k_stats_finalize(const float* __restrict__ part, int nparts, int C, double count, float eps,
+                                                        float momentum, float* __restrict__ mean, float* __restrict__ invstd,
+                                                        float* __restrict__ running_mean, float* __restrict__ running_var,
+                                                        long long* num_batches) {
+    const int c = blockIdx.x * 8 + (threadIdx.x >> 5), lane = threadIdx.x & 31;
+    if (num_batches && blockIdx.x == 0 && threadIdx.x == 0) *num_batches += 1;
+    if (c >= C) return;
+    double s = 0.0, q = 0.0;
+    for (int b = lane; b < nparts; b += 32) {
+        s += (double)part[(size_t)b * 2 * C + c];
+        q += (double)part[(size_t)b * 2 * C + C + c];
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        s += __shfl_xor_sync(0xffffffffu, s, o);
+        q += __shfl_xor_sync(0xffffffffu, q, o);
+    }
+    if (lane == 0) {
+        const double mu = s / count;
+        double var = q / count - mu * mu;
+        if (var < 0.0) var = 0.0;
+        mean[c] = (float)mu;
+        invstd[c] = (float)(1.0 / sqrt(var + (double)eps));
+        if (running_mean) {
+            const double unb = count > 1.0 ? var * count / (count - 1.0) : var;
+            running_mean[c] = (1.0f - momentum) * running_mean[c] + momentum * (float)mu;
+            running_var[c] = (1.0f - momentum) * running_var[c] + momentum * (float)unb;
+        }
+    }
+}
+
+}  // namespace convx
+}  // namespace lwc
