@@ -248,6 +248,37 @@ size_t lwc_stem_wgrad_workspace_bytes(int N, int OH);
 int lwc_stem_wgrad(const void* dy, const void* xs, void* out, float* workspace, int N, int OH, int OW, int out_dtype,
                    float scale, void* stream);
 
+/* Tap-table tcgen05 convolution family (csrc/convx.cu): every convolution of the model zoo on one persistent
+ * implicit-GEMM kernel (forward, data gradient) plus a split-pixel weight-gradient kernel.  bf16 channels-last.
+ * (nn.Conv2d forward/backward through cuDNN: IMAGENET/training/resnet.py:18-21,59-66,100-101,122-126;
+ * CIFAR10/dawn.py:23-35; CIFAR10/alexnet.py:15-27; CIFAR10/vgg16.py:69-82.)
+ *   forward : x [N][H][W][Cx] (Cx % 8 == 0), wt [Cout][k*k][round_up(Cx,64)], y [N][OH][OW][Cout]; k*k <= 16,
+ *             stride 1 or 2; bias fp32 / relu optional; stats (nullable) receives per-CTA batch-norm partials
+ *             [lwc_convx_max_partials()][2][Cout] and *nparts_out how many of them are valid; bn_hint = 0 (auto),
+ *             64, 128 or 256 output channels per tile.
+ *   dgrad1x1: dX = dY * W with the forward weight as stored (no transposed copy).
+ *   dgrad   : general k / stride / pad; wt_t [Cin][k*k][Cout] (channel-transposed forward weight, taps not flipped).
+ *   stem    : the 7x7/2 stem as a 4-row-tap convolution over overlapping 128-byte windows of the space-to-depth input.
+ *   wgrad   : dW [Cout][k*k][Cin_out] = scale * dY^T X, fp32 partials in `workspace` reduced in a fixed order. */
+int lwc_convx_max_partials(void);
+int lwc_convx_forward(const void* x, const void* wt, void* y, int N, int H, int W, int Cx, int Cout, int k, int stride,
+                      int pad, const float* bias, int relu, float* stats, int* nparts_out, int bn_hint, void* stream);
+int lwc_convx_dgrad1x1(const void* dy, const void* w, void* dx, long long M, int Cout, int Cin, int bn_hint, void* stream);
+int lwc_convx_dgrad(const void* dy, const void* wt_t, void* dx, int N, int H, int W, int Cin, int Cout, int k, int stride,
+                    int pad, int bn_hint, void* stream);
+int lwc_convx_stem_forward(const void* xs, const void* w4, void* y, int N, int OH, int OW, int Cout, float* stats,
+                           int* nparts_out, int bn_hint, void* stream);
+size_t lwc_convx_wgrad_workspace_bytes(int N, int H, int W, int Cx, int Cout, int k, int stride, int pad, int bn_hint);
+int lwc_convx_wgrad(const void* x, const void* dy, void* dw, float* workspace, int N, int H, int W, int Cx, int Cout,
+                    int Cin_out, int k, int stride, int pad, int out_dtype, float scale, int bn_hint, void* stream);
+/* Batch-norm mean / inverse std (+ running statistics, + num_batches_tracked) from those partials, and the
+ * apply-only batch-norm pass that consumes them (IMAGENET/training/resnet.py:72-92 conv -> bn -> relu chains). */
+int lwc_convx_stats_finalize(const float* partials, int nparts, int C, long long count, float eps, float momentum,
+                             float* mean, float* invstd, float* running_mean, float* running_var,
+                             long long* num_batches_tracked, void* stream);
+int lwc_bn_apply_stats(const void* x, void* y, const void* res, const float* gamma, const float* beta, const float* mean,
+                       const float* invstd, long long M, int C, int dtype, int relu, void* relu_mask, void* stream);
+
 /* Max pooling, NHWC, byte argmax forward + gather backward (CIFAR10/dawn.py:51,:70; resnet.py:104). */
 int lwc_maxpool_forward(const void* x, void* y, void* idx, int N, int H, int W, int C, int k, int stride,
                         int pad, int dtype, void* stream);

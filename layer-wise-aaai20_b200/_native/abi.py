@@ -105,6 +105,16 @@ def declare(lib: C.CDLL):
         C.c_int, vp, vp)
     sig("lwc_conv1x1_add", C.c_int, vp, vp, vp, vp, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, vp)
     sig("lwc_conv1x1_add_mask", C.c_int, vp, vp, vp, vp, vp, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, vp)
+    ci, ll, cf = C.c_int, C.c_longlong, C.c_float
+    sig("lwc_convx_max_partials", ci)
+    sig("lwc_convx_forward", ci, vp, vp, vp, ci, ci, ci, ci, ci, ci, ci, ci, vp, ci, vp, C.POINTER(ci), ci, vp)
+    sig("lwc_convx_dgrad1x1", ci, vp, vp, vp, ll, ci, ci, ci, vp)
+    sig("lwc_convx_dgrad", ci, vp, vp, vp, ci, ci, ci, ci, ci, ci, ci, ci, ci, vp)
+    sig("lwc_convx_stem_forward", ci, vp, vp, vp, ci, ci, ci, ci, vp, C.POINTER(ci), ci, vp)
+    sig("lwc_convx_wgrad_workspace_bytes", sz, ci, ci, ci, ci, ci, ci, ci, ci, ci)
+    sig("lwc_convx_wgrad", ci, vp, vp, vp, vp, ci, ci, ci, ci, ci, ci, ci, ci, ci, ci, cf, ci, vp)
+    sig("lwc_convx_stats_finalize", ci, vp, ci, ci, ll, cf, cf, vp, vp, vp, vp, vp, vp)
+    sig("lwc_bn_apply_stats", ci, vp, vp, vp, vp, vp, vp, vp, ll, ci, ci, ci, vp, vp)
     sig("lwc_stem_wgrad_workspace_bytes", C.c_size_t, C.c_int, C.c_int)
     sig("lwc_stem_wgrad", C.c_int, vp, vp, vp, vp, C.c_int, C.c_int, C.c_int, C.c_int, C.c_float, vp)
     sig("lwc_sgd_plan_create", C.c_int, c_void_pp, C.POINTER(LwcSgdTensor), i32)

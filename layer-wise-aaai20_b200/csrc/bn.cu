@@ -637,3 +637,21 @@ extern "C" int lwc_bn_backward_ex(const void* dy, const void* x, const void* y, 
     LWC_BN_DISPATCH(dtype, k_bn_bwd_apply<T><<<grid, THREADS, 0, st>>>(p));
     return (int)cudaGetLastError();
 }
+
+// Training-mode normalisation with batch statistics computed elsewhere (the convolution epilogue,
+// lwc_convx_stats_finalize): only the apply pass runs.  mean / invstd are the per-channel batch statistics.
+extern "C" int lwc_bn_apply_stats(const void* x, void* y, const void* res, const float* gamma, const float* beta, const float* mean,
+                                  const float* invstd, long long M, int C, int dtype, int relu, void* relu_mask, void* stream) {
+    if (!x || !y || !mean || !invstd || M <= 0 || C <= 0 || (C % VEC)) return LWC_EINVAL;
+    cudaStream_t st = (cudaStream_t)stream;
+    Params p;
+    memset(&p, 0, sizeof(p));
+    p.x = x; p.y = y; p.res = res; p.gamma = gamma; p.beta = beta;
+    p.mean = const_cast<float*>(mean); p.invstd = const_cast<float*>(invstd);
+    p.M = M; p.C = C; p.relu = relu;
+    p.mask = reinterpret_cast<unsigned char*>(relu_mask);
+    dim3 grid;
+    plan_grid(M, C, &p.nblk, &p.rows_per_blk, &grid, 2);
+    LWC_BN_DISPATCH(dtype, k_bn_apply<T><<<grid, THREADS, 0, st>>>(p, 0));
+    return (int)cudaGetLastError();
+}

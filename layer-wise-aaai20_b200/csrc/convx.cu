@@ -488,3 +488,422 @@ __global__ void __launch_bounds__(256) k_stats_finalize(const float* __restrict_
 
 }  // namespace convx
 }  // namespace lwc
+
+using namespace lwc::convx;
+
+// ---------------------------------------------------------------------------------------------- host side
+namespace {
+
+int g_sm_count = 0;
+int sm_count() {
+    if (!g_sm_count) {
+        int dev = 0;
+        cudaGetDevice(&dev);
+        cudaDeviceGetAttribute(&g_sm_count, cudaDevAttrMultiProcessorCount, dev);
+        if (g_sm_count <= 0) g_sm_count = 148;
+    }
+    return g_sm_count;
+}
+
+void ensure_context() {
+    CUcontext ctx = nullptr;
+    if (cuCtxGetCurrent(&ctx) != CUDA_SUCCESS || !ctx) {
+        int dev = 0;
+        cudaGetDevice(&dev);
+        CUcontext prim = nullptr;
+        if (cuDevicePrimaryCtxRetain(&prim, dev) == CUDA_SUCCESS) cuCtxSetCurrent(prim);
+    }
+}
+
+// bf16 tensor map, 128-byte swizzle, zero fill out of bounds; estr = traversal strides (NULL = all 1).
+int encode(CUtensorMap* map, const void* ptr, int rank, const cuuint64_t* gdim, const cuuint64_t* gstride_bytes,
+           const cuuint32_t* box, const cuuint32_t* estr_in) {
+    cuuint32_t estr[5] = {1, 1, 1, 1, 1};
+    if (estr_in) for (int i = 0; i < rank; ++i) estr[i] = estr_in[i];
+    CUresult r = cuTensorMapEncodeTiled(map, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, rank, const_cast<void*>(ptr), gdim, gstride_bytes,
+                                        box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
+                                        CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS && getenv("LWC_DEBUG"))
+        fprintf(stderr, "lwc_convx: cuTensorMapEncodeTiled rank %d -> %d (dims %llu %llu %llu %llu box %u %u %u %u)\n", rank, (int)r,
+                (unsigned long long)gdim[0], (unsigned long long)gdim[1], rank > 2 ? (unsigned long long)gdim[2] : 0ULL,
+                rank > 3 ? (unsigned long long)gdim[3] : 0ULL, box[0], box[1], rank > 2 ? box[2] : 0, rank > 3 ? box[3] : 0);
+    return r == CUDA_SUCCESS ? 0 : LWC_EINVAL;
+}
+
+// Channels-last activation [N][H][W][C] (pixel pitch `cpitch` elements) as a 4-D map (C, W, H, N) whose boxes
+// are 64 channels x (bw, bh, bn) traversed pixels with traversal stride (s, s) over W and H.
+int encode_act(CUtensorMap* map, const void* ptr, int C, int cpitch, int W, int H, int N, int bw, int bh, int bn, int s) {
+    cuuint64_t gd[4] = {(cuuint64_t)C, (cuuint64_t)W, (cuuint64_t)H, (cuuint64_t)N};
+    cuuint64_t gs[3] = {(cuuint64_t)cpitch * 2, (cuuint64_t)W * cpitch * 2, (cuuint64_t)H * W * cpitch * 2};
+    cuuint32_t bx[4] = {64, (cuuint32_t)(bw * s), (cuuint32_t)(bh * s), (cuuint32_t)bn};
+    cuuint32_t es[4] = {1, (cuuint32_t)s, (cuuint32_t)s, 1};
+    if (bx[1] > 256 || bx[2] > 256 || bx[3] > 256) return LWC_EINVAL;
+    return encode(map, ptr, 4, gd, gs, bx, es);
+}
+
+// Pixel patch (Wb, Hb, Nb) for an output extent (OW, OH, ON): rows = Wb * Hb * Nb <= max_rows, and, when `mult` > 1,
+// a multiple of `mult` (the weight gradient's K steps).  Picks the best coverage, then the most rows, then the widest.
+struct Patch { int Wb, Hb, Nb, rows, tiles_w, tiles_h, tiles_n; };
+Patch pick_patch(int OW, int OH, int ON, int max_rows, int mult, int max_w) {
+    Patch best = {1, 1, 1, 1, OW, OH, ON};
+    double best_score = -1.0;
+    for (int wb = 1; wb <= OW && wb <= max_rows && wb <= max_w; ++wb) {
+        for (int hb = 1; hb <= OH && wb * hb <= max_rows && hb <= max_w; ++hb) {
+            int nmax = max_rows / (wb * hb);
+            if (nmax > 256) nmax = 256;
+            for (int nb = 1; nb <= nmax && nb <= ON; ++nb) {
+                const int rows = wb * hb * nb;
+                if (mult > 1 && rows % mult) continue;
+                const int tw = (OW + wb - 1) / wb, th = (OH + hb - 1) / hb, tn = (ON + nb - 1) / nb;
+                const double eff = (double)OW * OH * ON / ((double)tw * wb * th * hb * tn * nb);
+                const double score = eff * 1e6 + rows * 10.0 + wb * 0.01 + hb * 0.0001;
+                if (score > best_score) { best_score = score; best = {wb, hb, nb, rows, tw, th, tn}; }
+            }
+        }
+    }
+    return best;
+}
+
+struct FxGeom {
+    // input activation
+    const void* x; int C, cpitch, W, H, N;       // channels visible to the map, pixel pitch, extent
+    int window;                                  // 1: overlapping-window map (stem): W axis pitch = `wpitch` elements,
+    int wpitch;                                  //    `cpitch` is then the ROW pitch in elements
+    // weights: K-major [rows = Cout][Ktot] (b_mn = 0) or MN-major [Ktot][Cout] (b_mn = 1)
+    const void* w; int Ktot; int b_mn;
+    // output [ON][OH][OW][Cout] seen through (base, pitches): element strides in elements
+    void* y; int OW, OH, ON, Cout; long long y_wpitch, y_hpitch, y_npitch;
+    int stride;                                  // input traversal stride
+    int ntaps, kchunks;
+    short dw[MAXT], dh[MAXT]; int a_c0[MAXT], b_k0[MAXT];
+    const float* bias; int relu; float* stats; int bn_hint;
+};
+
+template <int BN, bool B_MN>
+int launch_fx(const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMap& tc_, const FxParams& p, int smem, int grid, cudaStream_t st) {
+    static bool attr = false;
+    if (!attr) {
+        LWC_CUDA_CHECK(cudaFuncSetAttribute(k_fx<BN, B_MN>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BUDGET));
+        attr = true;
+    }
+    k_fx<BN, B_MN><<<grid, THREADS, smem, st>>>(ta, tb, tc_, p);
+    return 0;
+}
+
+int pick_bn(int Cout, int hint) {
+    if ((hint == 64 || hint == 128 || hint == 256) && Cout % hint == 0) return hint;
+    if (Cout % 256 == 0) return 256;
+    if (Cout % 128 == 0) return 128;
+    return 64;
+}
+
+int run_fx(const FxGeom& g, cudaStream_t st, int* grid_out) {
+    if (g.Cout % 64 || g.ntaps < 1 || g.ntaps > MAXT || g.kchunks < 1) return LWC_EINVAL;
+    ensure_context();
+    const int BN = pick_bn(g.Cout, g.bn_hint);
+    FxParams p;
+    memset(&p, 0, sizeof(p));
+    const Patch pt = pick_patch(g.OW, g.OH, g.ON, BM, 1, 256 / g.stride);
+    p.N = g.Cout; p.ntaps = g.ntaps; p.kchunks = g.kchunks;
+    p.Wb = pt.Wb; p.Hb = pt.Hb; p.Nb = pt.Nb; p.tiles_w = pt.tiles_w; p.tiles_h = pt.tiles_h;
+    p.sw = g.stride; p.sh = g.stride; p.OW = g.OW; p.OH = g.OH; p.ON = g.ON;
+    p.tiles_m = pt.tiles_w * pt.tiles_h * pt.tiles_n; p.tiles_n = g.Cout / BN; p.rows_per_tile = pt.rows;
+    p.relu = g.relu; p.bias = g.bias; p.stats = g.stats;
+    for (int t = 0; t < g.ntaps; ++t) { p.dw[t] = g.dw[t]; p.dh[t] = g.dh[t]; p.a_c0[t] = g.a_c0[t]; p.b_k0[t] = g.b_k0[t]; }
+    // shared-memory plan
+    const int stage_bytes = BM * BK * 2 + BN * BK * 2;
+    const int stat_bytes = g.stats ? (2 * g.Cout + 512) * 4 : 0;
+    int ncs = 4;
+    const int fixed = 1024 + 256 + stat_bytes;
+    int stages = (SMEM_BUDGET - fixed - ncs * SUB_BYTES) / stage_bytes;
+    if (stages < 3) { ncs = 2; stages = (SMEM_BUDGET - fixed - ncs * SUB_BYTES) / stage_bytes; }
+    if (stages > 8) stages = 8;
+    if (stages < 2) return LWC_ETOOBIG;
+    p.stages = stages; p.ncs = ncs;
+    p.c_off = stages * stage_bytes;
+    p.stat_off = p.c_off + ncs * SUB_BYTES;
+    p.bar_off = p.stat_off + stat_bytes;
+    const int smem = p.bar_off + 256 + 1024;
+
+    CUtensorMap ta, tb, tc_;
+    int rc;
+    if (g.window) {
+        // overlapping windows: "pixel" w of the map starts wpitch elements after pixel w - 1 and spans 64 elements
+        cuuint64_t gd[4] = {64, (cuuint64_t)g.W, (cuuint64_t)g.H, (cuuint64_t)g.N};
+        cuuint64_t gs[3] = {(cuuint64_t)g.wpitch * 2, (cuuint64_t)g.cpitch * 2, (cuuint64_t)g.H * g.cpitch * 2};
+        cuuint32_t bx[4] = {64, (cuuint32_t)pt.Wb, (cuuint32_t)pt.Hb, (cuuint32_t)pt.Nb};
+        rc = encode(&ta, g.x, 4, gd, gs, bx, nullptr);
+    } else {
+        rc = encode_act(&ta, g.x, g.C, g.cpitch, g.W, g.H, g.N, pt.Wb, pt.Hb, pt.Nb, g.stride);
+    }
+    if (rc) return rc;
+    if (g.b_mn) {
+        cuuint64_t bd[2] = {(cuuint64_t)g.Cout, (cuuint64_t)g.Ktot}, bs[1] = {(cuuint64_t)g.Cout * 2};
+        cuuint32_t bb[2] = {64, BK};
+        rc = encode(&tb, g.w, 2, bd, bs, bb, nullptr);
+    } else {
+        cuuint64_t bd[2] = {(cuuint64_t)g.Ktot, (cuuint64_t)g.Cout}, bs[1] = {(cuuint64_t)g.Ktot * 2};
+        cuuint32_t bb[2] = {BK, (cuuint32_t)BN};
+        rc = encode(&tb, g.w, 2, bd, bs, bb, nullptr);
+    }
+    if (rc) return rc;
+    {
+        cuuint64_t cd[4] = {(cuuint64_t)g.Cout, (cuuint64_t)g.OW, (cuuint64_t)g.OH, (cuuint64_t)g.ON};
+        cuuint64_t cs[3] = {(cuuint64_t)g.y_wpitch * 2, (cuuint64_t)g.y_hpitch * 2, (cuuint64_t)g.y_npitch * 2};
+        cuuint32_t cb[4] = {64, (cuuint32_t)pt.Wb, (cuuint32_t)pt.Hb, (cuuint32_t)pt.Nb};
+        rc = encode(&tc_, g.y, 4, cd, cs, cb, nullptr);
+        if (rc) return rc;
+    }
+    int grid = p.tiles_m * p.tiles_n;
+    if (grid > sm_count()) grid = sm_count();
+    if (grid_out) *grid_out = grid;
+    if (BN == 256) rc = g.b_mn ? launch_fx<256, true>(ta, tb, tc_, p, smem, grid, st) : launch_fx<256, false>(ta, tb, tc_, p, smem, grid, st);
+    else if (BN == 128) rc = g.b_mn ? launch_fx<128, true>(ta, tb, tc_, p, smem, grid, st) : launch_fx<128, false>(ta, tb, tc_, p, smem, grid, st);
+    else rc = g.b_mn ? launch_fx<64, true>(ta, tb, tc_, p, smem, grid, st) : launch_fx<64, false>(ta, tb, tc_, p, smem, grid, st);
+    if (rc) return rc;
+    return (int)cudaGetLastError();
+}
+
+}  // namespace
+
+// Number of per-CTA statistics partials a forward call may write (callers size the buffer [this][2][Cout]).
+extern "C" int lwc_convx_max_partials(void) { return sm_count(); }
+
+// Forward convolution, square kernel k (k * k <= 16), stride 1 or 2, symmetric padding `pad`.
+//   x    : [N][H][W][Cx] bf16 channels-last; Cx % 8 == 0 (3-channel inputs are stored with 8 channels)
+//   wt   : [Cout][k*k][Kc] bf16 with Kc = round_up(Cx, 64) (channels past Cx zero); Cout % 64 == 0
+//   y    : [N][OH][OW][Cout] bf16, OH = (H + 2 pad - k) / stride + 1
+//   bias : fp32 [Cout] or NULL; relu in {0, 1}
+//   stats: [lwc_convx_max_partials()][2][Cout] fp32 or NULL; *nparts_out receives the number of partials written
+//   bn_hint: 0 = automatic output-tile width, else 64 / 128 / 256
+extern "C" int lwc_convx_forward(const void* x, const void* wt, void* y, int N, int H, int W, int Cx, int Cout, int k, int stride,
+                                 int pad, const float* bias, int relu, float* stats, int* nparts_out, int bn_hint, void* stream) {
+    if (!x || !wt || !y || N <= 0 || H <= 0 || W <= 0 || (Cx % 8) || (Cout % 64) || k < 1 || k * k > MAXT) return LWC_EINVAL;
+    if (stride != 1 && stride != 2) return LWC_EINVAL;
+    FxGeom g;
+    memset(&g, 0, sizeof(g));
+    const int OH = (H + 2 * pad - k) / stride + 1, OW = (W + 2 * pad - k) / stride + 1;
+    if (OH <= 0 || OW <= 0) return LWC_EINVAL;
+    const int Kc = (Cx + 63) / 64 * 64;
+    g.x = x; g.C = Cx; g.cpitch = Cx; g.W = W; g.H = H; g.N = N;
+    g.w = wt; g.Ktot = k * k * Kc; g.b_mn = 0;
+    g.y = y; g.OW = OW; g.OH = OH; g.ON = N; g.Cout = Cout;
+    g.y_wpitch = Cout; g.y_hpitch = (long long)OW * Cout; g.y_npitch = (long long)OH * OW * Cout;
+    g.stride = stride; g.ntaps = k * k; g.kchunks = Kc / 64;
+    g.bias = bias; g.relu = relu; g.stats = stats; g.bn_hint = bn_hint;
+    if (k == 1 && stride == 1 && pad == 0) {
+        // flatten the pixels: any 128 consecutive rows form a tile
+        const long long M = (long long)N * H * W;
+        if (M > 0x7fffffffLL) return LWC_ETOOBIG;
+        g.W = (int)M; g.H = 1; g.N = 1; g.OW = (int)M; g.OH = 1; g.ON = 1;
+        g.y_hpitch = M * Cout; g.y_npitch = M * Cout;
+    }
+    for (int a = 0; a < k; ++a)
+        for (int b = 0; b < k; ++b) {
+            const int t = a * k + b;
+            g.dh[t] = (short)(a - pad); g.dw[t] = (short)(b - pad); g.a_c0[t] = 0; g.b_k0[t] = t * Kc;
+        }
+    return run_fx(g, (cudaStream_t)stream, nparts_out);
+}
+
+// 1x1 stride-1 data gradient with the forward weight as stored: dX[p][ci] = sum_co dY[p][co] * W[co][ci]
+// (W is the MN-major B operand: no transposed copy).  Cin, Cout multiples of 64.
+extern "C" int lwc_convx_dgrad1x1(const void* dy, const void* w, void* dx, long long M, int Cout, int Cin, int bn_hint, void* stream) {
+    if (!dy || !w || !dx || M <= 0 || M > 0x7fffffffLL || (Cout % 64) || (Cin % 64)) return LWC_EINVAL;
+    FxGeom g;
+    memset(&g, 0, sizeof(g));
+    g.x = dy; g.C = Cout; g.cpitch = Cout; g.W = (int)M; g.H = 1; g.N = 1;
+    g.w = w; g.Ktot = Cout; g.b_mn = 1;
+    g.y = dx; g.OW = (int)M; g.OH = 1; g.ON = 1; g.Cout = Cin;
+    g.y_wpitch = Cin; g.y_hpitch = M * Cin; g.y_npitch = M * Cin;
+    g.stride = 1; g.ntaps = 1; g.kchunks = Cout / 64; g.bn_hint = bn_hint;
+    return run_fx(g, (cudaStream_t)stream, nullptr);
+}
+
+// Data gradient of a k x k / stride s / pad convolution:  dX[h][w] = sum_{(a,b)} Wt[a][b] dY[(h + pad - a) / s][(w + pad - b) / s]
+// over the taps whose divisions are exact.  One launch per output parity class (s * s of them); classes without a tap
+// are zero (dX is cleared up front when there is one, e.g. 1x1 / stride 2).
+//   dy : [N][OH][OW][Cout];  wt_t : [Cin][k*k][Cout] bf16 (the forward weight with channels transposed, taps NOT flipped)
+//   dx : [N][H][W][Cin];  Cin, Cout multiples of 64
+extern "C" int lwc_convx_dgrad(const void* dy, const void* wt_t, void* dx, int N, int H, int W, int Cin, int Cout, int k, int stride,
+                               int pad, int bn_hint, void* stream) {
+    if (!dy || !wt_t || !dx || N <= 0 || (Cin % 64) || (Cout % 64) || k < 1 || k * k > MAXT) return LWC_EINVAL;
+    if (stride != 1 && stride != 2) return LWC_EINVAL;
+    const int OH = (H + 2 * pad - k) / stride + 1, OW = (W + 2 * pad - k) / stride + 1;
+    cudaStream_t st = (cudaStream_t)stream;
+    bool any_empty = false;
+    for (int ph = 0; ph < stride; ++ph)
+        for (int pw = 0; pw < stride; ++pw) {
+            int n = 0;
+            for (int a = 0; a < k; ++a)
+                for (int b = 0; b < k; ++b)
+                    if ((ph + pad - a) % stride == 0 && (pw + pad - b) % stride == 0) ++n;
+            if (!n) any_empty = true;
+        }
+    if (any_empty) LWC_CUDA_CHECK(cudaMemsetAsync(dx, 0, (size_t)N * H * W * Cin * 2, st));
+    for (int ph = 0; ph < stride; ++ph)
+        for (int pw = 0; pw < stride; ++pw) {
+            FxGeom g;
+            memset(&g, 0, sizeof(g));
+            int n = 0;
+            for (int a = 0; a < k; ++a)
+                for (int b = 0; b < k; ++b) {
+                    const int nh = ph + pad - a, nw = pw + pad - b;
+                    // C++ '%' and '/' truncate toward zero: exactness and the quotient are still right for negative nh
+                    if (nh % stride || nw % stride) continue;
+                    g.dh[n] = (short)(nh / stride); g.dw[n] = (short)(nw / stride); g.a_c0[n] = 0; g.b_k0[n] = (a * k + b) * Cout;
+                    ++n;
+                }
+            if (!n) continue;
+            const int CH = (H - ph + stride - 1) / stride, CW = (W - pw + stride - 1) / stride;   // pixels of this class
+            if (CH <= 0 || CW <= 0) continue;
+            g.x = dy; g.C = Cout; g.cpitch = Cout; g.W = OW; g.H = OH; g.N = N;
+            g.w = wt_t; g.Ktot = k * k * Cout; g.b_mn = 0;
+            g.y = (char*)dx + ((size_t)ph * W + pw) * Cin * 2; g.OW = CW; g.OH = CH; g.ON = N; g.Cout = Cin;
+            g.y_wpitch = (long long)stride * Cin; g.y_hpitch = (long long)stride * W * Cin; g.y_npitch = (long long)H * W * Cin;
+            g.stride = 1; g.ntaps = n; g.kchunks = Cout / 64; g.bn_hint = bn_hint;
+            const int rc = run_fx(g, st, nullptr);
+            if (rc) return rc;
+        }
+    return 0;
+}
+
+// The 7x7/2 ResNet stem on the 2x2 space-to-depth input (see lwc_normalize_u8 mode 1): a dense 4x4/1 convolution
+// whose four kernel rows are the taps and whose 4 pixels x 16 channels kernel-row windows (128 bytes, overlapping,
+// one pixel apart) are the K = 64 chunks.
+//   xs : [N][OH+3][OW+3][16] bf16;  w4 : [Cout][4 rows][4 cols * 16 ch] bf16 (s2d_stem_weight, channels-last);  y : [N][OH][OW][Cout]
+extern "C" int lwc_convx_stem_forward(const void* xs, const void* w4, void* y, int N, int OH, int OW, int Cout, float* stats,
+                                      int* nparts_out, int bn_hint, void* stream) {
+    if (!xs || !w4 || !y || N <= 0 || OH <= 0 || OW <= 0 || (Cout % 64)) return LWC_EINVAL;
+    FxGeom g;
+    memset(&g, 0, sizeof(g));
+    g.x = xs; g.window = 1; g.wpitch = 16; g.cpitch = (OW + 3) * 16; g.W = OW; g.H = OH + 3; g.N = N; g.C = 64;
+    g.w = w4; g.Ktot = 256; g.b_mn = 0;
+    g.y = y; g.OW = OW; g.OH = OH; g.ON = N; g.Cout = Cout;
+    g.y_wpitch = Cout; g.y_hpitch = (long long)OW * Cout; g.y_npitch = (long long)OH * OW * Cout;
+    g.stride = 1; g.ntaps = 4; g.kchunks = 1; g.stats = stats; g.bn_hint = bn_hint;
+    for (int a = 0; a < 4; ++a) { g.dh[a] = (short)a; g.dw[a] = 0; g.a_c0[a] = 0; g.b_k0[a] = a * 64; }
+    return run_fx(g, (cudaStream_t)stream, nparts_out);
+}
+
+// Batch-norm statistics from the forward kernel's per-CTA partials.
+extern "C" int lwc_convx_stats_finalize(const float* partials, int nparts, int C, long long count, float eps, float momentum,
+                                        float* mean, float* invstd, float* running_mean, float* running_var,
+                                        long long* num_batches_tracked, void* stream) {
+    if (!partials || nparts <= 0 || C <= 0 || count <= 0 || !mean || !invstd) return LWC_EINVAL;
+    k_stats_finalize<<<(C + 7) / 8, 256, 0, (cudaStream_t)stream>>>(partials, nparts, C, (double)count, eps, momentum, mean, invstd,
+                                                                    running_mean, running_var, num_batches_tracked);
+    return (int)cudaGetLastError();
+}
+
+namespace {
+
+struct WxPlan { WxParams p; int BN; int smem; int ngroups; Patch pt; size_t ws_bytes; };
+
+int plan_wx(int N, int H, int W, int Cx, int Cout, int k, int stride, int pad, int bn_hint, WxPlan* out) {
+    if (N <= 0 || H <= 0 || W <= 0 || (Cx % 8) || (Cout % 64) || k < 1 || k * k > MAXT) return LWC_EINVAL;
+    if (stride != 1 && stride != 2) return LWC_EINVAL;
+    int OH = (H + 2 * pad - k) / stride + 1, OW = (W + 2 * pad - k) / stride + 1, ON = N;
+    if (OH <= 0 || OW <= 0) return LWC_EINVAL;
+    if (k == 1 && stride == 1 && pad == 0) {
+        const long long M = (long long)N * H * W;
+        if (M > 0x7fffffffLL) return LWC_ETOOBIG;
+        OW = (int)M; OH = 1; ON = 1;
+    }
+    WxPlan& P = *out;
+    memset(&P, 0, sizeof(P));
+    WxParams& p = P.p;
+    const int BN = pick_bn(Cout, bn_hint);
+    p.Cout = Cout; p.cchunks = (Cx + 63) / 64; p.Cin_pad = p.cchunks * 64; p.ntaps = k * k; p.nboxes = p.ntaps * p.cchunks;
+    const int nslices = (p.nboxes + 1) / 2;
+    p.nacc = 512 / BN;
+    if (p.nacc > nslices) p.nacc = nslices;
+    p.groups_per_co = (nslices + p.nacc - 1) / p.nacc;
+    p.nacc = (nslices + p.groups_per_co - 1) / p.groups_per_co;          // balance the groups
+    P.ngroups = p.groups_per_co * (Cout / BN);
+    P.BN = BN;
+    int stages = 0;
+    Patch pt = {};
+    for (int max_rows = 64; max_rows >= 16; max_rows /= 2) {
+        pt = pick_patch(OW, OH, ON, max_rows, 16, 256 / stride);
+        if (pt.rows % 16) continue;
+        p.PK = pt.rows;
+        p.stage_bytes = p.PK * 128 * (BN / 64 + 2 * p.nacc);
+        stages = (SMEM_BUDGET - 2048) / p.stage_bytes;
+        if (stages >= 3 || max_rows == 16) break;
+    }
+    if (pt.rows % 16 || stages < 2) return LWC_ETOOBIG;
+    if (stages > 8) stages = 8;
+    p.stages = stages;
+    p.bar_off = stages * p.stage_bytes;
+    P.smem = p.bar_off + 256 + 1024;
+    p.Wb = pt.Wb; p.Hb = pt.Hb; p.Nb = pt.Nb; p.tiles_w = pt.tiles_w; p.tiles_h = pt.tiles_h;
+    p.npatches = pt.tiles_w * pt.tiles_h * pt.tiles_n;
+    p.sw = stride; p.sh = stride;
+    int ks = sm_count() / P.ngroups;
+    if (ks < 1) ks = 1;
+    if (ks > p.npatches) ks = p.npatches;
+    p.ksplit = ks;
+    for (int a = 0; a < k; ++a)
+        for (int b = 0; b < k; ++b) { p.dh[a * k + b] = (short)(a - pad); p.dw[a * k + b] = (short)(b - pad); }
+    P.pt = pt;
+    P.ws_bytes = (size_t)ks * p.nboxes * 64 * Cout * sizeof(float);
+    return 0;
+}
+
+template <int BN>
+int launch_wx(const CUtensorMap& tx, const CUtensorMap& td, const WxPlan& P, cudaStream_t st) {
+    static bool attr = false;
+    if (!attr) {
+        LWC_CUDA_CHECK(cudaFuncSetAttribute(k_wx<BN>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BUDGET));
+        attr = true;
+    }
+    k_wx<BN><<<dim3(P.ngroups, P.p.ksplit), THREADS, P.smem, st>>>(tx, td, P.p);
+    return 0;
+}
+
+}  // namespace
+
+extern "C" size_t lwc_convx_wgrad_workspace_bytes(int N, int H, int W, int Cx, int Cout, int k, int stride, int pad, int bn_hint) {
+    WxPlan P;
+    if (plan_wx(N, H, W, Cx, Cout, k, stride, pad, bn_hint, &P)) return 0;
+    return P.ws_bytes;
+}
+
+// Weight gradient  dW[co][tap][ci] = scale * sum_p dY[p][co] * X[p * stride + tap - pad][ci].
+//   x  : [N][H][W][Cx] bf16 (Cx % 8 == 0);  dy : [N][OH][OW][Cout] bf16
+//   dw : [Cout][k*k][Cin_out] in out_dtype (LWC_BF16 / LWC_F32); Cin_out <= Cx (3 for an 8-channel-stored RGB input)
+//   workspace : lwc_convx_wgrad_workspace_bytes(...) bytes of fp32 partials
+extern "C" int lwc_convx_wgrad(const void* x, const void* dy, void* dw, float* workspace, int N, int H, int W, int Cx, int Cout,
+                               int Cin_out, int k, int stride, int pad, int out_dtype, float scale, int bn_hint, void* stream) {
+    if (!x || !dy || !dw || !workspace || Cin_out <= 0 || Cin_out > Cx) return LWC_EINVAL;
+    if (out_dtype != LWC_F32 && out_dtype != LWC_BF16) return LWC_EINVAL;
+    WxPlan P;
+    int rc = plan_wx(N, H, W, Cx, Cout, k, stride, pad, bn_hint, &P);
+    if (rc) return rc;
+    ensure_context();
+    cudaStream_t st = (cudaStream_t)stream;
+    P.p.ws = workspace;
+    int OH = (H + 2 * pad - k) / stride + 1, OW = (W + 2 * pad - k) / stride + 1, ON = N;
+    int XW = W, XH = H, XN = N;
+    if (k == 1 && stride == 1 && pad == 0) {
+        const long long M = (long long)N * H * W;
+        OW = (int)M; OH = 1; ON = 1; XW = (int)M; XH = 1; XN = 1;
+    }
+    CUtensorMap tx, td;
+    rc = encode_act(&tx, x, Cx, Cx, XW, XH, XN, P.pt.Wb, P.pt.Hb, P.pt.Nb, stride);
+    if (rc) return rc;
+    rc = encode_act(&td, dy, Cout, Cout, OW, OH, ON, P.pt.Wb, P.pt.Hb, P.pt.Nb, 1);
+    if (rc) return rc;
+    if (P.BN == 256) rc = launch_wx<256>(tx, td, P, st);
+    else if (P.BN == 128) rc = launch_wx<128>(tx, td, P, st);
+    else rc = launch_wx<64>(tx, td, P, st);
+    if (rc) return rc;
+    const dim3 rg(P.p.nboxes, Cout / 64), rb(64, 4);
+    if (out_dtype == LWC_F32)
+        k_wx_reduce<float><<<rg, rb, 0, st>>>(workspace, (float*)dw, P.p.ksplit, P.p.nboxes, P.p.cchunks, Cout, Cin_out, P.p.ntaps, scale);
+    else
+        k_wx_reduce<__nv_bfloat16><<<rg, rb, 0, st>>>(workspace, (__nv_bfloat16*)dw, P.p.ksplit, P.p.nboxes, P.p.cchunks, Cout, Cin_out,
+                                                      P.p.ntaps, scale);
+    return (int)cudaGetLastError();
+}
