@@ -19,12 +19,24 @@ from ..ops import nn as lnn
 __all__ = ["ResNet", "resnet18", "resnet34", "resnet50", "resnet101", "resnet152"]
 
 
+def _stats_on():
+    from ..ops import conv as _conv
+    return _conv._FUSE_STATS["on"]
+
+
+def _bn_fed(conv):
+    """Every convolution of these networks feeds a batch norm: its epilogue sums the batch statistics
+    (``ops/conv.py``), so the batch norm runs no statistics pass of its own."""
+    conv.emit_bn_stats = True
+    return conv
+
+
 def conv3x3(c_in, c_out, stride=1):
-    return lnn.Conv2d(c_in, c_out, kernel_size=3, stride=stride, padding=1, bias=False)
+    return _bn_fed(lnn.Conv2d(c_in, c_out, kernel_size=3, stride=stride, padding=1, bias=False))
 
 
 def conv1x1(c_in, c_out, stride=1):
-    return lnn.Conv2d(c_in, c_out, kernel_size=1, stride=stride, bias=False)
+    return _bn_fed(lnn.Conv2d(c_in, c_out, kernel_size=1, stride=stride, bias=False))
 
 
 class BasicBlock(nn.Module):
@@ -85,7 +97,7 @@ class ResNet(nn.Module):
     def __init__(self, block, layers, num_classes=1000, bn0=False):
         super().__init__()
         self.inplanes = 64
-        self.conv1 = lnn.Conv2d(3, 64, kernel_size=7, stride=2, padding=3, bias=False)
+        self.conv1 = _bn_fed(lnn.Conv2d(3, 64, kernel_size=7, stride=2, padding=3, bias=False))
         self.bn1 = lnn.BatchNorm2d(64)
         self.relu = lnn.ReLU(inplace=True)
         self.maxpool = lnn.MaxPool2d(kernel_size=3, stride=2, padding=1)
@@ -127,7 +139,7 @@ class ResNet(nn.Module):
         (K = 256 instead of a 3-channel 7x7 window), which maps onto the tensor cores far better."""
         if x.shape[1] == 16:
             from ..ops.input import stem_s2d
-            return stem_s2d(x, self.conv1.weight)
+            return stem_s2d(x, self.conv1.weight, want_stats=self.training and torch.is_grad_enabled() and _stats_on())
         return self.conv1(x)
 
     def forward(self, x):

@@ -62,7 +62,7 @@ class _BatchNormAct(torch.autograd.Function):
 
     @staticmethod
     def forward(ctx, x, weight, bias, running_mean, running_var, residual, training, momentum, eps, relu,
-                num_batches_tracked=None):
+                num_batches_tracked=None, stat_partials=None, stat_nparts=0, stat_count=0):
         lib = _native.lib()
         M, Cc = _rows_channels(x)
         y = torch.empty_like(x)       # preserves the channels-last strides
@@ -77,12 +77,23 @@ class _BatchNormAct(torch.autograd.Function):
         mask = None
         if training and relu and residual is not None:
             mask = torch.empty(M * Cc // 8, dtype=torch.uint8, device=x.device)
-        rc = lib.lwc_bn_forward_ex(x.data_ptr(), y.data_ptr(), _ptr(residual), _ptr(weight), _ptr(bias), _ptr(mean),
-                                   _ptr(invstd), _ptr(running_mean), _ptr(running_var), ws_ptr, M, Cc,
-                                   abi.dtype_code(x.dtype), int(training), int(relu), float(eps), float(momentum),
-                                   _ptr(num_batches_tracked), _ptr(mask), C.c_void_p(st))
-        abi.check(rc, "lwc_bn_forward_ex")
-        _native.counters.add(3 if training else 1)
+        if training and stat_partials is not None:
+            # the producing convolution's epilogue already summed the batch statistics: finalize + apply only
+            rc = lib.lwc_convx_stats_finalize(stat_partials.data_ptr(), int(stat_nparts), Cc, int(stat_count), float(eps),
+                                              float(momentum), mean.data_ptr(), invstd.data_ptr(), _ptr(running_mean),
+                                              _ptr(running_var), _ptr(num_batches_tracked), C.c_void_p(st))
+            abi.check(rc, "lwc_convx_stats_finalize")
+            rc = lib.lwc_bn_apply_stats(x.data_ptr(), y.data_ptr(), _ptr(residual), _ptr(weight), _ptr(bias), mean.data_ptr(),
+                                        invstd.data_ptr(), M, Cc, abi.dtype_code(x.dtype), int(relu), _ptr(mask), C.c_void_p(st))
+            abi.check(rc, "lwc_bn_apply_stats")
+            _native.counters.add(2)
+        else:
+            rc = lib.lwc_bn_forward_ex(x.data_ptr(), y.data_ptr(), _ptr(residual), _ptr(weight), _ptr(bias), _ptr(mean),
+                                       _ptr(invstd), _ptr(running_mean), _ptr(running_var), ws_ptr, M, Cc,
+                                       abi.dtype_code(x.dtype), int(training), int(relu), float(eps), float(momentum),
+                                       _ptr(num_batches_tracked), _ptr(mask), C.c_void_p(st))
+            abi.check(rc, "lwc_bn_forward_ex")
+            _native.counters.add(3 if training else 1)
         ctx.training, ctx.relu, ctx.has_res = training, relu, residual is not None
         ctx.eps = eps
         # the ReLU mask is recomputed from x unless a residual was fused (then it depends on y)
@@ -112,7 +123,7 @@ class _BatchNormAct(torch.autograd.Function):
             xhat = (x.float() - mean.view(shape)) * torch.rsqrt(invstd + ctx.eps).view(shape)
             dims = (0, 2, 3) if x.dim() == 4 else (0,)
             return (dx, (g.float() * xhat).sum(dims), g.float().sum(dims), None, None,
-                    g if ctx.has_res else None, None, None, None, None, None)
+                    g if ctx.has_res else None, None, None, None, None, None, None, None, None)
         dx = torch.empty_like(x)
         premasked = ctx.mask_taken is not None and ctx.mask_taken[0]
         if premasked:
@@ -134,16 +145,20 @@ class _BatchNormAct(torch.autograd.Function):
             dres = dy
         _native.counters.add(3)
         return (dx, dgamma if weight is not None else None, dbeta if weight is not None else None, None, None,
-                dres, None, None, None, None, None)
+                dres, None, None, None, None, None, None, None, None)
 
 
 def batch_norm_act(x, weight, bias, running_mean, running_var, residual=None, training=True,
-                   momentum=0.1, eps=1e-5, relu=False, num_batches_tracked=None):
+                   momentum=0.1, eps=1e-5, relu=False, num_batches_tracked=None, stats=None):
     """``relu?(batch_norm(x) + residual?)`` in one fused pass structure (see module docstring).
     ``num_batches_tracked`` (int64 CUDA scalar) is incremented inside the statistics-finalize kernel."""
     _BatchNormAct.last_mask = (None, None)
-    y = _BatchNormAct.apply(x, weight, bias, running_mean, running_var, residual, training, momentum, eps, relu,
-                            num_batches_tracked)
+    if stats is not None and training:
+        y = _BatchNormAct.apply(x, weight, bias, running_mean, running_var, residual, training, momentum, eps, relu,
+                                num_batches_tracked, stats.partials, stats.nparts, stats.count)
+    else:
+        y = _BatchNormAct.apply(x, weight, bias, running_mean, running_var, residual, training, momentum, eps, relu,
+                                num_batches_tracked)
     mask, taken = _BatchNormAct.last_mask
     if mask is not None:
         y.relu_mask, y.relu_mask_taken = mask, taken       # see ops.conv.fork_conv1x1
@@ -165,4 +180,5 @@ def maybe_batch_norm(module, x, residual=None, relu=False):
             nbt.add_(1)
             nbt = None
     return batch_norm_act(x, module.weight, module.bias, module.running_mean, module.running_var,
-                          residual, training, module.momentum, module.eps, relu, nbt)
+                          residual, training, module.momentum, module.eps, relu, nbt,
+                          stats=getattr(x, "bn_stats", None))

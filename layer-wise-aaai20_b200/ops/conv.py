@@ -1,20 +1,26 @@
-"""Convolution front end for the persistent tcgen05 implicit-GEMM kernel (``csrc/conv.cu``).
+"""Convolution front end for the tcgen05 convolution kernels (``csrc/convx.cu``, ``csrc/conv.cu``).
 
-Covers stride-1 "same" convolutions with 1x1 and 3x3 kernels on channels-last bf16 activations whose channel
-counts are multiples of 64: forward (optionally emitting batch-norm statistics partials from the epilogue) and the
-data gradient (a convolution with the spatially flipped, channel-transposed kernel).  Weight gradients of 1x1
-layers go through the split-K MN-major GEMM (``ops/gemm.py``); everything else falls back to the stock op.
+Every convolution of the model zoo runs on hand-written sm_100a kernels: forward (optionally with bias + ReLU in
+the epilogue, optionally emitting batch-norm statistics so that the following batch norm skips its statistics
+pass), data gradient and weight gradient, for square kernels with ``k * k <= 16``, stride 1 or 2, channels-last
+bf16 activations, ``Cout % 64 == 0`` and any ``Cin`` (3-channel inputs are stored with 8 channels; the padding to
+the 64-wide K chunk happens in the TMA descriptor).  The ResNet stem runs on the same kernel through an
+overlapping-window tensor map over the space-to-depth input (``ops/input.py``).
 
-Reference ops: ``nn.Conv2d`` forward / backward through cuDNN (IMAGENET/training/resnet.py:21-24,:55-69,
-CIFAR10/dawn.py:23-35).
+The output-tile width (64 / 128 / 256 channels) is chosen per layer shape by timing the candidates once, the way
+the reference relies on ``cudnn.benchmark = True`` (CIFAR10/torch_backend.py:7, train_imagenet_nv.py:95).
+
+Reference ops: ``nn.Conv2d`` forward / backward through cuDNN (IMAGENET/training/resnet.py:18-21,59-66,100-101,
+122-126; CIFAR10/dawn.py:23-35; CIFAR10/alexnet.py:15-27; CIFAR10/vgg16.py:69-82).
 """
 from __future__ import annotations
 
 import ctypes as C
 import os
-from typing import Optional, Tuple
+from typing import Dict, Optional, Tuple
 
 import torch
+import torch.nn.functional as F
 
 from .. import _native
 from .._native import abi
@@ -24,111 +30,278 @@ def _nhwc(x: torch.Tensor) -> bool:
     return x.dim() == 4 and x.is_contiguous(memory_format=torch.channels_last)
 
 
+def _stream():
+    return C.c_void_p(torch.cuda.current_stream().cuda_stream)
+
+
+# ---- per-shape choice of the output-tile width -----------------------------------------------------------------
+_TUNE: Dict[tuple, int] = {}
+_TUNE_ON = {"on": os.environ.get("LWC_CONV_TUNE", "1") != "0"}
+
+
+def autotune(flag: bool = True):
+    """Time the tile-width candidates on the first call of every new layer shape (default on)."""
+    _TUNE_ON["on"] = bool(flag)
+
+
+def _candidates(cout: int):
+    return [b for b in (64, 128, 256) if cout % b == 0] or [64]
+
+
+def _tuned(key: tuple, cout: int, run) -> int:
+    """``run(bn_hint)`` launches the kernel; returns the fastest hint for ``key`` (cached)."""
+    hint = _TUNE.get(key)
+    if hint is not None:
+        return hint
+    cands = _candidates(cout)
+    if not _TUNE_ON["on"] or len(cands) == 1 or torch.cuda.is_current_stream_capturing():
+        return 0
+    best, best_t = 0, float("inf")
+    for b in cands:
+        run(b)                                      # warm-up (also sets the kernel's shared-memory attribute)
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(3):
+            run(b)
+        e1.record()
+        e1.synchronize()
+        t = e0.elapsed_time(e1)
+        if t < best_t:
+            best, best_t = b, t
+    _TUNE[key] = best
+    return best
+
+
+def tuned_table() -> Dict[tuple, int]:
+    return dict(_TUNE)
+
+
+# ---- operand preparation --------------------------------------------------------------------------------------
+def _prep_input(x: torch.Tensor) -> torch.Tensor:
+    """Channels-last with a channel count the TMA unit can address (multiple of 8: 16-byte pixel pitch)."""
+    if x.shape[1] % 8:
+        x = F.pad(x, (0, 0, 0, 0, 0, 8 - x.shape[1] % 8))
+    if not _nhwc(x):
+        x = x.contiguous(memory_format=torch.channels_last)
+    return x
+
+
+def _prep_weight(weight: torch.Tensor) -> torch.Tensor:
+    """[Cout, Cin, k, k] -> memory [Cout][k*k][Kc] with Kc = round_up(Cin, 64) (zero-padded only when needed)."""
+    ci = weight.shape[1]
+    w = weight.detach().permute(0, 2, 3, 1)        # a view when the weight is channels-last
+    if ci % 64:
+        w = F.pad(w, (0, 64 - ci % 64))
+    return w.contiguous()
+
+
 def supported(x: torch.Tensor, weight: torch.Tensor, stride, padding, dilation, groups) -> bool:
-    if not (x.is_cuda and x.dtype == torch.bfloat16 and weight.dtype == torch.bfloat16 and _nhwc(x)):
+    if not (x.is_cuda and x.dim() == 4 and x.dtype == torch.bfloat16 and weight.dtype == torch.bfloat16):
+        return False
+    if isinstance(padding, str):
         return False
     co, ci, kh, kw = weight.shape
-    if kh != kw or kh not in (1, 3) or tuple(stride) != (1, 1) or tuple(dilation) != (1, 1) or groups != 1:
+    s, p = tuple(stride), tuple(padding)
+    if kh != kw or kh * kw > 16 or s[0] != s[1] or s[0] not in (1, 2) or tuple(dilation) != (1, 1) or groups != 1:
         return False
-    if tuple(padding) != (kh // 2, kh // 2) or ci % 64 or co % 64:
+    if p[0] != p[1] or co % 64:
         return False
-    return weight.is_contiguous(memory_format=torch.channels_last) or kh == 1
+    return x.shape[1] == ci
 
 
-def tiles_m(n: int, h: int, w: int, kh: int) -> Tuple[int, int]:
-    rows = C.c_int(0)
-    t = int(_native.lib().lwc_conv_tiles_m(n, h, w, kh, C.byref(rows)))
-    return t, int(rows.value)
+def out_hw(h: int, w: int, k: int, stride: int, pad: int) -> Tuple[int, int]:
+    return (h + 2 * pad - k) // stride + 1, (w + 2 * pad - k) // stride + 1
+
+
+# ---- kernels ----------------------------------------------------------------------------------------------------
+class Stats:
+    """Per-CTA batch-norm partials written by a forward kernel: ``partials[:nparts]`` = [sum, sum of squares] per
+    channel over ``count`` output pixels."""
+    __slots__ = ("partials", "nparts", "count")
+
+    def __init__(self, partials, nparts, count):
+        self.partials, self.nparts, self.count = partials, nparts, count
+
+    def sums(self) -> torch.Tensor:
+        return self.partials[: self.nparts].sum(0)
 
 
 def conv_forward(x: torch.Tensor, weight: torch.Tensor, bias: Optional[torch.Tensor] = None, relu: bool = False,
-                 want_stats: bool = False, b_mn: bool = False, out_channels: Optional[int] = None):
-    """``y = conv(x, weight)``; returns ``(y, stats)`` with ``stats`` = ``[tiles_m, 2, Cout]`` fp32 or ``None``.
-
-    ``weight`` is the channels-last forward weight ``[Cout, Cin, k, k]`` (memory order Cout, k, k, Cin).  With
-    ``b_mn`` (1x1 only) ``weight`` is used as stored ``[K][N]``, which turns the call into the data-gradient GEMM.
-    """
+                 want_stats: bool = False, stride: int = 1, padding: Optional[int] = None, bn_hint: Optional[int] = None):
+    """``y = relu?(conv(x, weight) + bias?)``; returns ``(y, Stats | None)``.  ``x`` [N,Cin,H,W] channels-last bf16,
+    ``weight`` [Cout,Cin,k,k] bf16."""
     lib = _native.lib()
-    n, ci, h, w = x.shape
-    kh = weight.shape[2]
-    co = out_channels if out_channels is not None else weight.shape[0]
-    y = torch.empty((n, co, h, w), dtype=x.dtype, device=x.device, memory_format=torch.channels_last)
-    stats = None
+    co, ci, k, _ = weight.shape
+    pad = k // 2 if padding is None else int(padding)
+    xin = _prep_input(x.detach())
+    n, cx, h, w = xin.shape
+    oh, ow = out_hw(h, w, k, stride, pad)
+    wt = _prep_weight(weight)
+    y = torch.empty((n, co, oh, ow), dtype=x.dtype, device=x.device, memory_format=torch.channels_last)
+    part = None
     if want_stats:
-        tm, _ = tiles_m(n, h, w, kh)
-        stats = torch.empty((tm, 2, co), dtype=torch.float32, device=x.device)
+        part = torch.empty((int(lib.lwc_convx_max_partials()), 2, co), dtype=torch.float32, device=x.device)
+    bptr = 0
     if bias is not None:
-        bias = bias.float().contiguous()
-    st = torch.cuda.current_stream().cuda_stream
-    rc = lib.lwc_conv_forward(x.data_ptr(), weight.data_ptr(), y.data_ptr(), n, h, w, ci, co, kh, int(b_mn),
-                              0 if bias is None else bias.data_ptr(), int(relu), 0 if stats is None else stats.data_ptr(),
-                              C.c_void_p(st))
-    abi.check(rc, "lwc_conv_forward")
+        bias = bias.detach().float().contiguous()
+        bptr = bias.data_ptr()
+    nparts = C.c_int(0)
+
+    def run(hint):
+        rc = lib.lwc_convx_forward(xin.data_ptr(), wt.data_ptr(), y.data_ptr(), n, h, w, cx, co, k, stride, pad, bptr,
+                                   int(relu), 0 if part is None else part.data_ptr(), C.byref(nparts), hint, _stream())
+        abi.check(rc, "lwc_convx_forward")
+
+    if bn_hint is None:
+        bn_hint = _tuned(("f", n, h, w, cx, co, k, stride, pad, want_stats), co, run)
+    run(bn_hint)
     _native.counters.add(1)
-    return y, stats
+    return y, (Stats(part, int(nparts.value), n * oh * ow) if want_stats else None)
 
 
-def flipped_transposed(weight: torch.Tensor) -> torch.Tensor:
-    """Kernel of the data-gradient convolution: ``Wd[ci, co, a, b] = W[co, ci, k-1-a, k-1-b]`` (channels-last)."""
-    return weight.flip(2, 3).transpose(0, 1).contiguous(memory_format=torch.channels_last)
+def conv_dgrad(dy: torch.Tensor, weight: torch.Tensor, in_hw: Tuple[int, int], stride: int = 1,
+               padding: Optional[int] = None, bn_hint: Optional[int] = None) -> torch.Tensor:
+    """Data gradient ``dX`` [N,Cin,H,W] of ``conv(x, weight)`` given ``dY`` (Cin, Cout multiples of 64)."""
+    lib = _native.lib()
+    co, ci, k, _ = weight.shape
+    pad = k // 2 if padding is None else int(padding)
+    if not _nhwc(dy):
+        dy = dy.contiguous(memory_format=torch.channels_last)
+    n = dy.shape[0]
+    h, w = in_hw
+    dx = torch.empty((n, ci, h, w), dtype=dy.dtype, device=dy.device, memory_format=torch.channels_last)
+    if k == 1 and stride == 1 and pad == 0:
+        wv = weight.detach().reshape(co, ci).contiguous()
+
+        def run(hint):
+            abi.check(lib.lwc_convx_dgrad1x1(dy.data_ptr(), wv.data_ptr(), dx.data_ptr(), n * h * w, co, ci, hint, _stream()),
+                      "lwc_convx_dgrad1x1")
+        nl = 1
+    else:
+        wt_t = weight.detach().permute(1, 2, 3, 0).contiguous()      # [Cin][k][k][Cout]
+
+        def run(hint):
+            abi.check(lib.lwc_convx_dgrad(dy.data_ptr(), wt_t.data_ptr(), dx.data_ptr(), n, h, w, ci, co, k, stride, pad, hint,
+                                          _stream()), "lwc_convx_dgrad")
+        nl = stride * stride
+    if bn_hint is None:
+        bn_hint = _tuned(("d", n, h, w, ci, co, k, stride, pad), ci, run)
+    run(bn_hint)
+    _native.counters.add(nl)
+    return dx
+
+
+_WS: Dict[tuple, torch.Tensor] = {}
+
+
+def _workspace(nbytes: int, device) -> torch.Tensor:
+    key = (device.index, torch.cuda.current_stream(device).cuda_stream)
+    ws = _WS.get(key)
+    if ws is None or ws.numel() * 4 < nbytes:
+        ws = _WS[key] = torch.empty(max(nbytes // 4 + 1, 1 << 20), dtype=torch.float32, device=device)
+    return ws
+
+
+def conv_wgrad(x: torch.Tensor, dy: torch.Tensor, weight_shape, stride: int = 1, padding: Optional[int] = None,
+               out_dtype=torch.bfloat16, scale: float = 1.0, bn_hint: Optional[int] = None) -> torch.Tensor:
+    """Weight gradient [Cout,Cin,k,k] (channels-last) from the layer input ``x`` and ``dY``."""
+    lib = _native.lib()
+    co, ci, k, _ = weight_shape
+    pad = k // 2 if padding is None else int(padding)
+    xin = _prep_input(x.detach())
+    if not _nhwc(dy):
+        dy = dy.contiguous(memory_format=torch.channels_last)
+    n, cx, h, w = xin.shape
+    dw = torch.empty((co, k, k, ci), dtype=out_dtype, device=x.device)
+
+    def run(hint):
+        nbytes = int(lib.lwc_convx_wgrad_workspace_bytes(n, h, w, cx, co, k, stride, pad, hint))
+        if nbytes == 0:
+            raise RuntimeError(f"conv_wgrad: unsupported shape {tuple(x.shape)} -> {tuple(weight_shape)}")
+        ws = _workspace(nbytes, x.device)
+        abi.check(lib.lwc_convx_wgrad(xin.data_ptr(), dy.data_ptr(), dw.data_ptr(), ws.data_ptr(), n, h, w, cx, co, ci, k,
+                                      stride, pad, abi.dtype_code(out_dtype), float(scale), hint, _stream()), "lwc_convx_wgrad")
+
+    if bn_hint is None:
+        bn_hint = _tuned(("w", n, h, w, cx, co, k, stride, pad), co, run)
+    run(bn_hint)
+    _native.counters.add(2)
+    return dw.permute(0, 3, 1, 2)                     # logical [Cout,Cin,k,k], channels-last memory
 
 
 class _ConvFn(torch.autograd.Function):
-    @staticmethod
-    def forward(ctx, x, weight, bias, want_stats):
-        y, stats = conv_forward(x, weight, bias, want_stats=want_stats)
-        ctx.save_for_backward(x, weight)
-        ctx.has_bias = bias is not None
-        ctx.mark_non_differentiable(*([stats] if stats is not None else []))
-        return (y, stats) if stats is not None else (y, None)
+    last_stats = None
 
     @staticmethod
-    def backward(ctx, dy, _dstats=None):
-        x, weight = ctx.saved_tensors
+    def forward(ctx, x, weight, bias, stride, padding, relu, want_stats):
+        y, stats = conv_forward(x, weight, bias, relu=relu, want_stats=want_stats, stride=stride, padding=padding)
+        ctx.save_for_backward(x, weight, y if relu else None)
+        ctx.conf = (stride, padding, relu, bias is not None)
+        _ConvFn.last_stats = stats
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        x, weight, y = ctx.saved_tensors
+        stride, padding, relu, has_bias = ctx.conf
+        if relu:
+            dy = dy * (y > 0)
         if not _nhwc(dy):
             dy = dy.contiguous(memory_format=torch.channels_last)
-        kh = weight.shape[2]
         dx = dw = db = None
         if ctx.needs_input_grad[0]:
-            if kh == 1:        # dX = dY * W with W used as stored [Cout][Cin] (MN-major B): no transpose pass
-                dx, _ = conv_forward(dy, weight, b_mn=True, out_channels=weight.shape[1])
-            else:
-                dx, _ = conv_forward(dy, flipped_transposed(weight))
+            if weight.shape[1] % 64 == 0:
+                dx = conv_dgrad(dy, weight, (x.shape[2], x.shape[3]), stride, padding)
+            else:       # not reached by the model zoo (only first layers have such inputs, and they need no dX)
+                dx = torch.ops.aten.convolution_backward(dy, x, weight, None, [stride] * 2, [padding] * 2, [1, 1], False,
+                                                         [0, 0], 1, [True, False, False])[0]
         if ctx.needs_input_grad[1]:
-            if kh == 1:
-                from .gemm import gemm
-                n, co, h, w = dy.shape
-                dy2 = dy.permute(0, 2, 3, 1).reshape(-1, co)
-                x2 = x.permute(0, 2, 3, 1).reshape(-1, x.shape[1])
-                dw = gemm(dy2, x2, a_mn=True, b_mn=True).view(co, x.shape[1], 1, 1).contiguous(memory_format=torch.channels_last)
-            else:
-                dw = torch.ops.aten.convolution_backward(dy, x, weight, None, [1, 1], [1, 1], [1, 1], False, [0, 0], 1,
-                                                         [False, True, False])[1]
-        if ctx.has_bias and ctx.needs_input_grad[2]:
+            dw = conv_wgrad(x, dy, weight.shape, stride, padding, out_dtype=weight.dtype)
+        if has_bias and ctx.needs_input_grad[2]:
             db = dy.float().sum((0, 2, 3)).to(dy.dtype)
-        return dx, dw, db, None
+        return dx, dw, db, None, None, None, None
 
 
-def conv2d(x, weight, bias=None, want_stats: bool = False):
-    """Autograd-aware native convolution; returns ``(y, stats_or_None)``."""
-    return _ConvFn.apply(x, weight, bias, want_stats)
+def conv2d(x, weight, bias=None, want_stats: bool = False, stride: int = 1, padding: Optional[int] = None,
+           relu: bool = False):
+    """Autograd-aware native convolution; returns ``(y, Stats | None)``."""
+    pad = weight.shape[2] // 2 if padding is None else int(padding)
+    _ConvFn.last_stats = None
+    y = _ConvFn.apply(x, weight, bias, int(stride), pad, bool(relu), bool(want_stats))
+    stats, _ConvFn.last_stats = _ConvFn.last_stats, None
+    return y, stats
 
 
-_ENABLED = {"on": False}
+_ENABLED = {"on": os.environ.get("LWC_NATIVE_CONV", "1") != "0"}
 
 
 def enable(flag: bool = True):
-    """Route eligible ``ops.nn.Conv2d`` layers through the native kernel (off by default: see DESIGN.md)."""
+    """Route ``ops.nn.Conv2d`` layers through the native kernels (default on)."""
     _ENABLED["on"] = bool(flag)
 
 
-def maybe_conv2d(module, x):
+def enabled() -> bool:
+    return _ENABLED["on"]
+
+
+_FUSE_STATS = {"on": os.environ.get("LWC_CONV_BN_STATS", "1") != "0"}
+
+
+def fuse_bn_stats(flag: bool = True):
+    """Let convolutions marked ``emit_bn_stats`` sum the following batch norm's statistics in their epilogue."""
+    _FUSE_STATS["on"] = bool(flag)
+
+
+def maybe_conv2d(module, x, relu: bool = False):
     """Module dispatch; returns ``None`` when the stock implementation must run."""
     if not _ENABLED["on"]:
         return None
     if not supported(x, module.weight, module.stride, module.padding, module.dilation, module.groups):
         return None
-    y, stats = conv2d(x, module.weight, module.bias, want_stats=getattr(module, "emit_bn_stats", False))
+    want = (_FUSE_STATS["on"] and bool(getattr(module, "emit_bn_stats", False)) and module.training
+            and torch.is_grad_enabled() and module.bias is None)
+    y, stats = conv2d(x, module.weight, module.bias, want_stats=want, stride=module.stride[0], padding=module.padding[0],
+                      relu=relu)
     if stats is not None:
         y.bn_stats = stats
     return y
@@ -143,14 +316,13 @@ def conv1x1_dgrad_add(dy: torch.Tensor, weight: torch.Tensor, addend: torch.Tens
     n, co, h, w = dy.shape
     ci = weight.shape[1]
     dx = torch.empty((n, ci, h, w), dtype=dy.dtype, device=dy.device, memory_format=torch.channels_last)
-    st = torch.cuda.current_stream().cuda_stream
     if relu_mask is not None:
         rc = lib.lwc_conv1x1_add_mask(dy.data_ptr(), weight.data_ptr(), addend.data_ptr(), relu_mask.data_ptr(), dx.data_ptr(),
-                                      n, h, w, co, ci, 1, C.c_void_p(st))
+                                      n, h, w, co, ci, 1, _stream())
         abi.check(rc, "lwc_conv1x1_add_mask")
     else:
         rc = lib.lwc_conv1x1_add(dy.data_ptr(), weight.data_ptr(), addend.data_ptr(), dx.data_ptr(), n, h, w, co, ci, 1,
-                                 C.c_void_p(st))
+                                 _stream())
         abi.check(rc, "lwc_conv1x1_add")
     _native.counters.add(1)
     return dx
@@ -170,9 +342,13 @@ class _ForkConv1x1(torch.autograd.Function):
     gradient runs on the tcgen05 kernel whose epilogue adds the skip-connection gradient on the way out."""
 
     @staticmethod
-    def forward(ctx, x, weight, relu_mask=None):
+    def forward(ctx, x, weight, relu_mask=None, want_stats=False):
         ctx.save_for_backward(x, weight, relu_mask)
-        y = torch.nn.functional.conv2d(x, weight)
+        if _ENABLED["on"]:
+            y, stats = conv_forward(x, weight, want_stats=want_stats, stride=1, padding=0)
+            _ConvFn.last_stats = stats
+        else:
+            y = F.conv2d(x, weight)
         return y, x.view_as(x)
 
     @staticmethod
@@ -185,15 +361,18 @@ class _ForkConv1x1(torch.autograd.Function):
             if d_identity is not None and _nhwc(d_identity) and d_identity.dtype == dy.dtype:
                 dx = conv1x1_dgrad_add(dy, weight, d_identity, relu_mask)
             else:
-                dx, _ = conv_forward(dy, weight, b_mn=True, out_channels=weight.shape[1])
+                dx = conv_dgrad(dy, weight, (x.shape[2], x.shape[3]), 1, 0)
                 if d_identity is not None:
                     dx = dx + d_identity
                 if relu_mask is not None:           # this function promised the producer a masked gradient
                     dx = apply_bitmask(dx, relu_mask)
         if ctx.needs_input_grad[1]:
-            dw = torch.ops.aten.convolution_backward(dy, x, weight, None, [1, 1], [0, 0], [1, 1], False, [0, 0], 1,
-                                                     [False, True, False])[1]
-        return dx, dw, None
+            if _ENABLED["on"]:
+                dw = conv_wgrad(x, dy, weight.shape, 1, 0, out_dtype=weight.dtype)
+            else:
+                dw = torch.ops.aten.convolution_backward(dy, x, weight, None, [1, 1], [0, 0], [1, 1], False, [0, 0], 1,
+                                                         [False, True, False])[1]
+        return dx, dw, None, None
 
 
 def fork_conv1x1(module, x):
@@ -210,9 +389,16 @@ def fork_conv1x1(module, x):
           and w.shape[0] % 64 == 0 and w.shape[1] % 64 == 0)
     if not ok:
         return module(x), x
+    want = _FUSE_STATS["on"] and bool(getattr(module, "emit_bn_stats", False)) and module.training and _ENABLED["on"]
     mask = getattr(x, "relu_mask", None)
     taken = getattr(x, "relu_mask_taken", None)
+    _ConvFn.last_stats = None
     if mask is not None and taken is not None and w.shape[1] % 128 == 0 and not os.environ.get("LWC_NO_PREMASK"):
         taken[0] = True
-        return _ForkConv1x1.apply(x, w, mask)
-    return _ForkConv1x1.apply(x, w)
+        y, ident = _ForkConv1x1.apply(x, w, mask, want)
+    else:
+        y, ident = _ForkConv1x1.apply(x, w, None, want)
+    stats, _ConvFn.last_stats = _ConvFn.last_stats, None
+    if stats is not None:
+        y.bn_stats = stats
+    return y, ident

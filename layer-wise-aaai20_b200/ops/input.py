@@ -72,37 +72,76 @@ class _StemS2D(torch.autograd.Function):
     4x4 form is ~2x slower than its 7x7 one on B200.  No input gradient: the stem consumes data."""
 
     @staticmethod
-    def forward(ctx, xs, x3, w7):
-        w = s2d_stem_weight(w7)
-        if xs.is_contiguous(memory_format=torch.channels_last):
-            w = w.contiguous(memory_format=torch.channels_last)
+    def forward(ctx, xs, x3, w7, want_stats=False):
         ctx.native = x3 is None
         ctx.save_for_backward(xs if x3 is None else x3, w7)
-        return F.conv2d(xs, w, None, stride=1, padding=0)
+        return stem_forward(xs, w7, want_stats)
 
     @staticmethod
     def backward(ctx, dy):
         x, w7 = ctx.saved_tensors
         if ctx.native:
-            return None, None, stem_wgrad(dy, x, w7.dtype)
+            return None, None, stem_wgrad(dy, x, w7.dtype), None
         gw = torch.ops.aten.convolution_backward(dy, x, w7, None, [2, 2], [3, 3], [1, 1], False, [0, 0], 1,
                                                  [False, True, False])[1]
-        return None, None, gw
+        return None, None, gw, None
 
 
-def stem_s2d(xs: torch.Tensor, w7: torch.Tensor) -> torch.Tensor:
+_LAST_STATS = {"v": None}
+
+
+def stem_forward_native_ok(xs: torch.Tensor, w7: torch.Tensor) -> bool:
+    from . import conv as _conv
+    return (_conv.enabled() and xs.is_cuda and _native.available() and xs.dtype == torch.bfloat16
+            and w7.dtype == torch.bfloat16 and tuple(w7.shape[1:]) == (3, 7, 7) and w7.shape[0] % 64 == 0
+            and xs.shape[1] == 16 and xs.is_contiguous(memory_format=torch.channels_last))
+
+
+def stem_forward(xs: torch.Tensor, w7: torch.Tensor, want_stats: bool = False) -> torch.Tensor:
+    """The stem convolution on the space-to-depth input: the tap-table tcgen05 kernel (four kernel-row taps over
+    overlapping 128-byte windows, K = 256) or, off the GPU, the equivalent dense 4x4 convolution."""
+    w = s2d_stem_weight(w7.detach())
+    _LAST_STATS["v"] = None
+    if not stem_forward_native_ok(xs, w7):
+        if xs.is_contiguous(memory_format=torch.channels_last):
+            w = w.contiguous(memory_format=torch.channels_last)
+        return F.conv2d(xs, w, None, stride=1, padding=0)
+    from .conv import Stats
+    lib = _native.lib()
+    n, _, hs, ws_ = xs.shape
+    oh, ow, co = hs - 3, ws_ - 3, w7.shape[0]
+    w4 = w.permute(0, 2, 3, 1).contiguous()                       # [Cout][4 rows][4 cols][16 ch]
+    y = torch.empty((n, co, oh, ow), dtype=xs.dtype, device=xs.device, memory_format=torch.channels_last)
+    part = None
+    if want_stats:
+        part = torch.empty((int(lib.lwc_convx_max_partials()), 2, co), dtype=torch.float32, device=xs.device)
+    nparts = C.c_int(0)
+    st = torch.cuda.current_stream().cuda_stream
+    abi.check(lib.lwc_convx_stem_forward(xs.data_ptr(), w4.data_ptr(), y.data_ptr(), n, oh, ow, co,
+                                         0 if part is None else part.data_ptr(), C.byref(nparts), 0, C.c_void_p(st)),
+              "lwc_convx_stem_forward")
+    _native.counters.add(1)
+    if want_stats:
+        _LAST_STATS["v"] = Stats(part, int(nparts.value), n * oh * ow)
+    return y
+
+
+def stem_s2d(xs: torch.Tensor, w7: torch.Tensor, want_stats: bool = False) -> torch.Tensor:
     x3 = getattr(xs, "plain3", None)
+    y = None
     if w7.requires_grad and torch.is_grad_enabled():
         if (xs.is_cuda and xs.dtype == torch.bfloat16 and w7.dtype == torch.bfloat16 and tuple(w7.shape) == (64, 3, 7, 7)
                 and xs.shape[1] == 16 and xs.is_contiguous(memory_format=torch.channels_last)
                 and stem_wgrad_native_ok(xs.shape[2] - 3, xs.shape[3] - 3, xs.dtype, w7.shape[0])):
-            return _StemS2D.apply(xs, None, w7)
-        if x3 is not None:
-            return _StemS2D.apply(xs, x3, w7)
-    w = s2d_stem_weight(w7)
-    if xs.is_contiguous(memory_format=torch.channels_last):
-        w = w.contiguous(memory_format=torch.channels_last)
-    return F.conv2d(xs, w, None, stride=1, padding=0)
+            y = _StemS2D.apply(xs, None, w7, want_stats)
+        elif x3 is not None:
+            y = _StemS2D.apply(xs, x3, w7, want_stats)
+    if y is None:
+        y = stem_forward(xs, w7, want_stats)
+    stats, _LAST_STATS["v"] = _LAST_STATS["v"], None
+    if stats is not None:
+        y.bn_stats = stats
+    return y
 
 
 def normalize_u8(x: torch.Tensor, dtype=torch.bfloat16, s2d: bool = False, mean=IMAGENET_MEAN, std=IMAGENET_STD,

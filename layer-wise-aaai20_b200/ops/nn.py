@@ -38,10 +38,11 @@ class Conv2d(nn.Conv2d):
     def forward(self, x):
         if _native_ok(x):
             from . import conv as _conv
-            y = _conv.maybe_conv2d(self, x)
+            y = _conv.maybe_conv2d(self, x, relu=getattr(self, "fuse_relu", False))
             if y is not None:
                 return y
-        return super().forward(x)
+        y = super().forward(x)
+        return F.relu(y) if getattr(self, "fuse_relu", False) else y
 
 
 class Linear(nn.Linear):
