@@ -1,4 +1,4 @@
-"""Persistent tcgen05 implicit-GEMM convolution vs an fp32 PyTorch reference."""
+"""tcgen05 tap-table convolution kernels (csrc/convx.cu, csrc/conv.cu) vs an fp32 PyTorch reference."""
 import os
 
 import pytest
@@ -28,7 +28,7 @@ def test_conv1x1_forward_stats_and_backward(n, ci, co, h, w):
     assert y.shape == yr.shape and y.is_contiguous(memory_format=torch.channels_last)
     assert (y.float() - yr).abs().max() <= 2e-2 * yr.abs().max()
     # epilogue statistics = column sums of the rounded output
-    s = stats.sum(0)
+    s = stats.sums()
     yf = y.float()
     assert torch.allclose(s[0], yf.sum((0, 2, 3)), rtol=1e-3, atol=1e-2)
     assert torch.allclose(s[1], (yf * yf).sum((0, 2, 3)), rtol=1e-3, atol=1e-2)
@@ -49,7 +49,7 @@ def test_conv3x3_forward_stats_and_dgrad(n, ci, co, h, w):
     ref_in, ref_w = x.float().requires_grad_(True), wt.float().requires_grad_(True)
     yr = F.conv2d(ref_in, ref_w, padding=1)
     assert (y.float() - yr).abs().max() <= 2e-2 * yr.abs().max()
-    s = stats.sum(0)
+    s = stats.sums()
     yf = y.float()
     assert torch.allclose(s[0], yf.sum((0, 2, 3)), rtol=1e-3, atol=2e-2)
     assert torch.allclose(s[1], (yf * yf).sum((0, 2, 3)), rtol=1e-3, atol=2e-2)
@@ -137,3 +137,115 @@ def test_fork_premasks_gradient_for_the_producing_batchnorm():
     assert rel(gx_a, gx_b) < 0.25, rel(gx_a, gx_b)
     for a, b in zip(gp_a, gp_b):
         assert rel(a, b) < 0.25, (a.shape, rel(a, b))
+
+
+def _rel(a, b):
+    return float((a.float() - b.float()).abs().max() / (b.float().abs().max() + 1e-12))
+
+
+@pytest.mark.parametrize("n,ci,co,h,w,k,stride,pad", [
+    (4, 128, 128, 56, 56, 3, 2, 1),      # ResNet-50 stage transitions: 3x3 / 2
+    (3, 256, 256, 28, 28, 3, 2, 1),
+    (5, 512, 512, 14, 14, 3, 2, 1),
+    (4, 256, 512, 56, 56, 1, 2, 0),      # 1x1 / 2 downsample
+    (3, 1024, 2048, 14, 14, 1, 2, 0),
+    (2, 64, 128, 15, 17, 3, 2, 1),       # odd extent
+    (2, 192, 384, 8, 8, 3, 1, 1),        # AlexNet channel counts
+    (2, 64, 192, 16, 16, 3, 1, 1),
+    (6, 64, 64, 2, 2, 3, 1, 1),          # tiny late VGG maps
+])
+def test_convx_strided_and_odd_shapes(n, ci, co, h, w, k, stride, pad):
+    from layerwise_b200.ops.conv import conv2d
+    x, wt = _mk(n, ci, co, h, w, k)
+    x1, w1 = x.clone().requires_grad_(True), wt.clone().requires_grad_(True)
+    y, stats = conv2d(x1, w1, None, want_stats=True, stride=stride, padding=pad)
+    ref_in, ref_w = x.float().requires_grad_(True), wt.float().requires_grad_(True)
+    yr = F.conv2d(ref_in, ref_w, stride=stride, padding=pad)
+    assert y.shape == yr.shape and y.is_contiguous(memory_format=torch.channels_last)
+    assert _rel(y, yr) <= 2e-2
+    s = stats.sums()
+    yf = y.float()
+    assert torch.allclose(s[0], yf.sum((0, 2, 3)), rtol=1e-3, atol=3e-2)
+    assert torch.allclose(s[1], (yf * yf).sum((0, 2, 3)), rtol=1e-3, atol=3e-2)
+    dy = torch.randn_like(y)
+    y.backward(dy)
+    yr.backward(dy.float())
+    assert _rel(x1.grad, ref_in.grad) <= 2e-2
+    assert _rel(w1.grad, ref_w.grad) <= 3e-2
+
+
+@pytest.mark.parametrize("bn", [64, 128, 256])
+@pytest.mark.parametrize("k", [1, 3])
+def test_convx_every_tile_width(bn, k):
+    from layerwise_b200.ops.conv import conv_forward, conv_dgrad, conv_wgrad
+    x, wt = _mk(3, 256, 256, 14, 14, k)
+    y, st = conv_forward(x, wt, want_stats=True, bn_hint=bn)
+    yr = F.conv2d(x.float(), wt.float(), padding=k // 2)
+    assert _rel(y, yr) <= 2e-2
+    assert torch.allclose(st.sums()[0], y.float().sum((0, 2, 3)), rtol=1e-3, atol=3e-2)
+    dy = torch.randn_like(y)
+    xi, wi = x.float().requires_grad_(True), wt.float().requires_grad_(True)
+    F.conv2d(xi, wi, padding=k // 2).backward(dy.float())
+    assert _rel(conv_dgrad(dy, wt, (14, 14), 1, k // 2, bn_hint=bn), xi.grad) <= 2e-2
+    assert _rel(conv_wgrad(x, dy, wt.shape, 1, k // 2, bn_hint=bn), wi.grad) <= 3e-2
+
+
+@pytest.mark.parametrize("n,co,h,w,k,stride,pad", [(8, 64, 32, 32, 3, 1, 1), (4, 64, 32, 32, 3, 2, 1), (2, 128, 9, 11, 3, 1, 1)])
+def test_convx_three_channel_input_bias_relu(n, co, h, w, k, stride, pad):
+    """First layers: 3 input channels (stored as 8, padded to the 64-wide K chunk by the TMA descriptor), bias + ReLU
+    fused in the epilogue (CIFAR10/alexnet.py:15-16, CIFAR10/vgg16.py:69-82, CIFAR10/dawn.py:23-28)."""
+    from layerwise_b200.ops.conv import conv2d
+    torch.manual_seed(1)
+    x = torch.randn(n, 3, h, w, device="cuda").to(torch.bfloat16).contiguous(memory_format=torch.channels_last)
+    wt = (torch.randn(co, 3, k, k, device="cuda") / 5).to(torch.bfloat16).contiguous(memory_format=torch.channels_last)
+    b = torch.randn(co, device="cuda").to(torch.bfloat16)
+    w1, b1 = wt.clone().requires_grad_(True), b.clone().requires_grad_(True)
+    y, _ = conv2d(x, w1, b1, stride=stride, padding=pad, relu=True)
+    wr, br = wt.float().requires_grad_(True), b.float().requires_grad_(True)
+    yr = F.relu(F.conv2d(x.float(), wr, br, stride=stride, padding=pad))
+    assert _rel(y, yr) <= 2e-2
+    dy = torch.randn_like(y)
+    y.backward(dy)
+    (F.conv2d(x.float(), wr, br, stride=stride, padding=pad) * (dy.float() * (y.float() > 0))).sum().backward()
+    assert _rel(w1.grad, wr.grad) <= 3e-2
+    assert _rel(b1.grad, br.grad) <= 3e-2
+
+
+@pytest.mark.parametrize("n,hw", [(4, 64), (2, 224), (3, 96)])
+def test_convx_stem_forward_matches_7x7(n, hw):
+    """The 7x7/2 stem through the overlapping-window tensor map (IMAGENET/training/resnet.py:100-101)."""
+    from layerwise_b200.ops.input import normalize_u8, stem_forward
+    torch.manual_seed(0)
+    xu = torch.randint(0, 256, (n, 3, hw, hw), dtype=torch.uint8, device="cuda")
+    w7 = (torch.randn(64, 3, 7, 7, device="cuda") / 12).to(torch.bfloat16)
+    xs = normalize_u8(xu, s2d=True)
+    y = stem_forward(xs, w7, want_stats=False)
+    xn = normalize_u8(xu, s2d=False).float()
+    yr = F.conv2d(xn.to(torch.bfloat16).float(), w7.float(), stride=2, padding=3)
+    assert y.shape == yr.shape
+    assert _rel(y, yr) <= 2e-2
+
+
+def test_conv_emitted_statistics_feed_the_batch_norm():
+    """conv -> bn with the statistics summed in the convolution epilogue equals conv -> bn with the statistics pass."""
+    from layerwise_b200.ops import nn as lnn
+    torch.manual_seed(0)
+    conv = lnn.Conv2d(128, 256, 3, padding=1, bias=False).cuda().to(torch.bfloat16).to(memory_format=torch.channels_last)
+    bn = lnn.BatchNorm2d(256).cuda()
+    x = torch.randn(6, 128, 14, 14, device="cuda").to(torch.bfloat16).contiguous(memory_format=torch.channels_last)
+    outs = []
+    for fused in (True, False):
+        conv.emit_bn_stats = fused
+        bn.reset_running_stats()
+        xi = x.clone().requires_grad_(True)
+        h = conv(xi)
+        assert (getattr(h, "bn_stats", None) is not None) == fused
+        y = bn(h, relu=True)
+        y.float().square().sum().backward()
+        outs.append((y.float(), xi.grad.float(), bn.running_mean.clone(), bn.running_var.clone(), int(bn.num_batches_tracked)))
+        conv.weight.grad = None
+        bn.weight.grad = bn.bias.grad = None
+    (ya, ga, ma, va, na), (yb, gb, mb, vb, nb) = outs
+    assert na == nb == 1
+    assert torch.allclose(ma, mb, rtol=1e-4, atol=1e-5) and torch.allclose(va, vb, rtol=1e-3, atol=1e-5)
+    assert _rel(ya, yb) <= 1e-2 and _rel(ga, gb) <= 2e-2
