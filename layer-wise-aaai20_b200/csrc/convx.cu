@@ -47,7 +47,8 @@ using namespace lwc::tc;
 
 constexpr int BM = 128;
 constexpr int BK = 64;
-constexpr int THREADS = 192;
+constexpr int THREADS = 320;          // k_fx: TMA warp, MMA warp, 8 epilogue warps
+constexpr int WX_THREADS = 192;       // k_wx: TMA warp, MMA warp, 4 epilogue warps
 constexpr int MAXT = 16;
 constexpr int SUB_BYTES = BM * 128;          // one 128-row x 64-column bf16 staging sub-tile
 constexpr int SMEM_BUDGET = 227 * 1024;
@@ -104,7 +105,7 @@ __global__ void __launch_bounds__(THREADS, 1) k_fx(const __grid_constant__ CUten
     if (threadIdx.x == 0) {
         prefetch_tensormap(&tmA); prefetch_tensormap(&tmB); prefetch_tensormap(&tmC);
         for (int s = 0; s < stages; ++s) { mbar_init(&full[s], 1); mbar_init(&empty[s], 1); }
-        for (int a = 0; a < 2; ++a) { mbar_init(&tmem_full[a], 1); mbar_init(&tmem_empty[a], 4); }
+        for (int a = 0; a < 2; ++a) { mbar_init(&tmem_full[a], 1); mbar_init(&tmem_empty[a], 8); }
         fence_barrier_init();
     }
     if (warp == 1) tmem_alloc<2 * BN>(tmem_slot);
@@ -165,14 +166,18 @@ __global__ void __launch_bounds__(THREADS, 1) k_fx(const __grid_constant__ CUten
             umma_commit(&tmem_full[as]);
         }
     } else if (warp >= 2) {
-        // ---------------- epilogue ----------------
-        const int q = warp & 3;
-        const int r = q * 32 + lane;
-        const int et = threadIdx.x - 64;               // 0..127
+        // ---------------- epilogue: 8 warps, two per TMEM lane quarter (each takes 32 of a chunk's 64 columns) --------
+        const int ew = warp - 2;                       // 0..7
+        const int q = warp & 3;                        // TMEM lane quarter this warp may read
+        const int hsel = ew >> 2;                      // which 32-column half of every 64-column chunk
+        const int r = q * 32 + lane;                   // accumulator row = pixel of the patch
+        const int et = threadIdx.x - 64;               // 0..255
         const bool leader = et == 0;
         const int r_w = r % p.Wb, r_h = (r / p.Wb) % p.Hb, r_n = r / (p.Wb * p.Hb);
+        const bool slow = p.bias != nullptr || p.relu != 0;
         float* acc = reinterpret_cast<float*>(smem + p.stat_off);
-        float* scratch = acc + 2 * p.N;                // [4 warps][2][64]
+        float* scratch = acc + 2 * p.N;                // [8 warps][2][64]
+        constexpr int NCH = BN / 64;
         uint32_t tcount = 0, sub = 0;
         for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++tcount) {
             const TileCoord t = tile_coord(p, tile);
@@ -183,61 +188,67 @@ __global__ void __launch_bounds__(THREADS, 1) k_fx(const __grid_constant__ CUten
             const bool row_live = r < p.rows_per_tile && t.w0 + r_w < p.OW && t.h0 + r_h < p.OH && t.n0 + r_n < p.ON;
             mbar_wait(&tmem_full[as], aph);
             fence_after();
-#pragma unroll 1
-            for (int h = 0; h < BN / 64; ++h) {
+            const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + as * BN + (uint32_t)(hsel * 32);
+            uint32_t vv[2][32];
+            tmem_ld32_issue(taddr, vv[0]);
+#pragma unroll
+            for (int h = 0; h < NCH; ++h) {
                 uint8_t* cst = smem + p.c_off + sub * SUB_BYTES;
+                uint32_t* v = vv[h & 1];
                 // the store that read this staging buffer `ncs` chunks ago must have finished reading it
                 if (leader) {
                     if (p.ncs >= 4) tma_wait_group_read<3>(); else if (p.ncs == 3) tma_wait_group_read<2>(); else tma_wait_group_read<1>();
                 }
-                uint32_t v0[32], v1[32];
-                const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + as * BN + (uint32_t)(h * 64);
-                tmem_ld32_issue(taddr, v0);
-                tmem_ld32_issue(taddr + 32, v1);
                 tmem_ld_wait();
-                if (h == BN / 64 - 1) {                 // whole row is in registers: the accumulator may be overwritten
+                if (h + 1 < NCH) {
+                    tmem_ld32_issue(taddr + (uint32_t)((h + 1) * 64), vv[(h + 1) & 1]);     // next chunk in flight
+                } else {                                // whole row is in registers: the accumulator may be overwritten
                     fence_before();
                     __syncwarp();
                     if (lane == 0) mbar_arrive(&tmem_empty[as]);
                 }
-                epi_bar_sync();                         // staging buffer free (leader waited above)
-                use_after_wait(v0);
-                use_after_wait(v1);
+                epi_bar_sync_n<256>();                         // staging buffer free (leader waited above)
+                use_after_wait(v);
+                if (slow) {
+#pragma unroll
+                    for (int e = 0; e < 32; ++e) {
+                        float x = __uint_as_float(v[e]);
+                        if (p.bias) x += __ldg(p.bias + co0 + h * 64 + hsel * 32 + e);
+                        if (p.relu) x = fmaxf(x, 0.0f);
+                        v[e] = __float_as_uint(x);
+                    }
+                }
+                if (!row_live) {
+#pragma unroll
+                    for (int e = 0; e < 32; ++e) v[e] = 0u;
+                }
                 uint8_t* rowp = cst + r * 128;
 #pragma unroll
-                for (int j = 0; j < 8; ++j) {           // eight 16-byte chunks (8 bf16 each)
-                    const uint32_t* v = j < 4 ? v0 : v1;
-                    const int jj = (j & 3) * 8;
+                for (int j = 0; j < 4; ++j) {           // four 16-byte chunks (8 bf16 each) of this thread's half row
                     uint32_t w[4];
 #pragma unroll
                     for (int e = 0; e < 4; ++e) {
-                        float x0 = __uint_as_float(v[jj + 2 * e]), x1 = __uint_as_float(v[jj + 2 * e + 1]);
-                        if (p.bias) {
-                            const int c = co0 + h * 64 + j * 8 + 2 * e;
-                            x0 += __ldg(p.bias + c); x1 += __ldg(p.bias + c + 1);
-                        }
-                        if (p.relu) { x0 = fmaxf(x0, 0.0f); x1 = fmaxf(x1, 0.0f); }
-                        if (!row_live) { x0 = 0.0f; x1 = 0.0f; }
-                        __nv_bfloat162 hb = __floats2bfloat162_rn(x0, x1);
+                        __nv_bfloat162 hb = __floats2bfloat162_rn(__uint_as_float(v[j * 8 + 2 * e]), __uint_as_float(v[j * 8 + 2 * e + 1]));
                         w[e] = *reinterpret_cast<uint32_t*>(&hb);
                     }
-                    *reinterpret_cast<uint4*>(rowp + ((j ^ (r & 7)) * 16)) = make_uint4(w[0], w[1], w[2], w[3]);
+                    *reinterpret_cast<uint4*>(rowp + (((hsel * 4 + j) ^ (r & 7)) * 16)) = make_uint4(w[0], w[1], w[2], w[3]);
                 }
                 fence_proxy_async_smem();
-                epi_bar_sync();
+                epi_bar_sync_n<256>();
                 if (leader) {
                     if (co0 + h * 64 < p.N) tma_store_4d(&tmC, cst, co0 + h * 64, t.w0, t.h0, t.n0);
                     tma_commit_group();                 // one group per chunk keeps the count in step with the ring
                 }
                 if (p.stats) {
-                    // column sums of the rounded 128 x 64 sub-tile: thread = (row group of 8, 16-byte chunk)
+                    // column sums of the rounded 128 x 64 sub-tile: thread = (group of 4 rows, 16-byte chunk)
                     const int c = et & 7, rg = et >> 3;
                     float s1[8], s2[8];
 #pragma unroll
                     for (int k = 0; k < 8; ++k) { s1[k] = 0.0f; s2[k] = 0.0f; }
 #pragma unroll
-                    for (int i = 0; i < 8; ++i) {
-                        const uint4 u = *reinterpret_cast<const uint4*>(cst + (rg * 8 + i) * 128 + ((c ^ i) * 16));
+                    for (int i = 0; i < 4; ++i) {
+                        const int row = rg * 4 + i;
+                        const uint4 u = *reinterpret_cast<const uint4*>(cst + row * 128 + ((c ^ (row & 7)) * 16));
                         const uint32_t uw[4] = {u.x, u.y, u.z, u.w};
 #pragma unroll
                         for (int e = 0; e < 4; ++e) {
@@ -254,15 +265,15 @@ __global__ void __launch_bounds__(THREADS, 1) k_fx(const __grid_constant__ CUten
                         s2[k] += __shfl_xor_sync(0xffffffffu, s2[k], 16);
                     }
                     if (lane < 8) {
-                        float* o = scratch + q * 128 + lane * 8;
+                        float* o = scratch + ew * 128 + lane * 8;
 #pragma unroll
                         for (int k = 0; k < 8; ++k) { o[k] = s1[k]; o[64 + k] = s2[k]; }
                     }
-                    epi_bar_sync();
-                    {
-                        const int which = et >> 6, ch = et & 63;           // fixed order over the four warps
-                        const float tot = (scratch[0 * 128 + which * 64 + ch] + scratch[1 * 128 + which * 64 + ch]) +
-                                          (scratch[2 * 128 + which * 64 + ch] + scratch[3 * 128 + which * 64 + ch]);
+                    epi_bar_sync_n<256>();
+                    if (et < 128) {
+                        const int which = et >> 6, ch = et & 63;           // fixed order over the eight warps
+                        const float* sp = scratch + which * 64 + ch;
+                        const float tot = ((sp[0] + sp[128]) + (sp[256] + sp[384])) + ((sp[512] + sp[640]) + (sp[768] + sp[896]));
                         const int cg = co0 + h * 64 + ch;
                         if (cg < p.N) acc[which * p.N + cg] += tot;
                     }
@@ -272,9 +283,9 @@ __global__ void __launch_bounds__(THREADS, 1) k_fx(const __grid_constant__ CUten
         }
         if (leader) tma_wait_group<0>();
         if (p.stats) {
-            epi_bar_sync();
+            epi_bar_sync_n<256>();
             float* o = p.stats + (size_t)blockIdx.x * 2 * p.N;
-            for (int i = et; i < 2 * p.N; i += 128) o[i] = acc[i];
+            for (int i = et; i < 2 * p.N; i += 256) o[i] = acc[i];
         }
     }
     fence_before();
@@ -309,7 +320,7 @@ struct WxParams {
 };
 
 template <int BN>
-__global__ void __launch_bounds__(THREADS, 1) k_wx(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ CUtensorMap tmDY,
+__global__ void __launch_bounds__(WX_THREADS, 1) k_wx(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ CUtensorMap tmDY,
                                                    const WxParams p) {
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
@@ -428,25 +439,34 @@ __global__ void __launch_bounds__(THREADS, 1) k_wx(const __grid_constant__ CUten
 }
 
 // Sum the split partials in a fixed order and transpose [box = (tap, chunk)][64 ci][Cout] -> [Cout][tap][Cin].
-// grid = (nboxes, Cout / 64), block = (64, 4): a 64 x 64 tile per CTA through shared memory.
+// grid = (nboxes * 8, Cout / 64), block = 256 = 64 output channels x 4 split lanes: a CTA owns 8 input channels x 64
+// output channels of one box; lane z sums splits z, z + 4, ... (8 independent loads in flight per step), the four
+// lane sums are combined in a fixed order.
 template <typename OutT>
 __global__ void __launch_bounds__(256) k_wx_reduce(const float* __restrict__ ws, OutT* __restrict__ out, int ksplit, int nboxes,
                                                    int cchunks, int Cout, int Cin, int ntaps, float scale) {
-    __shared__ float tile[64][65];
-    const int bx = blockIdx.x, co0 = blockIdx.y * 64;
+    __shared__ float part[4][8][65];
+    const int bx = blockIdx.x >> 3, i0 = (blockIdx.x & 7) * 8, co0 = blockIdx.y * 64;
     const int tap = bx / cchunks, cc = bx - tap * cchunks;
-    const int tx = threadIdx.x, ty = threadIdx.y;
-    for (int i = ty; i < 64; i += 4) {                     // i = input channel within the box, tx = output channel
-        float s = 0.0f;
-        const float* src = ws + ((size_t)bx * 64 + i) * Cout + co0 + tx;
-        for (int zz = 0; zz < ksplit; ++zz) s += src[(size_t)zz * nboxes * 64 * Cout];
-        tile[i][tx] = s;
+    const int tx = threadIdx.x & 63, zl = threadIdx.x >> 6;
+    float s[8];
+#pragma unroll
+    for (int i = 0; i < 8; ++i) s[i] = 0.0f;
+    const size_t zstride = (size_t)nboxes * 64 * Cout;
+    const float* src = ws + ((size_t)bx * 64 + i0) * Cout + co0 + tx;
+    for (int zz = zl; zz < ksplit; zz += 4) {
+        const float* q = src + (size_t)zz * zstride;
+#pragma unroll
+        for (int i = 0; i < 8; ++i) s[i] += q[(size_t)i * Cout];
     }
+#pragma unroll
+    for (int i = 0; i < 8; ++i) part[zl][i][tx] = s[i];
     __syncthreads();
-    for (int o = ty; o < 64; o += 4) {                     // o = output channel, tx = input channel
-        const int ci = cc * 64 + tx;
+    for (int idx = threadIdx.x; idx < 512; idx += 256) {
+        const int i = idx & 7, o = idx >> 3;
+        const int ci = cc * 64 + i0 + i;
         if (ci < Cin) {
-            const float v = tile[tx][o] * scale;
+            const float v = ((part[0][i][o] + part[1][i][o]) + (part[2][i][o] + part[3][i][o])) * scale;
             OutT* dst = out + ((size_t)(co0 + o) * ntaps + tap) * Cin + ci;
             if constexpr (sizeof(OutT) == 4) *dst = v; else *dst = __float2bfloat16_rn(v);
         }
@@ -612,7 +632,7 @@ int run_fx(const FxGeom& g, cudaStream_t st, int* grid_out) {
     for (int t = 0; t < g.ntaps; ++t) { p.dw[t] = g.dw[t]; p.dh[t] = g.dh[t]; p.a_c0[t] = g.a_c0[t]; p.b_k0[t] = g.b_k0[t]; }
     // shared-memory plan
     const int stage_bytes = BM * BK * 2 + BN * BK * 2;
-    const int stat_bytes = g.stats ? (2 * g.Cout + 512) * 4 : 0;
+    const int stat_bytes = g.stats ? (2 * g.Cout + 1024) * 4 : 0;
     int ncs = 4;
     const int fixed = 1024 + 256 + stat_bytes;
     int stages = (SMEM_BUDGET - fixed - ncs * SUB_BYTES) / stage_bytes;
@@ -858,7 +878,7 @@ int launch_wx(const CUtensorMap& tx, const CUtensorMap& td, const WxPlan& P, cud
         LWC_CUDA_CHECK(cudaFuncSetAttribute(k_wx<BN>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BUDGET));
         attr = true;
     }
-    k_wx<BN><<<dim3(P.ngroups, P.p.ksplit), THREADS, P.smem, st>>>(tx, td, P.p);
+    k_wx<BN><<<dim3(P.ngroups, P.p.ksplit), WX_THREADS, P.smem, st>>>(tx, td, P.p);
     return 0;
 }
 
@@ -899,7 +919,7 @@ extern "C" int lwc_convx_wgrad(const void* x, const void* dy, void* dw, float* w
     else if (P.BN == 128) rc = launch_wx<128>(tx, td, P, st);
     else rc = launch_wx<64>(tx, td, P, st);
     if (rc) return rc;
-    const dim3 rg(P.p.nboxes, Cout / 64), rb(64, 4);
+    const dim3 rg(P.p.nboxes * 8, Cout / 64), rb(256);
     if (out_dtype == LWC_F32)
         k_wx_reduce<float><<<rg, rb, 0, st>>>(workspace, (float*)dw, P.p.ksplit, P.p.nboxes, P.p.cchunks, Cout, Cin_out, P.p.ntaps, scale);
     else

@@ -144,8 +144,9 @@ __device__ __forceinline__ void use_after_wait(uint32_t r[32]) {
                    "+r"(r[24]), "+r"(r[25]), "+r"(r[26]), "+r"(r[27]), "+r"(r[28]), "+r"(r[29]), "+r"(r[30]), "+r"(r[31])
                  :: "memory");
 }
-// Named barrier over the four epilogue warps (128 threads).
-__device__ __forceinline__ void epi_bar_sync() { asm volatile("bar.sync 1, 128;" ::: "memory"); }
+// Named barrier over the epilogue warps (NT threads).
+template <int NT = 128>
+__device__ __forceinline__ void epi_bar_sync_n() { asm volatile("bar.sync 1, %0;" ::"n"(NT) : "memory"); }
 
 }  // namespace tc
 }  // namespace lwc
