@@ -109,10 +109,6 @@ __global__ void __launch_bounds__(THREADS, 1) k_fx(const __grid_constant__ CUten
         fence_barrier_init();
     }
     if (warp == 1) tmem_alloc<2 * BN>(tmem_slot);
-    if (p.stats) {                                          // per-CTA statistics accumulators start at zero
-        float* acc0 = reinterpret_cast<float*>(smem + p.stat_off);
-        for (int i = threadIdx.x; i < 2 * p.N; i += THREADS) acc0[i] = 0.0f;
-    }
     fence_before();
     __syncthreads();
     fence_after();
@@ -175,9 +171,12 @@ __global__ void __launch_bounds__(THREADS, 1) k_fx(const __grid_constant__ CUten
         const bool leader = et == 0;
         const int r_w = r % p.Wb, r_h = (r / p.Wb) % p.Hb, r_n = r / (p.Wb * p.Hb);
         const bool slow = p.bias != nullptr || p.relu != 0;
-        float* acc = reinterpret_cast<float*>(smem + p.stat_off);
-        float* scratch = acc + 2 * p.N;                // [8 warps][2][64]
         constexpr int NCH = BN / 64;
+        float sacc[NCH][16];                           // [chunk][sum x 8 channels | sum of squares x 8 channels]
+#pragma unroll
+        for (int h = 0; h < NCH; ++h)
+#pragma unroll
+            for (int k = 0; k < 16; ++k) sacc[h][k] = 0.0f;
         uint32_t tcount = 0, sub = 0;
         for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++tcount) {
             const TileCoord t = tile_coord(p, tile);
@@ -240,11 +239,10 @@ __global__ void __launch_bounds__(THREADS, 1) k_fx(const __grid_constant__ CUten
                     tma_commit_group();                 // one group per chunk keeps the count in step with the ring
                 }
                 if (p.stats) {
-                    // column sums of the rounded 128 x 64 sub-tile: thread = (group of 4 rows, 16-byte chunk)
+                    // column sums of the rounded 128 x 64 sub-tile, kept in registers for the whole kernel: thread =
+                    // (group of 4 rows, 16-byte chunk of 8 channels); the host sizes the grid so that a CTA always
+                    // works on the same BN output channels, i.e. chunk h means the same channels in every tile
                     const int c = et & 7, rg = et >> 3;
-                    float s1[8], s2[8];
-#pragma unroll
-                    for (int k = 0; k < 8; ++k) { s1[k] = 0.0f; s2[k] = 0.0f; }
 #pragma unroll
                     for (int i = 0; i < 4; ++i) {
                         const int row = rg * 4 + i;
@@ -253,29 +251,9 @@ __global__ void __launch_bounds__(THREADS, 1) k_fx(const __grid_constant__ CUten
 #pragma unroll
                         for (int e = 0; e < 4; ++e) {
                             const float lo = __uint_as_float(uw[e] << 16), hi = __uint_as_float(uw[e] & 0xffff0000u);
-                            s1[2 * e] += lo; s2[2 * e] = fmaf(lo, lo, s2[2 * e]);
-                            s1[2 * e + 1] += hi; s2[2 * e + 1] = fmaf(hi, hi, s2[2 * e + 1]);
+                            sacc[h][2 * e] += lo; sacc[h][8 + 2 * e] = fmaf(lo, lo, sacc[h][8 + 2 * e]);
+                            sacc[h][2 * e + 1] += hi; sacc[h][8 + 2 * e + 1] = fmaf(hi, hi, sacc[h][8 + 2 * e + 1]);
                         }
-                    }
-#pragma unroll
-                    for (int k = 0; k < 8; ++k) {      // the four row groups of a warp: lanes l, l^8, l^16, l^24
-                        s1[k] += __shfl_xor_sync(0xffffffffu, s1[k], 8);
-                        s2[k] += __shfl_xor_sync(0xffffffffu, s2[k], 8);
-                        s1[k] += __shfl_xor_sync(0xffffffffu, s1[k], 16);
-                        s2[k] += __shfl_xor_sync(0xffffffffu, s2[k], 16);
-                    }
-                    if (lane < 8) {
-                        float* o = scratch + ew * 128 + lane * 8;
-#pragma unroll
-                        for (int k = 0; k < 8; ++k) { o[k] = s1[k]; o[64 + k] = s2[k]; }
-                    }
-                    epi_bar_sync_n<256>();
-                    if (et < 128) {
-                        const int which = et >> 6, ch = et & 63;           // fixed order over the eight warps
-                        const float* sp = scratch + which * 64 + ch;
-                        const float tot = ((sp[0] + sp[128]) + (sp[256] + sp[384])) + ((sp[512] + sp[640]) + (sp[768] + sp[896]));
-                        const int cg = co0 + h * 64 + ch;
-                        if (cg < p.N) acc[which * p.N + cg] += tot;
                     }
                 }
                 if (++sub == (uint32_t)p.ncs) sub = 0;
@@ -283,9 +261,39 @@ __global__ void __launch_bounds__(THREADS, 1) k_fx(const __grid_constant__ CUten
         }
         if (leader) tma_wait_group<0>();
         if (p.stats) {
+            // once per kernel: row groups of a warp by shuffles, the eight warps through shared memory (the staging
+            // ring is free now) in a fixed order, then one partial row [2][N] per CTA (zero outside its BN channels)
+            epi_bar_sync_n<256>();
+            float* scratch = reinterpret_cast<float*>(smem + p.c_off);     // [8 warps][NCH][2][64]
+#pragma unroll
+            for (int h = 0; h < NCH; ++h) {
+#pragma unroll
+                for (int k = 0; k < 16; ++k) {
+                    float v = sacc[h][k];
+                    v += __shfl_xor_sync(0xffffffffu, v, 8);
+                    v += __shfl_xor_sync(0xffffffffu, v, 16);
+                    sacc[h][k] = v;
+                }
+                if (lane < 8) {
+                    float* o = scratch + (ew * NCH + h) * 128 + lane * 8;
+#pragma unroll
+                    for (int k = 0; k < 8; ++k) { o[k] = sacc[h][k]; o[64 + k] = sacc[h][8 + k]; }
+                }
+            }
             epi_bar_sync_n<256>();
             float* o = p.stats + (size_t)blockIdx.x * 2 * p.N;
-            for (int i = et; i < 2 * p.N; i += 256) o[i] = acc[i];
+            const int nt_mine = ((int)blockIdx.x < num_tiles) ? (int)blockIdx.x % p.tiles_n : 0;
+            for (int i = et; i < 2 * p.N; i += 256) {
+                const int which = i / p.N, cg = i - which * p.N;
+                const int local = cg - nt_mine * BN;
+                float tot = 0.0f;
+                if (local >= 0 && local < BN) {
+                    const float* sp = scratch + (local >> 6) * 128 + which * 64 + (local & 63);
+                    constexpr int WS = NCH * 128;
+                    tot = ((sp[0] + sp[WS]) + (sp[2 * WS] + sp[3 * WS])) + ((sp[4 * WS] + sp[5 * WS]) + (sp[6 * WS] + sp[7 * WS]));
+                }
+                o[i] = tot;
+            }
         }
     }
     fence_before();
@@ -407,10 +415,10 @@ __global__ void __launch_bounds__(WX_THREADS, 1) k_wx(const __grid_constant__ CU
         const int r = q * 32 + lane;                       // accumulator row = (box parity, channel)
         mbar_wait(tmem_full, 0);
         fence_after();
+        // Each warp transposes its 32 accumulator rows through shared memory (the operand ring is idle now) so that a
+        // store instruction writes 128 contiguous bytes of one partial row instead of 32 scattered 16-byte pieces.
+        float* tb = reinterpret_cast<float*>(smem) + (warp - 2) * (32 * 33);
         for (int j = 0; j < nslices; ++j) {
-            const int bx = box0 + 2 * j + (r >> 6);
-            const bool live = bx < p.nboxes;
-            float* dst = p.ws + (((size_t)z * p.nboxes + (live ? bx : 0)) * 64 + (r & 63)) * p.Cout + co0;
 #pragma unroll 1
             for (int c = 0; c < BN; c += 32) {
                 uint32_t v[32];
@@ -421,11 +429,18 @@ __global__ void __launch_bounds__(WX_THREADS, 1) k_wx(const __grid_constant__ CU
 #pragma unroll
                     for (int e = 0; e < 32; ++e) v[e] = 0u;
                 }
-                if (live && co0 + c < p.Cout) {
+                __syncwarp();
 #pragma unroll
-                    for (int e = 0; e < 32; e += 4)
-                        *reinterpret_cast<float4*>(dst + c + e) = make_float4(__uint_as_float(v[e]), __uint_as_float(v[e + 1]),
-                                                                              __uint_as_float(v[e + 2]), __uint_as_float(v[e + 3]));
+                for (int e = 0; e < 32; ++e) tb[lane * 33 + e] = __uint_as_float(v[e]);
+                __syncwarp();
+                if (co0 + c < p.Cout) {
+#pragma unroll 4
+                    for (int rr = 0; rr < 32; ++rr) {
+                        const int row = q * 32 + rr;
+                        const int bx = box0 + 2 * j + (row >> 6);
+                        if (bx < p.nboxes)
+                            p.ws[(((size_t)z * p.nboxes + bx) * 64 + (row & 63)) * p.Cout + co0 + c + lane] = tb[rr * 33 + lane];
+                    }
                 }
             }
         }
@@ -632,7 +647,7 @@ int run_fx(const FxGeom& g, cudaStream_t st, int* grid_out) {
     for (int t = 0; t < g.ntaps; ++t) { p.dw[t] = g.dw[t]; p.dh[t] = g.dh[t]; p.a_c0[t] = g.a_c0[t]; p.b_k0[t] = g.b_k0[t]; }
     // shared-memory plan
     const int stage_bytes = BM * BK * 2 + BN * BK * 2;
-    const int stat_bytes = g.stats ? (2 * g.Cout + 1024) * 4 : 0;
+    const int stat_bytes = 0;       // statistics live in registers; their final reduction reuses the staging ring
     int ncs = 4;
     const int fixed = 1024 + 256 + stat_bytes;
     int stages = (SMEM_BUDGET - fixed - ncs * SUB_BYTES) / stage_bytes;
@@ -676,6 +691,9 @@ int run_fx(const FxGeom& g, cudaStream_t st, int* grid_out) {
     }
     int grid = p.tiles_m * p.tiles_n;
     if (grid > sm_count()) grid = sm_count();
+    // with statistics a CTA must stay on one column of output-channel tiles (tile = mt * tiles_n + nt, stride = grid)
+    if (g.stats && grid % p.tiles_n) grid = grid > p.tiles_n ? grid / p.tiles_n * p.tiles_n : p.tiles_n;
+    if (g.stats && p.tiles_n > sm_count()) return LWC_ETOOBIG;
     if (grid_out) *grid_out = grid;
     if (BN == 256) rc = g.b_mn ? launch_fx<256, true>(ta, tb, tc_, p, smem, grid, st) : launch_fx<256, false>(ta, tb, tc_, p, smem, grid, st);
     else if (BN == 128) rc = g.b_mn ? launch_fx<128, true>(ta, tb, tc_, p, smem, grid, st) : launch_fx<128, false>(ta, tb, tc_, p, smem, grid, st);
@@ -833,10 +851,13 @@ int plan_wx(int N, int H, int W, int Cx, int Cout, int k, int stride, int pad, i
     WxPlan& P = *out;
     memset(&P, 0, sizeof(P));
     WxParams& p = P.p;
-    const int BN = pick_bn(Cout, bn_hint);
+    // hint = 1000 * (cap on accumulator slices per CTA, 0 = as many as tensor memory holds) + tile width
+    const int nacc_cap = bn_hint / 1000;
+    const int BN = pick_bn(Cout, bn_hint % 1000);
     p.Cout = Cout; p.cchunks = (Cx + 63) / 64; p.Cin_pad = p.cchunks * 64; p.ntaps = k * k; p.nboxes = p.ntaps * p.cchunks;
     const int nslices = (p.nboxes + 1) / 2;
     p.nacc = 512 / BN;
+    if (nacc_cap > 0 && p.nacc > nacc_cap) p.nacc = nacc_cap;
     if (p.nacc > nslices) p.nacc = nslices;
     p.groups_per_co = (nslices + p.nacc - 1) / p.nacc;
     p.nacc = (nslices + p.groups_per_co - 1) / p.groups_per_co;          // balance the groups

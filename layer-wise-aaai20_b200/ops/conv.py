@@ -48,12 +48,12 @@ def _candidates(cout: int):
     return [b for b in (64, 128, 256) if cout % b == 0] or [64]
 
 
-def _tuned(key: tuple, cout: int, run) -> int:
+def _tuned(key: tuple, cout: int, run, cands=None) -> int:
     """``run(bn_hint)`` launches the kernel; returns the fastest hint for ``key`` (cached)."""
     hint = _TUNE.get(key)
     if hint is not None:
         return hint
-    cands = _candidates(cout)
+    cands = cands or _candidates(cout)
     if not _TUNE_ON["on"] or len(cands) == 1 or torch.cuda.is_current_stream_capturing():
         return 0
     best, best_t = 0, float("inf")
@@ -223,7 +223,9 @@ def conv_wgrad(x: torch.Tensor, dy: torch.Tensor, weight_shape, stride: int = 1,
                                       stride, pad, abi.dtype_code(out_dtype), float(scale), hint, _stream()), "lwc_convx_wgrad")
 
     if bn_hint is None:
-        bn_hint = _tuned(("w", n, h, w, cx, co, k, stride, pad), co, run)
+        # weight gradient: tile width x accumulator slices per CTA (hint = 1000 * slices + width, see csrc/convx.cu)
+        cands = [cap * 1000 + b for b in _candidates(co) for cap in (0, 1, 2)]
+        bn_hint = _tuned(("w", n, h, w, cx, co, k, stride, pad), co, run, cands)
     run(bn_hint)
     _native.counters.add(2)
     return dw.permute(0, 3, 1, 2)                     # logical [Cout,Cin,k,k], channels-last memory

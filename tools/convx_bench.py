@@ -88,6 +88,10 @@ def main():
                     gw = cv.conv_wgrad(x, dy, w.shape, s, pad, bn_hint=bn)
                     r["wgrad_err"] = rel(gw, gw_ref)
                     r["wgrad"] = timeit(lambda: cv.conv_wgrad(x, dy, w.shape, s, pad, bn_hint=bn), flush)
+                    for cap in (1, 2):
+                        hint = cap * 1000 + bn
+                        r[f"wgrad_cap{cap}"] = timeit(lambda: cv.conv_wgrad(x, dy, w.shape, s, pad, bn_hint=hint), flush)
+                        r["wgrad"] = min(r["wgrad"], r[f"wgrad_cap{cap}"])
                 if ci % bn == 0:
                     gx = cv.conv_dgrad(dy, w, (hw, hw), s, pad, bn_hint=bn)
                     r["dgrad_err"] = rel(gx, gx_ref)
