@@ -363,28 +363,48 @@ __global__ void __launch_bounds__(WX_THREADS, 1) k_wx(const __grid_constant__ CU
     fence_after();
     const uint32_t tmem_base = *tmem_slot;
 
-    if (warp == 0 && lane == 0) {
-        // ---------------- TMA producer ----------------
+    if (warp == 0) {
+        // ---------------- TMA producer: one lane per box, so the boxes of a stage are issued side by side -------------
+        // (a single thread walking the boxes -- two integer divisions and a 4-D TMA issue each -- was the bottleneck:
+        //  ncu showed the MMA thread waiting on `full` with the tensor pipe 25 % busy)
         int nlive = p.nboxes - box0;                       // boxes of this group that exist
         if (nlive > 2 * nslices) nlive = 2 * nslices;
+        if (nlive < 0) nlive = 0;
+        constexpr int NDY = BN / 64;
+        const bool is_dy = lane < NDY;
+        const bool act = lane < NDY + nlive;
+        int my_c = 0, my_dw = 0, my_dh = 0, my_sw = 1, my_sh = 1;
+        uint32_t my_off = 0;
+        if (is_dy) {
+            my_c = co0 + lane * 64;
+            my_off = (uint32_t)(lane * box_bytes);
+        } else if (act) {
+            const int bx = box0 + lane - NDY;
+            const int tap = bx / p.cchunks, cc = bx - tap * p.cchunks;
+            my_c = cc * 64; my_dw = p.dw[tap]; my_dh = p.dh[tap]; my_sw = p.sw; my_sh = p.sh;
+            my_off = (uint32_t)(b_bytes + (lane - NDY) * box_bytes);
+        }
+        const CUtensorMap* my_map = is_dy ? &tmDY : &tmX;
+        // patch index z, z + ksplit, ... in mixed radix (tiles_w, tiles_h, images): no division inside the loop
+        int tw = z % p.tiles_w, th = (z / p.tiles_w) % p.tiles_h, tn = z / (p.tiles_w * p.tiles_h);
+        const int step_w = p.ksplit % p.tiles_w, step_h = (p.ksplit / p.tiles_w) % p.tiles_h, step_n = p.ksplit / (p.tiles_w * p.tiles_h);
+        const uint32_t stage_tx = (uint32_t)(b_bytes + nlive * box_bytes);
         uint32_t s = 0, ph = 0;
         for (int i = 0; i < npat; ++i) {
-            const int pt = z + i * p.ksplit;
-            const int tw = pt % p.tiles_w;
-            const int rr = pt / p.tiles_w;
-            const int th = rr % p.tiles_h;
-            const int w0 = tw * p.Wb, h0 = th * p.Hb, n0 = (rr / p.tiles_h) * p.Nb;
-            mbar_wait(&empty[s], ph ^ 1);
-            uint8_t* b = smem + s * p.stage_bytes;
-            uint8_t* a = b + b_bytes;
-            mbar_expect_tx(&full[s], (uint32_t)(b_bytes + nlive * box_bytes));
-#pragma unroll
-            for (int h = 0; h < BN / 64; ++h) tma_load_4d(b + h * box_bytes, &tmDY, &full[s], co0 + h * 64, w0, h0, n0);
-            for (int j = 0; j < nlive; ++j) {
-                const int bx = box0 + j;
-                const int tap = bx / p.cchunks, cc = bx - tap * p.cchunks;
-                tma_load_4d(a + j * box_bytes, &tmX, &full[s], cc * 64, w0 * p.sw + p.dw[tap], h0 * p.sh + p.dh[tap], n0);
+            if (lane == 0) {
+                mbar_wait(&empty[s], ph ^ 1);
+                mbar_expect_tx(&full[s], stage_tx);
             }
+            __syncwarp();
+            if (act) tma_load_4d(smem + s * p.stage_bytes + my_off, my_map, &full[s], my_c, tw * p.Wb * my_sw + my_dw,
+                                 th * p.Hb * my_sh + my_dh, tn * p.Nb);
+            tw += step_w;
+            int carry = 0;
+            if (tw >= p.tiles_w) { tw -= p.tiles_w; carry = 1; }
+            th += step_h + carry;
+            carry = 0;
+            if (th >= p.tiles_h) { th -= p.tiles_h; carry = 1; }
+            tn += step_n + carry;
             if (++s == (uint32_t)p.stages) { s = 0; ph ^= 1; }
         }
     } else if (warp == 1 && lane == 0) {
