@@ -257,14 +257,14 @@ int lwc_stem_wgrad(const void* dy, const void* xs, void* out, float* workspace, 
  *             [lwc_convx_max_partials()][2][Cout] and *nparts_out how many of them are valid; bn_hint = 0 (auto),
  *             64, 128 or 256 output channels per tile.
  *   dgrad1x1: dX = dY * W with the forward weight as stored (no transposed copy).
- *   dgrad   : general k / stride / pad; wt_t [Cin][k*k][Cout] (channel-transposed forward weight, taps not flipped).
+ *   dgrad   : general k / stride / pad; wt = the forward weight [Cout][k*k][Cin] as stored (read MN-major per tap).
  *   stem    : the 7x7/2 stem as a 4-row-tap convolution over overlapping 128-byte windows of the space-to-depth input.
  *   wgrad   : dW [Cout][k*k][Cin_out] = scale * dY^T X, fp32 partials in `workspace` reduced in a fixed order. */
 int lwc_convx_max_partials(void);
 int lwc_convx_forward(const void* x, const void* wt, void* y, int N, int H, int W, int Cx, int Cout, int k, int stride,
                       int pad, const float* bias, int relu, float* stats, int* nparts_out, int bn_hint, void* stream);
 int lwc_convx_dgrad1x1(const void* dy, const void* w, void* dx, long long M, int Cout, int Cin, int bn_hint, void* stream);
-int lwc_convx_dgrad(const void* dy, const void* wt_t, void* dx, int N, int H, int W, int Cin, int Cout, int k, int stride,
+int lwc_convx_dgrad(const void* dy, const void* wt, void* dx, int N, int H, int W, int Cin, int Cout, int k, int stride,
                     int pad, int bn_hint, void* stream);
 int lwc_convx_stem_forward(const void* xs, const void* w4, void* y, int N, int OH, int OW, int Cout, float* stats,
                            int* nparts_out, int bn_hint, void* stream);

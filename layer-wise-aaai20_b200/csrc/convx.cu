@@ -66,7 +66,7 @@ struct FxParams {
     const float* bias;
     float* stats;                            // [gridDim.x][2][N] per-CTA sums / sums of squares, or NULL
     short dw[MAXT], dh[MAXT];
-    int a_c0[MAXT], b_k0[MAXT];
+    int a_c0[MAXT], b_k0[MAXT], b_n0[MAXT];   // b_n0: column offset of the tap in an MN-major weight matrix
 };
 
 struct TileCoord { int mt, nt, w0, h0, n0; };
@@ -122,7 +122,7 @@ __global__ void __launch_bounds__(THREADS, 1) k_fx(const __grid_constant__ CUten
             const int co0 = t.nt * BN;
             const int wi = t.w0 * p.sw, hi = t.h0 * p.sh;
             for (int tap = 0; tap < p.ntaps; ++tap) {
-                const int aw = wi + p.dw[tap], ah = hi + p.dh[tap], ac = p.a_c0[tap], bk = p.b_k0[tap];
+                const int aw = wi + p.dw[tap], ah = hi + p.dh[tap], ac = p.a_c0[tap], bk = p.b_k0[tap], bn0 = p.b_n0[tap];
                 for (int ch = 0; ch < p.kchunks; ++ch) {
                     mbar_wait(&empty[s], ph ^ 1);
                     uint8_t* a = smem + s * STAGE_BYTES;
@@ -131,7 +131,7 @@ __global__ void __launch_bounds__(THREADS, 1) k_fx(const __grid_constant__ CUten
                     tma_load_4d(a, &tmA, &full[s], ac + ch * BK, aw, ah, t.n0);
                     if (B_MN) {
 #pragma unroll
-                        for (int h = 0; h < BN / 64; ++h) tma_load_2d(b + h * 8192, &tmB, &full[s], co0 + h * 64, bk + ch * BK);
+                        for (int h = 0; h < BN / 64; ++h) tma_load_2d(b + h * 8192, &tmB, &full[s], bn0 + co0 + h * 64, bk + ch * BK);
                     } else {
                         tma_load_2d(b, &tmB, &full[s], bk + ch * BK, co0);
                     }
@@ -625,12 +625,12 @@ struct FxGeom {
     int window;                                  // 1: overlapping-window map (stem): W axis pitch = `wpitch` elements,
     int wpitch;                                  //    `cpitch` is then the ROW pitch in elements
     // weights: K-major [rows = Cout][Ktot] (b_mn = 0) or MN-major [Ktot][Cout] (b_mn = 1)
-    const void* w; int Ktot; int b_mn;
+    const void* w; int Ktot; int b_mn; int b_ncols;   // b_ncols: columns of the MN-major matrix (0 = Cout)
     // output [ON][OH][OW][Cout] seen through (base, pitches): element strides in elements
     void* y; int OW, OH, ON, Cout; long long y_wpitch, y_hpitch, y_npitch;
     int stride;                                  // input traversal stride
     int ntaps, kchunks;
-    short dw[MAXT], dh[MAXT]; int a_c0[MAXT], b_k0[MAXT];
+    short dw[MAXT], dh[MAXT]; int a_c0[MAXT], b_k0[MAXT], b_n0[MAXT];
     const float* bias; int relu; float* stats; int bn_hint;
 };
 
@@ -664,7 +664,7 @@ int run_fx(const FxGeom& g, cudaStream_t st, int* grid_out) {
     p.sw = g.stride; p.sh = g.stride; p.OW = g.OW; p.OH = g.OH; p.ON = g.ON;
     p.tiles_m = pt.tiles_w * pt.tiles_h * pt.tiles_n; p.tiles_n = g.Cout / BN; p.rows_per_tile = pt.rows;
     p.relu = g.relu; p.bias = g.bias; p.stats = g.stats;
-    for (int t = 0; t < g.ntaps; ++t) { p.dw[t] = g.dw[t]; p.dh[t] = g.dh[t]; p.a_c0[t] = g.a_c0[t]; p.b_k0[t] = g.b_k0[t]; }
+    for (int t = 0; t < g.ntaps; ++t) { p.dw[t] = g.dw[t]; p.dh[t] = g.dh[t]; p.a_c0[t] = g.a_c0[t]; p.b_k0[t] = g.b_k0[t]; p.b_n0[t] = g.b_n0[t]; }
     // shared-memory plan
     const int stage_bytes = BM * BK * 2 + BN * BK * 2;
     const int stat_bytes = 0;       // statistics live in registers; their final reduction reuses the staging ring
@@ -693,7 +693,8 @@ int run_fx(const FxGeom& g, cudaStream_t st, int* grid_out) {
     }
     if (rc) return rc;
     if (g.b_mn) {
-        cuuint64_t bd[2] = {(cuuint64_t)g.Cout, (cuuint64_t)g.Ktot}, bs[1] = {(cuuint64_t)g.Cout * 2};
+        const cuuint64_t ncols = g.b_ncols ? g.b_ncols : g.Cout;
+        cuuint64_t bd[2] = {ncols, (cuuint64_t)g.Ktot}, bs[1] = {ncols * 2};
         cuuint32_t bb[2] = {64, BK};
         rc = encode(&tb, g.w, 2, bd, bs, bb, nullptr);
     } else {
@@ -778,14 +779,15 @@ extern "C" int lwc_convx_dgrad1x1(const void* dy, const void* w, void* dx, long 
     return run_fx(g, (cudaStream_t)stream, nullptr);
 }
 
-// Data gradient of a k x k / stride s / pad convolution:  dX[h][w] = sum_{(a,b)} Wt[a][b] dY[(h + pad - a) / s][(w + pad - b) / s]
+// Data gradient of a k x k / stride s / pad convolution:  dX[h][w] = sum_{(a,b)} W[a][b]^T dY[(h + pad - a) / s][(w + pad - b) / s]
 // over the taps whose divisions are exact.  One launch per output parity class (s * s of them); classes without a tap
-// are zero (dX is cleared up front when there is one, e.g. 1x1 / stride 2).
-//   dy : [N][OH][OW][Cout];  wt_t : [Cin][k*k][Cout] bf16 (the forward weight with channels transposed, taps NOT flipped)
+// are zero (dX is cleared up front when there is one, e.g. 1x1 / stride 2).  The forward weight is read as stored: for a
+// tap it is a [Cout][Cin] matrix with Cin contiguous, i.e. the MN-major B operand of this GEMM -- no transposed copy.
+//   dy : [N][OH][OW][Cout];  wt : [Cout][k*k][Cin] bf16 (the channels-last forward weight)
 //   dx : [N][H][W][Cin];  Cin, Cout multiples of 64
-extern "C" int lwc_convx_dgrad(const void* dy, const void* wt_t, void* dx, int N, int H, int W, int Cin, int Cout, int k, int stride,
+extern "C" int lwc_convx_dgrad(const void* dy, const void* wt, void* dx, int N, int H, int W, int Cin, int Cout, int k, int stride,
                                int pad, int bn_hint, void* stream) {
-    if (!dy || !wt_t || !dx || N <= 0 || (Cin % 64) || (Cout % 64) || k < 1 || k * k > MAXT) return LWC_EINVAL;
+    if (!dy || !wt || !dx || N <= 0 || (Cin % 64) || (Cout % 64) || k < 1 || k * k > MAXT) return LWC_EINVAL;
     if (stride != 1 && stride != 2) return LWC_EINVAL;
     const int OH = (H + 2 * pad - k) / stride + 1, OW = (W + 2 * pad - k) / stride + 1;
     cudaStream_t st = (cudaStream_t)stream;
@@ -809,14 +811,15 @@ extern "C" int lwc_convx_dgrad(const void* dy, const void* wt_t, void* dx, int N
                     const int nh = ph + pad - a, nw = pw + pad - b;
                     // C++ '%' and '/' truncate toward zero: exactness and the quotient are still right for negative nh
                     if (nh % stride || nw % stride) continue;
-                    g.dh[n] = (short)(nh / stride); g.dw[n] = (short)(nw / stride); g.a_c0[n] = 0; g.b_k0[n] = (a * k + b) * Cout;
+                    g.dh[n] = (short)(nh / stride); g.dw[n] = (short)(nw / stride); g.a_c0[n] = 0; g.b_k0[n] = 0;
+                    g.b_n0[n] = (a * k + b) * Cin;
                     ++n;
                 }
             if (!n) continue;
             const int CH = (H - ph + stride - 1) / stride, CW = (W - pw + stride - 1) / stride;   // pixels of this class
             if (CH <= 0 || CW <= 0) continue;
             g.x = dy; g.C = Cout; g.cpitch = Cout; g.W = OW; g.H = OH; g.N = N;
-            g.w = wt_t; g.Ktot = k * k * Cout; g.b_mn = 0;
+            g.w = wt; g.Ktot = Cout; g.b_mn = 1; g.b_ncols = k * k * Cin;
             g.y = (char*)dx + ((size_t)ph * W + pw) * Cin * 2; g.OW = CW; g.OH = CH; g.ON = N; g.Cout = Cin;
             g.y_wpitch = (long long)stride * Cin; g.y_hpitch = (long long)stride * W * Cin; g.y_npitch = (long long)H * W * Cin;
             g.stride = 1; g.ntaps = n; g.kchunks = Cout / 64; g.bn_hint = bn_hint;

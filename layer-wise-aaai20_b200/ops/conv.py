@@ -178,10 +178,10 @@ def conv_dgrad(dy: torch.Tensor, weight: torch.Tensor, in_hw: Tuple[int, int], s
                       "lwc_convx_dgrad1x1")
         nl = 1
     else:
-        wt_t = weight.detach().permute(1, 2, 3, 0).contiguous()      # [Cin][k][k][Cout]
+        wt = weight.detach().permute(0, 2, 3, 1).contiguous()        # [Cout][k][k][Cin]: a view of a channels-last weight
 
         def run(hint):
-            abi.check(lib.lwc_convx_dgrad(dy.data_ptr(), wt_t.data_ptr(), dx.data_ptr(), n, h, w, ci, co, k, stride, pad, hint,
+            abi.check(lib.lwc_convx_dgrad(dy.data_ptr(), wt.data_ptr(), dx.data_ptr(), n, h, w, ci, co, k, stride, pad, hint,
                                           _stream()), "lwc_convx_dgrad")
         nl = stride * stride
     if bn_hint is None:

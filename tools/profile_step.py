@@ -45,8 +45,13 @@ def main():
     tot = sum(v[1] for v in agg.values())
     rows = sorted(agg.items(), key=lambda kv: -kv[1][1])
     print(f"total device time per step: {tot / args.steps / 1e3:.3f} ms over {sum(v[0] for v in agg.values()) / args.steps:.0f} kernels")
-    cats = collections.OrderedDict([("bn (ours)", "lwc::bn"), ("exchange (ours)", "lwc::k_"), ("sgd (ours)", "lwc::k_sgd"),
+    cats = collections.OrderedDict([("bn (ours)", ("lwc::bn", "k_stats_finalize")),
+                                    ("conv fwd/dgrad (ours, tcgen05)", ("lwc::convx::k_fx", "lwc::conv::k_conv")),
+                                    ("conv wgrad (ours, tcgen05)", ("lwc::convx::k_wx", "lwc::stem")),
+                                    ("exchange (ours)", "lwc::k_"), ("sgd (ours)", "lwc::k_sgd"),
                                     ("pool (ours)", "lwc::pool"), ("gemm (ours)", "lwc::gemm"),
+                                    ("input/loss/misc (ours)", ("lwc::input", "lwc::loss", "lwc::k_ce", "lwc::")),
+                                    ("memset/memcpy", ("Memset", "Memcpy")),
                                     ("conv/gemm (cudnn/cublas)", ("cutlass", "nvjet", "xmma", "cudnn", "implicit_gemm", "nhwc")),
                                     ("elementwise/other (aten)", "at::native")])
     csum = collections.defaultdict(float)
