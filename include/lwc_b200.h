@@ -279,6 +279,21 @@ int lwc_convx_stats_finalize(const float* partials, int nparts, int C, long long
 int lwc_bn_apply_stats(const void* x, void* y, const void* res, const float* gamma, const float* beta, const float* mean,
                        const float* invstd, long long M, int C, int dtype, int relu, void* relu_mask, void* stream);
 
+/* Small model ops (csrc/misc.cu).  eltwise op: 0 = relu(x), 1 = alpha * x (Mul(0.125), CIFAR10/torch_backend.py:72-77),
+ * 2 = ReLU backward dy * (aux > 0) (nn.ReLU after biased layers, CIFAR10/alexnet.py:31-36, vgg16.py:24-30).
+ * Dropout (alexnet.py:30,33; vgg16.py:26,29): Philox4x32-10 keyed by (seed, offset + group), one mask bit per element.
+ * Adaptive average pooling on channels-last tensors (IMAGENET/training/resnet.py:109, CIFAR10/vgg16.py:22).
+ * Accuracy (torch_backend.py:88-90; train_imagenet_nv.py:679-689): per-sample argmax-correct bytes and/or
+ * accumulated top-1 / top-5 hit counters (float[2]) -- no host synchronisation. */
+int lwc_eltwise(const void* x, const void* aux, void* y, long long n, int op, float alpha, int dtype, void* stream);
+int lwc_dropout_forward(const void* x, void* y, void* mask, long long n, float p, unsigned long long seed,
+                        unsigned long long offset, int dtype, void* stream);
+int lwc_dropout_backward(const void* dy, const void* mask, void* dx, long long n, float p, int dtype, void* stream);
+int lwc_adaptive_avgpool(const void* in, void* out, int N, int IH, int IW, int OH, int OW, int C, int backward, int dtype,
+                         void* stream);
+int lwc_accuracy(const void* logits, const void* target_i64, void* correct, float* counters, int N, int C, int dtype,
+                 void* stream);
+
 /* Max pooling, NHWC, byte argmax forward + gather backward (CIFAR10/dawn.py:51,:70; resnet.py:104). */
 int lwc_maxpool_forward(const void* x, void* y, void* idx, int N, int H, int W, int C, int k, int stride,
                         int pad, int dtype, void* stream);

@@ -115,6 +115,11 @@ def declare(lib: C.CDLL):
     sig("lwc_convx_wgrad", ci, vp, vp, vp, vp, ci, ci, ci, ci, ci, ci, ci, ci, ci, ci, cf, ci, vp)
     sig("lwc_convx_stats_finalize", ci, vp, ci, ci, ll, cf, cf, vp, vp, vp, vp, vp, vp)
     sig("lwc_bn_apply_stats", ci, vp, vp, vp, vp, vp, vp, vp, ll, ci, ci, ci, vp, vp)
+    sig("lwc_eltwise", ci, vp, vp, vp, ll, ci, cf, ci, vp)
+    sig("lwc_dropout_forward", ci, vp, vp, vp, ll, cf, u64, u64, ci, vp)
+    sig("lwc_dropout_backward", ci, vp, vp, vp, ll, cf, ci, vp)
+    sig("lwc_adaptive_avgpool", ci, vp, vp, ci, ci, ci, ci, ci, ci, ci, ci, vp)
+    sig("lwc_accuracy", ci, vp, vp, vp, vp, ci, ci, ci, vp)
     sig("lwc_stem_wgrad_workspace_bytes", C.c_size_t, C.c_int, C.c_int)
     sig("lwc_stem_wgrad", C.c_int, vp, vp, vp, vp, C.c_int, C.c_int, C.c_int, C.c_int, C.c_float, vp)
     sig("lwc_sgd_plan_create", C.c_int, c_void_pp, C.POINTER(LwcSgdTensor), i32)

@@ -23,13 +23,16 @@ class AlexNet(nn.Module):
                (256, 256, 1, True)]
         feats = []
         for c_in, c_out, stride, pool in cfg:
-            feats += [lnn.Conv2d(c_in, c_out, kernel_size=3, stride=stride, padding=1), lnn.ReLU(True)]
+            conv, relu = lnn.Conv2d(c_in, c_out, kernel_size=3, stride=stride, padding=1), lnn.ReLU(True)
+            conv.fuse_relu = True              # bias + ReLU in the convolution epilogue (ops/conv.py)
+            relu.already_applied = True
+            feats += [conv, relu]
             if pool:
                 feats.append(lnn.MaxPool2d(kernel_size=2))
         self.features = nn.Sequential(*feats)
         self.classifier = nn.Sequential(
-            nn.Dropout(dropout), lnn.Linear(256 * 2 * 2, 4096), lnn.ReLU(True),
-            nn.Dropout(dropout), lnn.Linear(4096, 4096), lnn.ReLU(True),
+            lnn.Dropout(dropout), lnn.Linear(256 * 2 * 2, 4096), lnn.ReLU(True),
+            lnn.Dropout(dropout), lnn.Linear(4096, 4096), lnn.ReLU(True),
             lnn.Linear(4096, num_classes),
         )
         self.criterion = lnn.CrossEntropyLoss(reduction="none")

@@ -60,6 +60,11 @@ class Mul(nn.Module):
         self.weight = weight
 
     def forward(self, x):
+        if x.is_cuda:
+            from ..ops import misc as _misc
+            from ..ops.nn import get_backend
+            if get_backend() != "torch":
+                return _misc.scale(x, self.weight)
         return x * self.weight
 
 
@@ -80,6 +85,11 @@ class Concat(nn.Module):
 
 class Correct(nn.Module):
     def forward(self, classifier, target):
+        if classifier.is_cuda:
+            from ..ops import misc as _misc
+            from ..ops.nn import get_backend
+            if get_backend() != "torch":
+                return _misc.correct(classifier.detach(), target)
         return classifier.max(dim=1)[1] == target
 
 

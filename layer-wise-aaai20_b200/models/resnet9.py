@@ -36,8 +36,10 @@ def conv_bn(c_in, c_out, bn_weight_init=1.0, stride=1, fuse=True, **kw):
     relu = lnn.ReLU(True)
     bn.fuse_relu = bool(fuse)
     relu.already_applied = bool(fuse)
+    conv = lnn.Conv2d(c_in, c_out, kernel_size=3, stride=stride, padding=1, bias=False)
+    conv.emit_bn_stats = True              # the batch-norm statistics come out of the convolution epilogue
     return {
-        "conv": lnn.Conv2d(c_in, c_out, kernel_size=3, stride=stride, padding=1, bias=False),
+        "conv": conv,
         "bn": bn,
         "relu": relu,
     }

@@ -29,10 +29,16 @@ def make_layers(cfg, batch_norm: bool = False) -> nn.Sequential:
         if v == "M":
             layers.append(lnn.MaxPool2d(kernel_size=2, stride=2))
             continue
-        layers.append(lnn.Conv2d(c_in, v, kernel_size=3, padding=1))
+        conv, relu = lnn.Conv2d(c_in, v, kernel_size=3, padding=1), lnn.ReLU(True)
+        layers.append(conv)
         if batch_norm:
+            conv.emit_bn_stats = True          # (a biased conv does not emit them; kept for bias=False variants)
             layers.append(lnn.BatchNorm2d(v))
-        layers.append(lnn.ReLU(True))
+        else:
+            # bias + ReLU run in the convolution kernel's epilogue; the ReLU node stays for the module names
+            conv.fuse_relu = True
+            relu.already_applied = True
+        layers.append(relu)
         c_in = v
     return nn.Sequential(*layers)
 
@@ -42,10 +48,10 @@ class VGG(nn.Module):
                  dropout: float = 0.5):
         super().__init__()
         self.features = features
-        self.avgpool = nn.AdaptiveAvgPool2d((7, 7))
+        self.avgpool = lnn.AdaptiveAvgPool2d((7, 7))
         self.classifier = nn.Sequential(
-            lnn.Linear(512 * 7 * 7, 4096), lnn.ReLU(True), nn.Dropout(dropout),
-            lnn.Linear(4096, 4096), lnn.ReLU(True), nn.Dropout(dropout),
+            lnn.Linear(512 * 7 * 7, 4096), lnn.ReLU(True), lnn.Dropout(dropout),
+            lnn.Linear(4096, 4096), lnn.ReLU(True), lnn.Dropout(dropout),
             lnn.Linear(4096, num_classes),
         )
         self.criterion = lnn.CrossEntropyLoss(reduction="none")

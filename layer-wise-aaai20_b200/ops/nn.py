@@ -84,6 +84,27 @@ class ReLU(nn.ReLU):
     def forward(self, x):
         if getattr(self, "already_applied", False):
             return x
+        if _native_ok(x) and not (self.inplace and x.requires_grad and x.is_leaf):
+            from . import misc as _misc
+            return _misc.relu(x)
+        return super().forward(x)
+
+
+class Dropout(nn.Dropout):
+    """Inverted dropout on the Philox kernel of ``csrc/misc.cu`` (1-bit mask saved for the backward pass)."""
+
+    def forward(self, x):
+        if self.training and _native_ok(x):
+            from . import misc as _misc
+            return _misc.dropout(x, self.p, True)
+        return super().forward(x)
+
+
+class AdaptiveAvgPool2d(nn.AdaptiveAvgPool2d):
+    def forward(self, x):
+        if _native_ok(x):
+            from . import misc as _misc
+            return _misc.adaptive_avg_pool2d(x, self.output_size)
         return super().forward(x)
 
 

@@ -57,6 +57,12 @@ def default_phases(lr: float = 1.0) -> List[dict]:
 
 def correct(output: torch.Tensor, target: torch.Tensor, topk=(1,)):
     """Number of samples whose label is within the top-k predictions, one tensor per k."""
+    if output.is_cuda and set(topk) <= {1, 5} and output.shape[1] >= 5:
+        from ..ops import misc as _misc
+        from ..ops.nn import get_backend
+        if get_backend() != "torch":
+            hits = _misc.topk_hits(output.detach().contiguous(), target)       # one kernel, device counters
+            return [hits[0:1] if k == 1 else hits[1:2] for k in topk]
     maxk = max(topk)
     pred = output.topk(maxk, 1, True, True).indices.t()
     hit = pred.eq(target.view(1, -1).expand_as(pred))
@@ -318,16 +324,27 @@ class Trainer:
 
 # ---- distributed evaluation ----------------------------------------------------------------------------------
 @torch.no_grad()
-def distributed_predict(trainer: Trainer, images, target):
-    """Evaluation that tolerates ranks with an empty last batch (reference :523-542)."""
+def predict_metrics(trainer: Trainer, images, target) -> torch.Tensor:
+    """Device tensor [samples, batches, loss, top-1 hits, top-5 hits] of this rank's batch (zeros when the rank's last
+    batch is empty); nothing is read back to the host."""
     bs = images.size(0)
     m = torch.zeros(5, device=trainer.device)
     if bs:
         out, loss = trainer.predict(images, target)
         c1, c5 = correct(out.float(), target.to(trainer.device), topk=(1, 5))
-        m = torch.stack([torch.tensor(float(bs), device=trainer.device), torch.tensor(1.0, device=trainer.device),
-                         loss.float().reshape(()), c1.reshape(()), c5.reshape(())])
-    m = comm.sum_tensor(m)
+        m[0] = float(bs)
+        m[1] = 1.0
+        m[2] = loss.float().reshape(())
+        m[3] = c1.reshape(())
+        m[4] = c5.reshape(())
+    return m
+
+
+@torch.no_grad()
+def distributed_predict(trainer: Trainer, images, target):
+    """Evaluation that tolerates ranks with an empty last batch (reference :523-542); one reduction + host read per
+    call -- ``validate`` uses ``predict_metrics`` and reads back once per ``print_freq`` batches instead."""
+    m = comm.sum_tensor(predict_metrics(trainer, images, target))
     total, valid, loss_sum, c1, c5 = m.tolist()
     return c1 * 100.0 / max(total, 1), c5 * 100.0 / max(total, 1), loss_sum / max(valid, 1), total
 
@@ -336,16 +353,30 @@ def validate(trainer: Trainer, val_loader, epoch: int, log=None, tb=None, short_
     losses, top1, top5 = AverageMeter(), AverageMeter(), AverageMeter()
     t0 = time.time()
     n = len(val_loader)
+    # per-batch metrics stay on the device ([n_batches_in_window, 5]); ONE all-reduce + host read per print_freq
+    # batches instead of one per batch (reference :536-537 synchronises every eval batch)
+    window = []
+
+    def flush():
+        if not window:
+            return
+        rows = comm.sum_tensor(torch.stack(window)).tolist()
+        window.clear()
+        for total, valid, loss_sum, c1, c5 in rows:
+            losses.update(loss_sum / max(valid, 1), total)
+            top1.update(c1 * 100.0 / max(total, 1), total)
+            top5.update(c5 * 100.0 / max(total, 1), total)
+
     for i, (images, target) in enumerate(val_loader):
         if short_epoch and i > 10:
             break
-        a1, a5, loss, total = distributed_predict(trainer, images, target)
-        losses.update(loss, total)
-        top1.update(a1, total)
-        top5.update(a5, total)
+        window.append(predict_metrics(trainer, images, target))
+        if (i + 1) % print_freq == 0 or i + 1 == n:
+            flush()
         if log is not None and ((i + 1) % print_freq == 0 or i + 1 == n):
             log.verbose(f"Test:  [{epoch}][{i + 1}/{n}]\tLoss {losses.val:.4f} ({losses.avg:.4f})\t"
                         f"Acc@1 {top1.val:.3f} ({top1.avg:.3f})\tAcc@5 {top5.val:.3f} ({top5.avg:.3f})")
+    flush()
     if tb is not None:
         tb.log_eval(top1.avg, top5.avg, time.time() - t0)
         tb.log("epoch", epoch)
