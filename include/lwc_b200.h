@@ -165,6 +165,8 @@ typedef struct {
     const float* lr_dev;     /* optional: learning rate read from device memory (CUDA-graph replay) */
     int32_t param_dtype;     /* LWC_F32 (default): fp32 weights + momentum.  LWC_BF16 / LWC_F16: weights, momentum and
                               * gradients all in that type (training without fp32 masters); model copies unused */
+    const unsigned int* skip_flag;   /* optional device word: non-zero -> the step is skipped (lwc_poison_ptr: set by an
+                                      * exchange whose peer timed out, so stale gradients are never applied) */
 } LwcSgdDesc;
 /* table_dev: device array of num_tensors LwcSgdTensor; chunk table built by lwc_sgd_plan */
 typedef struct { void* param; const void* grad; void* mom; void* model; int64_t n; } LwcSgdTensor;
@@ -172,6 +174,11 @@ typedef struct LwcSgdPlan LwcSgdPlan;
 int lwc_sgd_plan_create(LwcSgdPlan** out, const LwcSgdTensor* tensors_host, int32_t num_tensors);
 int lwc_sgd_plan_destroy(LwcSgdPlan* plan);
 int lwc_sgd_step(LwcSgdPlan* plan, const LwcSgdDesc* desc, void* stream);
+/* Fail-closed word of this device: set by receivers / the dense all-reduce when a peer's flag wait ran out (no
+ * reference counterpart beyond the try/except of IMAGENET/training/train_imagenet_nv.py:704-716). */
+int lwc_poison_ptr(void** out_dev);
+int lwc_poison_read(unsigned int* out_host);
+int lwc_poison_clear(void);
 
 /* Re-point the input gradients of a plan (autograd's freshly written tensors are consumed in place; outputs
  * stay in the arena).  Stream-ordered table upload.  (no accumulate pass: cf. core.py:177 `layer.grad.data`) */

@@ -25,6 +25,7 @@ class LwcSgdDesc(C.Structure):
         ("lr", C.c_float), ("momentum", C.c_float), ("dampening", C.c_float),
         ("weight_decay", C.c_float), ("grad_scale", C.c_float),
         ("nesterov", C.c_int32), ("first_step", C.c_int32), ("lr_dev", C.c_void_p), ("param_dtype", C.c_int32),
+        ("skip_flag", C.c_void_p),
     ]
 
 
@@ -125,6 +126,9 @@ def declare(lib: C.CDLL):
     sig("lwc_sgd_plan_create", C.c_int, c_void_pp, C.POINTER(LwcSgdTensor), i32)
     sig("lwc_sgd_plan_destroy", C.c_int, vp)
     sig("lwc_sgd_step", C.c_int, vp, C.POINTER(LwcSgdDesc), vp)
+    sig("lwc_poison_ptr", C.c_int, c_void_pp)
+    sig("lwc_poison_read", C.c_int, C.POINTER(C.c_uint))
+    sig("lwc_poison_clear", C.c_int)
 
 
 def check(rc: int, what: str = ""):

@@ -629,6 +629,13 @@ __global__ void __launch_bounds__(kThreads) k_compact_send(DevPlan p) {
     publish_when_last(p);
 }
 
+// ---- fail closed: a flag wait that ran out poisons the step --------------------------------------------------
+// One word per device.  A receiver (or the dense all-reduce) whose peer did not show up within the time-out sets it;
+// the fused SGD kernels read it (LwcSgdDesc.skip_flag) and leave weights and momentum untouched, so a stalled peer
+// costs skipped updates instead of updates computed from stale slots.  The host reads / clears it at its next
+// natural synchronisation point (GradientExchanger.check_health).
+__device__ unsigned int g_lwc_poison = 0;
+
 // ---- wait for every source's flag (bounded spin) -------------------------------------------------------
 __device__ __forceinline__ void wait_sources(const DevPlan& p) {
     if (threadIdx.x < p.world && (int)threadIdx.x != p.rank) {
@@ -639,6 +646,7 @@ __device__ __forceinline__ void wait_sources(const DevPlan& p) {
         while (ld_acquire_sys(f) < want) {
             if ((++spins & 63u) == 0 && global_timer_ns() - t0 > p.timeout_ns) {
                 atomicAdd(&p.counters->timeouts, 1ULL);
+                atomicExch(&g_lwc_poison, 1u);
                 break;
             }
             __nanosleep(64);
@@ -1354,6 +1362,7 @@ __device__ __forceinline__ void ar_wait(const DevAR& p, int row) {
         while (ld_acquire_sys(f) < want) {
             if ((++spins & 63u) == 0 && global_timer_ns() - t0 > p.timeout_ns) {
                 atomicAdd(p.counters + 1, 1ULL);
+                atomicExch(&g_lwc_poison, 1u);
                 break;
             }
             __nanosleep(64);
@@ -1444,6 +1453,20 @@ extern "C" int lwc_dense_allreduce(void* const* arena_dev, void* const* flags_de
     }
     k_allreduce_wait_done<<<1, 32, 0, st>>>(p);
     return (int)cudaGetLastError();
+}
+
+// Device address of this device's poison word (hand it to LwcSgdDesc.skip_flag), its value, and a reset.
+extern "C" int lwc_poison_ptr(void** out_dev) {
+    if (!out_dev) return LWC_EINVAL;
+    return (int)cudaGetSymbolAddress(out_dev, g_lwc_poison);
+}
+extern "C" int lwc_poison_read(unsigned int* out_host) {
+    if (!out_host) return LWC_EINVAL;
+    return (int)cudaMemcpyFromSymbol(out_host, g_lwc_poison, sizeof(unsigned int));
+}
+extern "C" int lwc_poison_clear(void) {
+    const unsigned int z = 0;
+    return (int)cudaMemcpyToSymbol(g_lwc_poison, &z, sizeof(z));
 }
 
 // Re-point the *input* gradient of every tensor of a plan (outputs, residuals and geometry unchanged).

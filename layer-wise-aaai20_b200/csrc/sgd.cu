@@ -19,6 +19,7 @@ struct SgdChunk { int tensor; int len; long long start; };
 template <typename GradT, typename ModelT>
 __global__ void __launch_bounds__(kThreads) k_sgd(const LwcSgdTensor* __restrict__ tensors,
                                                   const SgdChunk* __restrict__ chunks, LwcSgdDesc d) {
+    if (d.skip_flag && *d.skip_flag) return;           // the exchange timed out on a peer: leave the weights alone
     const SgdChunk c = chunks[blockIdx.x];
     const LwcSgdTensor t = tensors[c.tensor];
     float* w = reinterpret_cast<float*>(t.param) + c.start;
@@ -55,6 +56,7 @@ __global__ void __launch_bounds__(kThreads) k_sgd(const LwcSgdTensor* __restrict
 template <typename T>
 __global__ void __launch_bounds__(kThreads) k_sgd_lowp(const LwcSgdTensor* __restrict__ tensors,
                                                        const SgdChunk* __restrict__ chunks, LwcSgdDesc d) {
+    if (d.skip_flag && *d.skip_flag) return;
     const SgdChunk c = chunks[blockIdx.x];
     const LwcSgdTensor t = tensors[c.tensor];
     T* w = reinterpret_cast<T*>(t.param) + c.start;

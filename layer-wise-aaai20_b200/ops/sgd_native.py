@@ -39,6 +39,20 @@ def _same_dense_layout(p, g) -> bool:
     return p.is_contiguous() or (p.dim() == 4 and p.is_contiguous(memory_format=torch.channels_last))
 
 
+_POISON = {}
+
+
+def _poison_ptr() -> int:
+    """Device address of the exchange's fail-closed word on the current device (see ``csrc/exchange.cu``)."""
+    dev = torch.cuda.current_device()
+    p = _POISON.get(dev)
+    if p is None:
+        out = C.c_void_p()
+        abi.check(_native.lib().lwc_poison_ptr(C.byref(out)), "lwc_poison_ptr")
+        p = _POISON[dev] = int(out.value or 0)
+    return p
+
+
 def step_group(opt, gi, group, params):
     """One fused launch per (dtype) subset of a param group."""
     lib = _native.lib()
@@ -57,6 +71,15 @@ def step_group(opt, gi, group, params):
         first = False
         bufs = None
         if mu != 0:
+            # `first_step` is one flag per launch: tensors that get their first gradient later than the others (or a
+            # partly restored optimizer state) take the plain per-tensor step once, so existing momentum is never reset
+            fresh = [p for p in ps if opt.state[p].get("momentum_buffer") is None]
+            if fresh and len(fresh) < len(ps):
+                opt._step_reference(group, fresh)
+                ps = [p for p in ps if not any(p is f for f in fresh)]
+            if fresh and len(fresh) == len(ps) and torch.cuda.is_current_stream_capturing():
+                raise RuntimeError("FusedSGD: the first optimizer step (momentum buffers are created in it) cannot be "
+                                   "captured in a CUDA graph -- run at least one eager step first")
             bufs = []
             for p in ps:
                 st = opt.state[p]
@@ -88,6 +111,7 @@ def step_group(opt, gi, group, params):
             if not torch.cuda.is_current_stream_capturing():
                 opt.sync_device_lr()
             d.lr_dev = lr_dev.data_ptr()
+        d.skip_flag = _poison_ptr()
         st = torch.cuda.current_stream().cuda_stream
         abi.check(lib.lwc_sgd_step(plan.handle, C.byref(d), C.c_void_p(st)), "lwc_sgd_step")
         _native.counters.add(1)

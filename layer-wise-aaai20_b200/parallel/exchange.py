@@ -264,12 +264,23 @@ class GradientExchanger:
         (``lwc_set_flag_timeout_ms``) and count every wait that ran out -- a stalled or dead rank then shows up as a
         growing ``timeouts`` counter instead of a hang.  Call at a point that may synchronise (the trainers do at
         their logging interval); returns the engine's counters and raises once new time-outs appeared.  Entries
-        dropped by the capacity clamp are reported in ``dropped`` (not an error: they stay in the error-feedback
-        residual)."""
+        cut by the capacity clamp are reported in ``dropped``: with error feedback they stay in the residual (not an
+        error); without it the slots hold whole tensors and the counter must stay zero -- a non-zero value then
+        raises, because those gradients would be lost."""
         stats = getattr(self.engine, "stats", None)
         if stats is None:
             return {}
         st = stats()
+        if self.engine_name in ("fused", "dense") and _native_poisoned():
+            st["poisoned"] = 1
+            if raise_on_timeout:
+                _native_poison_clear()
+                self._seen_timeouts = st.get("timeouts", 0)
+                raise RuntimeError(f"gradient exchange: a peer flag wait timed out (rank {comm.rank(self.group)} of "
+                                   f"{comm.world_size(self.group)}); optimizer steps since then were skipped on the device")
+        if st.get("dropped", 0) > 0 and not getattr(self.cfg, "error_feedback", False):
+            raise RuntimeError(f"gradient exchange: {st['dropped']} selected entries did not fit their slots and error "
+                               "feedback is off -- they were lost; enable error_feedback or raise the slot capacity")
         new = st.get("timeouts", 0) - self._seen_timeouts
         self._seen_timeouts = st.get("timeouts", 0)
         if new > 0 and raise_on_timeout:
@@ -280,6 +291,22 @@ class GradientExchanger:
     @property
     def step(self):
         return self.engine.step
+
+
+def _native_poisoned() -> bool:
+    import ctypes as _C
+    from .. import _native
+    if not _native.available():
+        return False
+    v = _C.c_uint(0)
+    _native.lib().lwc_poison_read(_C.byref(v))
+    return bool(v.value)
+
+
+def _native_poison_clear():
+    from .. import _native
+    if _native.available():
+        _native.lib().lwc_poison_clear()
 
 
 # ---- reference-compatible functional API -------------------------------------------------------

@@ -39,16 +39,23 @@ def _ptr_array(ptrs: Sequence[int]):
 
 
 def keep_and_cap(method: str, n: int, cfg) -> (int, int):
-    """Per-group keep count and payload capacity (entries)."""
+    """Per-group keep count and payload capacity (entries).
+
+    With error feedback a payload that outgrows its slot is clamped and the excess stays in the residual -- nothing
+    is lost, so the slots are sized for the expected count plus headroom.  WITHOUT error feedback (the reference's
+    menu semantics: every ``|g| >= V`` and every tie at the k-th value is sent, CIFAR10/core.py:178-193) a clamped
+    entry would simply vanish, so the slot holds the whole tensor: ties and loose thresholds can never drop a
+    gradient (the price is slot memory, n * 8 bytes per tensor and rank)."""
+    lossless = not getattr(cfg, "error_feedback", False)
     if method == cref.TOPK:
         keep = cref.topk_keep_count(n, cfg.ratio)
-        cap = min(n, int(math.ceil(keep * cfg.capacity_factor)) + 64)
+        cap = n if lossless else min(n, int(math.ceil(keep * cfg.capacity_factor)) + 64)
     elif method == cref.RANDOMK:
         keep = cref.randomk_keep_count(n, cfg.ratio)
         cap = keep
     elif method in (cref.THRESHOLDV, cref.ADAPTIVE):
         keep = 0
-        cap = min(n, max(int(math.ceil(n * cfg.dense_capacity)), 1024))
+        cap = n if lossless else min(n, max(int(math.ceil(n * cfg.dense_capacity)), 1024))
     else:
         keep, cap = 0, 0
     return max(keep, 0), max(cap, 1)

@@ -235,7 +235,30 @@ def test_missing_peer_times_out_instead_of_hanging():
         plans[0].recv(0)            # rank 1 never sent step 0
         torch.cuda.synchronize()
         assert plans[0].stats()["timeouts"] >= 1
+        # fail closed: the time-out poisoned the step, so the fused optimizer must not touch weights or momentum
+        import ctypes as C
+        from layerwise_b200.ops.sgd import FusedSGD
+        v = C.c_uint(0)
+        assert lib.lwc_poison_read(C.byref(v)) == 0 and v.value == 1
+        w = [torch.randn(5000, device="cuda", requires_grad=True), torch.randn(70, 3, device="cuda", requires_grad=True)]
+        opt = FusedSGD(w, lr=0.1, momentum=0.9, nesterov=True, weight_decay=1e-4)
+        lib.lwc_poison_clear()
+        for t in w:
+            t.grad = torch.randn_like(t)
+        opt.step()                   # a normal first step (creates the momentum buffers)
+        before = [t.detach().clone() for t in w]
+        mom = [opt.state[t]["momentum_buffer"].clone() for t in w]
+        plans[0].send(1)
+        plans[0].recv(1)            # times out again -> poisoned
+        opt.step()
+        torch.cuda.synchronize()
+        for t, b0, m0 in zip(w, before, mom):
+            assert torch.equal(t.detach(), b0) and torch.equal(opt.state[t]["momentum_buffer"], m0)
+        lib.lwc_poison_clear()
+        opt.step()
+        assert not torch.equal(w[0].detach(), before[0])       # cleared: updates resume
     finally:
+        lib.lwc_poison_clear()
         lib.lwc_set_flag_timeout_ms(10000)
 
 
@@ -272,3 +295,40 @@ def test_hook_overlap_and_grad_steal_match_plain_exchange(method, kw):
         for sa, sb in zip(results[0], other):
             for a, b in zip(sa, sb):
                 assert torch.equal(a, b)
+
+
+@pytest.mark.parametrize("method,kw", [("Topk", dict(ratio=0.01)), ("Thresholdv", dict(threshold=1e-30)),
+                                       ("AdaptiveThreshold", {})])
+@pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float32])
+def test_no_error_feedback_never_drops_at_default_capacity(method, kw, dtype):
+    """Reference semantics without error feedback: every tie at the k-th value and every |g| >= V is sent
+    (CIFAR10/core.py:178-193).  All-equal magnitudes and a tiny V select (almost) the whole tensor; with the default
+    CompressionConfig the slots must hold it -- nothing may be cut."""
+    cfg = CompressionConfig(compress="layerwise", method=method, **kw)          # default capacities, EF off
+    grads, outs, _, plans, lw = _world(2, [4096, 50000], cfg, False, dtype=dtype)
+    for r in range(2):
+        grads[r][0].copy_(torch.where(torch.rand(4096, device="cuda") < 0.5, -0.5, 0.5).to(dtype))     # all |g| equal
+    _run(plans, 0)
+    exp = _oracle(grads, cfg, False)
+    for e, o in zip(exp, outs[0]):
+        assert torch.allclose(e, o.float(), atol=2e-2 if dtype == torch.bfloat16 else 1e-6, rtol=1e-2)
+    assert plans[0].stats()["dropped"] == 0 and plans[1].stats()["dropped"] == 0
+
+
+@pytest.mark.parametrize("method,kw", [("Topk", dict(ratio=0.01)), ("Randomk", dict(ratio=0.05)), ("TernGrad", {}),
+                                       ("RandomDithering", dict(qstates=255)), ("none", {})])
+def test_eight_virtual_ranks(method, kw):
+    """W = 8 (the box size): every rank's receiver sees eight sources; replicas must agree bit for bit."""
+    cfg = CompressionConfig(compress="layerwise", method=method, **kw)
+    W = 8
+    grads, outs, _, plans, lw = _world(W, [64, 8193, 100000], cfg, False)
+    _run(plans, 0)
+    for r in range(1, W):
+        for o0, o in zip(outs[0], outs[r]):
+            assert torch.equal(o0, o)
+    if method in ("Topk", "none"):
+        exp = _oracle(grads, cfg, False)
+        for e, o in zip(exp, outs[0]):
+            assert torch.allclose(e, o, atol=1e-6, rtol=1e-6)
+    st = plans[0].stats()
+    assert st["timeouts"] == 0 and st["dropped"] == 0
