@@ -79,6 +79,7 @@ struct GroupState {
     unsigned long long gt_total;
     unsigned long long eq_total;
     unsigned long long kept;
+    unsigned ticket[4];     // per phase: chunk CTAs of this group that finished (the last one runs the group step)
 };
 struct Counters {
     unsigned long long sent;
@@ -178,6 +179,20 @@ __device__ __forceinline__ void load_acc(const TensorRec& t, long long start, in
 }
 
 enum { STAT_NONE = 0, STAT_HIST = 1, STAT_MAX = 2, STAT_SUMSQ = 3 };
+enum { G_SCAN1 = 1, G_SCAN2, G_SCAN3, G_SET_THRESH, G_SET_ADAPT, G_FIN_MAX, G_FIN_NORM, G_SCAN_COUNTS };
+__device__ void group_tail(const DevPlan& p, int group, int phase, int mode);   // defined after the group step
+
+// Selection threshold / tie quota of a group.  The radix-select methods leave them in the group state (G_SCAN3); the
+// two threshold methods need no group step at all: V is a plan constant and max|g| is complete once k_pre has ended.
+__device__ __forceinline__ unsigned group_threshold(const DevPlan& p, const GroupState& gs) {
+    if (p.method == LWC_THRESHOLDV) return __float_as_uint(fabsf(p.threshold));
+    if (p.method == LWC_ADAPTIVE) return gs.maxbits;
+    return gs.thresh;
+}
+__device__ __forceinline__ unsigned long long group_quota(const DevPlan& p, const GroupState& gs) {
+    return (p.method == LWC_THRESHOLDV || p.method == LWC_ADAPTIVE) ? kNoQuota : gs.eq_quota;
+}
+
 
 // ---- pass 1: error-feedback accumulate + first statistic -----------------------------------------------
 template <typename GradT, int STAT>
@@ -244,6 +259,8 @@ __global__ void __launch_bounds__(kThreads) k_pre(DevPlan p) {
             }
         }
     }
+    if (STAT == STAT_HIST) group_tail(p, t.group, 0, G_SCAN1);
+    else if (STAT == STAT_SUMSQ) group_tail(p, t.group, 0, G_FIN_NORM);
 }
 
 // ---- radix levels 2 and 3 -----------------------------------------------------------------------------
@@ -278,16 +295,17 @@ __global__ void __launch_bounds__(kThreads) k_hist(DevPlan p) {
             }
         }
     }
-    if (!__syncthreads_or(any)) return;
-    unsigned* dst = (LEVEL == 2) ? gs.hist2 : gs.hist3;
-    for (int b = tid; b < kHist2; b += kThreads) {
-        const unsigned h = sh_hist[b];
-        if (h) atomicAdd(&dst[b], h);
+    if (__syncthreads_or(any)) {
+        unsigned* dst = (LEVEL == 2) ? gs.hist2 : gs.hist3;
+        for (int b = tid; b < kHist2; b += kThreads) {
+            const unsigned h = sh_hist[b];
+            if (h) atomicAdd(&dst[b], h);
+        }
     }
+    group_tail(p, t.group, LEVEL == 2 ? 1 : 2, LEVEL == 2 ? G_SCAN2 : G_SCAN3);
 }
 
 // ---- per-group bookkeeping (one CTA per group) -----------------------------------------------------
-enum { G_SCAN1 = 1, G_SCAN2, G_SCAN3, G_SET_THRESH, G_SET_ADAPT, G_FIN_MAX, G_FIN_NORM, G_SCAN_COUNTS };
 
 __device__ __forceinline__ unsigned long long block_excl_scan_u64(unsigned long long v, unsigned long long* sh,
                                                                   unsigned long long* total) {
@@ -330,7 +348,7 @@ __device__ void select_bin(const unsigned* hist, unsigned long long target, unsi
     unsigned long long sum = 0;
 #pragma unroll
     for (int k = 0; k < PER; ++k) {
-        local[k] = hist[BINS - 1 - (tid * PER + k)];
+        local[k] = __ldcg(hist + (BINS - 1 - (tid * PER + k)));
         sum += local[k];
     }
     unsigned long long total;
@@ -338,7 +356,7 @@ __device__ void select_bin(const unsigned* hist, unsigned long long target, unsi
     __shared__ unsigned s_bin;
     __shared__ unsigned long long s_above;
     __shared__ unsigned s_cnt;
-    if (tid == 0) { s_bin = 0; s_above = total - hist[0]; s_cnt = hist[0]; }   // default: lowest bin
+    if (tid == 0) { const unsigned h0 = __ldcg(hist); s_bin = 0; s_above = total - h0; s_cnt = h0; }   // default: lowest bin
     __syncthreads();
     if (target > above && target <= above + sum) {
         unsigned long long a = above;
@@ -359,9 +377,10 @@ __device__ void select_bin(const unsigned* hist, unsigned long long target, unsi
     *out_cnt = s_cnt;
 }
 
-__global__ void __launch_bounds__(kThreads) k_group(DevPlan p, int mode) {
-    __shared__ unsigned long long sh_scan[kThreads / 32 + 1];
-    const int g = blockIdx.x;
+// Per-group bookkeeping, executed by all threads of one CTA.  It used to be a kernel of its own between the chunk
+// passes (k_group, one CTA per group: four extra launches per bucket); now the chunk CTA that finishes a group's
+// pass last runs it (group_tail), so a pass and its group step are one launch.
+__device__ void group_step(const DevPlan& p, int g, int mode, unsigned long long* sh_scan) {
     const GroupCfg cfg = p.gcfg[g];
     GroupState& gs = p.gstate[g];
     const int tid = threadIdx.x;
@@ -398,7 +417,7 @@ __global__ void __launch_bounds__(kThreads) k_group(DevPlan p, int mode) {
     } else if (mode == G_FIN_NORM) {
         // fixed-order double accumulation of the chunk partials: run-to-run deterministic
         double acc = 0.0;
-        for (int c = cfg.chunk_begin + tid; c < cfg.chunk_end; c += kThreads) acc += (double)p.chunk_part[c];
+        for (int c = cfg.chunk_begin + tid; c < cfg.chunk_end; c += kThreads) acc += (double)__ldcg(p.chunk_part + c);
         __shared__ double sh_d[kThreads];
         sh_d[tid] = acc;
         __syncthreads();
@@ -411,7 +430,7 @@ __global__ void __launch_bounds__(kThreads) k_group(DevPlan p, int mode) {
         unsigned long long run_gt = 0, run_eq = 0;
         for (int base = cfg.chunk_begin; base < cfg.chunk_end; base += kThreads) {
             const int c = base + tid;
-            const unsigned packed = c < cfg.chunk_end ? p.chunk_cnt[c] : 0u;
+            const unsigned packed = c < cfg.chunk_end ? __ldcg(p.chunk_cnt + c) : 0u;
             const unsigned long long v = (unsigned long long)(packed & 0xffffu) | ((unsigned long long)(packed >> 16) << 32);
             unsigned long long tot;
             const unsigned long long ex = block_excl_scan_u64(v, sh_scan, &tot);
@@ -424,7 +443,7 @@ __global__ void __launch_bounds__(kThreads) k_group(DevPlan p, int mode) {
             run_eq += tot >> 32;
         }
         if (tid == 0) {
-            const unsigned long long quota = gs.eq_quota;
+            const unsigned long long quota = group_quota(p, gs);
             unsigned long long want = run_gt + (run_eq < quota ? run_eq : quota);
             unsigned long long kept = want < (unsigned long long)cfg.cap ? want : (unsigned long long)cfg.cap;
             gs.gt_total = run_gt;
@@ -436,6 +455,29 @@ __global__ void __launch_bounds__(kThreads) k_group(DevPlan p, int mode) {
     }
 }
 
+// Ticket per (group, phase): the CTA that completes the group's pass runs the group step on the finished statistics.
+__device__ void group_tail(const DevPlan& p, int group, int phase, int mode) {
+    __shared__ unsigned long long sh_tail_scan[kThreads / 32 + 1];
+    __shared__ int s_last;
+    __threadfence();
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        const GroupCfg& cfg = p.gcfg[group];
+        const unsigned nchunks = (unsigned)(cfg.chunk_end - cfg.chunk_begin);
+        s_last = atomicAdd(&p.gstate[group].ticket[phase], 1u) == nchunks - 1 ? 1 : 0;
+    }
+    __syncthreads();
+    if (s_last) {
+        __threadfence();
+        group_step(p, group, mode, sh_tail_scan);
+    }
+}
+
+__global__ void __launch_bounds__(kThreads) k_group(DevPlan p, int mode) {
+    __shared__ unsigned long long sh_scan[kThreads / 32 + 1];
+    group_step(p, blockIdx.x, mode, sh_scan);
+}
+
 // ---- per chunk counts of keys > T and == T -----------------------------------------------------------
 template <typename GradT>
 __global__ void __launch_bounds__(kThreads) k_count(DevPlan p) {
@@ -443,7 +485,7 @@ __global__ void __launch_bounds__(kThreads) k_count(DevPlan p) {
     __shared__ unsigned sh[kThreads / 32];
     const ChunkRec c = p.chunks[blockIdx.x];
     const TensorRec t = p.tensors[c.tensor];
-    const unsigned T = p.gstate[t.group].thresh;
+    const unsigned T = group_threshold(p, p.gstate[t.group]);
     const uint64_t salt = group_salt(p, p.gcfg[t.group].uid);
     const int tid = threadIdx.x;
     unsigned cnt = 0;   // gt in low 16 bits, eq in high 16 bits (a thread sees at most 32 elements)
@@ -471,6 +513,7 @@ __global__ void __launch_bounds__(kThreads) k_count(DevPlan p) {
         for (int w = 0; w < kThreads / 32; ++w) s += sh[w];
         p.chunk_cnt[blockIdx.x] = s;
     }
+    group_tail(p, t.group, 3, G_SCAN_COUNTS);
 }
 
 // Publish "this rank's payload for `step` is complete" to every destination.  Called by all
@@ -500,8 +543,8 @@ __global__ void __launch_bounds__(kThreads) k_compact_send(DevPlan p) {
     const TensorRec t = p.tensors[c.tensor];
     const GroupCfg cfg = p.gcfg[t.group];
     const GroupState& gs = p.gstate[t.group];
-    const unsigned T = gs.thresh;
-    const unsigned long long quota = gs.eq_quota;
+    const unsigned T = group_threshold(p, gs);
+    const unsigned long long quota = group_quota(p, gs);
     const unsigned long long cap = (unsigned long long)cfg.cap;
     const uint64_t salt = group_salt(p, cfg.uid);
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -739,7 +782,7 @@ __global__ void __launch_bounds__(kThreads) k_quant_send(DevPlan p) {
     const GroupCfg cfg = p.gcfg[t.group];
     const GroupState& gs = p.gstate[t.group];
     const int tid = threadIdx.x, lane = tid & 31;
-    const float scale = gs.scale;
+    const float scale = p.method == LWC_TERNGRAD ? __uint_as_float(gs.maxbits) : gs.scale;   // max|g| is final after k_pre
     const float qf = (float)p.qstates;
     const uint64_t salt = group_salt(p, cfg.uid);
     const unsigned long long coff = p.code_off + (unsigned long long)blockIdx.x * p.code_stride;
@@ -1101,41 +1144,34 @@ extern "C" int lwc_plan_send(LwcPlan* P, uint64_t step, void* stream_) {
     D.timeout_ns = g_flag_timeout_ns;
     const int NC = D.num_chunks, G = D.num_groups, m = D.method;
     LWC_CUDA_CHECK(cudaMemsetAsync(P->d_gstate, 0, P->state_bytes, st));
+    // Every pass is one launch: the group bookkeeping that used to sit between the passes as a kernel of its own runs in
+    // the chunk CTA that finishes the group last (group_tail).  Top-k / Random-k: 5 kernels, was 10.
     switch (m) {
         case LWC_TOPK:
         case LWC_RANDOMK:
             LWC_DISPATCH_GRAD(P->grad_dtype, k_pre<GradT, STAT_HIST><<<NC, kThreads, 0, st>>>(D));
-            k_group<<<G, kThreads, 0, st>>>(D, G_SCAN1);
             LWC_DISPATCH_GRAD(P->grad_dtype, k_hist<GradT, 2><<<NC, kThreads, 0, st>>>(D));
-            k_group<<<G, kThreads, 0, st>>>(D, G_SCAN2);
             LWC_DISPATCH_GRAD(P->grad_dtype, k_hist<GradT, 3><<<NC, kThreads, 0, st>>>(D));
-            k_group<<<G, kThreads, 0, st>>>(D, G_SCAN3);
             break;
         case LWC_THRESHOLDV:
             if (P->any_resid) { LWC_DISPATCH_GRAD(P->grad_dtype, k_pre<GradT, STAT_NONE><<<NC, kThreads, 0, st>>>(D)); }
-            k_group<<<G, kThreads, 0, st>>>(D, G_SET_THRESH);
             break;
         case LWC_ADAPTIVE:
-            LWC_DISPATCH_GRAD(P->grad_dtype, k_pre<GradT, STAT_MAX><<<NC, kThreads, 0, st>>>(D));
-            k_group<<<G, kThreads, 0, st>>>(D, G_SET_ADAPT);
-            break;
         case LWC_TERNGRAD:
             LWC_DISPATCH_GRAD(P->grad_dtype, k_pre<GradT, STAT_MAX><<<NC, kThreads, 0, st>>>(D));
-            k_group<<<G, kThreads, 0, st>>>(D, G_FIN_MAX);
             break;
         case LWC_DITHERING:
             LWC_DISPATCH_GRAD(P->grad_dtype, k_pre<GradT, STAT_SUMSQ><<<NC, kThreads, 0, st>>>(D));
-            k_group<<<G, kThreads, 0, st>>>(D, G_FIN_NORM);
             break;
         default: break;
     }
     if (m >= LWC_TOPK && m <= LWC_ADAPTIVE) {
         LWC_DISPATCH_GRAD(P->grad_dtype, k_count<GradT><<<NC, kThreads, 0, st>>>(D));
-        k_group<<<G, kThreads, 0, st>>>(D, G_SCAN_COUNTS);
         LWC_DISPATCH_GRAD(P->grad_dtype, k_compact_send<GradT><<<NC, kThreads, 0, st>>>(D));
     } else {
         LWC_DISPATCH_GRAD(P->grad_dtype, k_quant_send<GradT><<<NC, kThreads, 0, st>>>(D));
     }
+    (void)G;
     return (int)cudaGetLastError();
 }
 
@@ -1262,13 +1298,9 @@ int lwc_topk_select_impl(const float* x, int64_t n, int64_t keep, int64_t cap, u
     D.direct_val = val_out;
     D.direct_count = reinterpret_cast<long long*>(count_out);
     k_pre<float, STAT_HIST><<<nc, kThreads, 0, st>>>(D);
-    k_group<<<1, kThreads, 0, st>>>(D, G_SCAN1);
     k_hist<float, 2><<<nc, kThreads, 0, st>>>(D);
-    k_group<<<1, kThreads, 0, st>>>(D, G_SCAN2);
     k_hist<float, 3><<<nc, kThreads, 0, st>>>(D);
-    k_group<<<1, kThreads, 0, st>>>(D, G_SCAN3);
     k_count<float><<<nc, kThreads, 0, st>>>(D);
-    k_group<<<1, kThreads, 0, st>>>(D, G_SCAN_COUNTS);
     k_compact_send<float><<<nc, kThreads, 0, st>>>(D);
     return (int)cudaGetLastError();
 }
