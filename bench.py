@@ -219,6 +219,20 @@ def build_reference(args, world, rank):
     return step
 
 
+def _phase_summary(tr, batch, steps):
+    from layerwise_b200.utils.timing import PhaseTimer
+    graph, tr._graph = tr._graph, None
+    cg, tr.cuda_graph = tr.cuda_graph, False
+    tr.phase_timer = PhaseTimer()
+    try:
+        for _ in range(steps):
+            tr.train_step(batch[0], batch[1])
+        return tr.phase_timer.summary()
+    finally:
+        tr.phase_timer = None
+        tr._graph, tr.cuda_graph = graph, cg
+
+
 def main():
     args = parse()
     if not torch.cuda.is_available():
@@ -286,7 +300,7 @@ def main():
 
         def e2e_step(i):
             loss = step_e2e(i)
-            sink.append(float(loss))             # device -> host read of the step's result
+            sink.append(float(loss.detach() if hasattr(loss, 'detach') else loss))    # device -> host read of the step's result
         for i in range(2):
             e2e_step(i)
         ms2, _ = timed(e2e_step, args.steps)
@@ -299,6 +313,10 @@ def main():
         # compress + exchange + decompress alone (no backward to overlap with), device-timed, max over ranks
         extra["compress_comm_ms_per_step"] = max_over_ranks(tr.exchanger.engine.benchmark_exchange(10))
         extra["exchange_stats"] = tr.exchanger.engine.stats()
+    if args.impl == "ours" and args.phase_times and hasattr(tr, "profile_phases"):
+        # eager steps timed phase by phase with CUDA events (max over ranks): explains the number, is not the number
+        tr.profile_phases(dev_x[0], dev_y[0], steps=2)           # warm the eager path
+        extra["phases_ms_per_step"] = {k: v / 5 for k, v in _phase_summary(tr, (dev_x[0], dev_y[0]), 5).items()}
     if rank == 0:
         out = {
             "metric": "ResNet-50 img/s, layerwise Top-k 1% (train step incl. compress+exchange+SGD)",

@@ -49,6 +49,8 @@ def get_parser():
     p.add_argument("--max_batches", type=int, default=None)
     p.add_argument("--cuda_graph", action="store_true",
                    help="capture the training step once and replay it as a CUDA graph (fused engine)")
+    p.add_argument("--phase_times", action="store_true",
+                   help="print per-phase device times (CUDA events + NVTX ranges, max over ranks) after every epoch")
     p.add_argument("--dtype", type=str, default="fp32", choices=["fp32", "bf16", "fp16"])
     p.add_argument("--host_loader", action="store_true", help="DataLoader pipeline instead of device-resident data")
     p.add_argument("--nchw", action="store_true", help="keep NCHW activations (default on CUDA: channels_last, which the fused kernels need)")
@@ -98,7 +100,7 @@ def main(argv=None):
                     loggers=loggers, timer=timer, test_time_in_total=False, compress=args.compress,
                     method=args.method, K=args.ratio, V=args.threshold, qstates=args.qstates,
                     error_feedback=args.error_feedback, backend=args.backend, engine=args.engine,
-                    max_batches=args.max_batches, cuda_graph=args.cuda_graph)
+                    max_batches=args.max_batches, cuda_graph=args.cuda_graph, phase_times=args.phase_times)
     if rank == 0:
         os.makedirs(os.path.expanduser(args.log_dir), exist_ok=True)
         with open(os.path.join(os.path.expanduser(args.log_dir), "logs.tsv"), "w") as f:

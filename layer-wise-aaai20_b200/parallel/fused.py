@@ -111,8 +111,8 @@ class ExchangePlan:
         self.region_bytes = int(self.lib.lwc_plan_region_bytes(self.handle))
         self.numel = sum(numel)
         # kernels per send (the memset is not one of ours) and per receive
-        self.kernels_per_send = {cref.TOPK: 9, cref.RANDOMK: 9, cref.THRESHOLDV: 4 + int(resids is not None),
-                                 cref.ADAPTIVE: 5, cref.TERNGRAD: 3, cref.DITHERING: 3}.get(self.method, 1)
+        self.kernels_per_send = {cref.TOPK: 5, cref.RANDOMK: 5, cref.THRESHOLDV: 2 + int(resids is not None),
+                                 cref.ADAPTIVE: 3, cref.TERNGRAD: 2, cref.DITHERING: 2}.get(self.method, 1)
 
     def bind(self, region_ptrs: Sequence[int], flag_ptrs: Sequence[int]):
         abi.check(self.lib.lwc_plan_bind(self.handle, _ptr_array(region_ptrs), _ptr_array(flag_ptrs)),

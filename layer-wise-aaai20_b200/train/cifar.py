@@ -125,7 +125,9 @@ class GraphedTrainStep:
 
 
 def run_batches(model, batches, training, exchanger: Optional[GradientExchanger] = None,
-                optimizer_step=None, stats=None, max_batches: Optional[int] = None, graphed=None):
+                optimizer_step=None, stats=None, max_batches: Optional[int] = None, graphed=None, phase_timer=None):
+    """``phase_timer`` (utils.timing.PhaseTimer): CUDA-event time + NVTX range per phase of every training step."""
+    from ..utils.timing import maybe_phase
     stats = stats or StatsLogger(("loss", "correct"))
     model.train(training)
     ctx = torch.enable_grad() if training else torch.no_grad()
@@ -136,21 +138,25 @@ def run_batches(model, batches, training, exchanger: Optional[GradientExchanger]
             if training and graphed is not None:
                 stats.append(graphed(batch))
                 continue
-            output = model(batch)
+            with maybe_phase(phase_timer, "forward" if training else "eval forward"):
+                output = model(batch)
             stats.append(output)
             if training:
-                output["loss"].sum().backward()
+                with maybe_phase(phase_timer, "backward (+hooked compress/send)"):
+                    output["loss"].sum().backward()
                 if exchanger is not None:
-                    exchanger.exchange()
-                optimizer_step()
-                _zero_grads(model, exchanger)
+                    with maybe_phase(phase_timer, "exchange (exposed: join + receive)"):
+                        exchanger.exchange()
+                with maybe_phase(phase_timer, "optimizer"):
+                    optimizer_step()
+                    _zero_grads(model, exchanger)
     return stats
 
 
 def train_epoch(model, train_batches, test_batches, optimizer_step, timer, exchanger=None,
-                test_time_in_total=True, max_batches=None, graphed=None):
+                test_time_in_total=True, max_batches=None, graphed=None, phase_timer=None):
     train_stats = run_batches(model, train_batches, True, exchanger, optimizer_step,
-                              max_batches=max_batches, graphed=graphed)
+                              max_batches=max_batches, graphed=graphed, phase_timer=phase_timer)
     train_time = timer()
     test_stats = run_batches(model, test_batches, False, max_batches=max_batches)
     test_time = timer(test_time_in_total)
@@ -166,8 +172,10 @@ def train_epoch(model, train_batches, test_batches, optimizer_step, timer, excha
 def train(model, optimizer, train_batches, test_batches, epochs, master_address=None,
           world_size=1, rank=0, loggers=(), test_time_in_total=True, timer=None, compress=None,
           method=None, K=None, V=None, qstates=None, error_feedback=False, backend=None,
-          engine="auto", max_batches=None, cfg: Optional[CompressionConfig] = None, cuda_graph: bool = False):
-    """Train for ``epochs``; returns the last epoch's summary dict."""
+          engine="auto", max_batches=None, cfg: Optional[CompressionConfig] = None, cuda_graph: bool = False,
+          phase_times: bool = False):
+    """Train for ``epochs``; returns the last epoch's summary dict.  ``phase_times``: print a per-phase device-time
+    table (forward / backward / exposed exchange / optimizer, max over ranks) after every epoch."""
     if world_size > 1 or master_address:
         comm.init_process_group(backend=backend, init_method=master_address,
                                 world_size=world_size, rank=rank)
@@ -177,11 +185,20 @@ def train(model, optimizer, train_batches, test_batches, epochs, master_address=
     exchanger = GradientExchanger([p for p in model.parameters() if p.requires_grad], cfg,
                                   engine=engine)
     timer = timer or Timer(torch.cuda.synchronize if torch.cuda.is_available() else None)
-    graphed = GraphedTrainStep(model, exchanger, optimizer) if cuda_graph else None
+    graphed = GraphedTrainStep(model, exchanger, optimizer) if (cuda_graph and not phase_times) else None
+    from ..utils.timing import PhaseTimer
+    ptimer = PhaseTimer() if phase_times else None
     summary = {}
     for epoch in range(epochs):
         stats = train_epoch(model, train_batches, test_batches, optimizer.step, timer, exchanger,
-                            test_time_in_total=test_time_in_total, max_batches=max_batches, graphed=graphed)
+                            test_time_in_total=test_time_in_total, max_batches=max_batches, graphed=graphed,
+                            phase_timer=ptimer)
+        if ptimer is not None:
+            nsteps = min(len(train_batches), max_batches) if max_batches else len(train_batches)
+            table = ptimer.table(nsteps)
+            ptimer.reset()
+            if rank == 0:
+                print(table, flush=True)
         exchanger.check_health()             # a peer whose flags stopped arriving raises here instead of hanging the job
         lr = optimizer.param_values()["lr"] * train_batches.batch_size \
             if hasattr(optimizer, "param_values") else optimizer.param_groups[0]["lr"]

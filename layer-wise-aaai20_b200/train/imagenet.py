@@ -33,6 +33,7 @@ from ..parallel.exchange import CompressionConfig, GradientExchanger
 from ..utils import mixed
 from ..utils.checkpoint import load_checkpoint, save_checkpoint
 from ..utils.logging import FileLogger, TensorboardLogger
+from ..utils.timing import maybe_phase
 from ..utils.meter import AverageMeter, NetworkMeter, TimeMeter
 from ..utils.schedule import PhaseScheduler
 
@@ -103,6 +104,7 @@ class Trainer:
                  wrapper: Optional[str] = None, randk: float = 1.0, seed: int = 2147483647,
                  cuda_graph: bool = False):
         self.device = torch.device(device or ("cuda" if torch.cuda.is_available() else "cpu"))
+        self.phase_timer = None           # a utils.timing.PhaseTimer while profile_phases() runs
         if self.device.type == "cuda":
             torch.backends.cudnn.benchmark = True     # as the reference does (train_imagenet_nv.py:95): autotune conv algos
             if os.environ.get("LWC_CUDNN_BENCH_LIMIT") is not None:      # 0 = try every algorithm (default: the first 10)
@@ -166,9 +168,13 @@ class Trainer:
 
     # ---- one optimisation step ---------------------------------------------------------------------------
     def forward_backward(self, x: torch.Tensor, target: torch.Tensor):
-        out = (self.wrapper if self.wrapper is not None else self.net)(x)
-        loss = self.criterion(out, target)
-        (loss * self.loss_scale if self.loss_scale != 1.0 else loss).backward()
+        with maybe_phase(self.phase_timer, "forward"):
+            out = (self.wrapper if self.wrapper is not None else self.net)(x)
+            loss = self.criterion(out, target)
+        # the backward hooks launch compress + send of every finished bucket on the comm stream: that work overlaps
+        # this phase and is not part of "exchange (exposed)" below
+        with maybe_phase(self.phase_timer, "backward (+hooked compress/send)"):
+            (loss * self.loss_scale if self.loss_scale != 1.0 else loss).backward()
         return out, loss
 
     # ---- whole-step CUDA graph (opt-in) ---------------------------------------------------------------------
@@ -224,14 +230,33 @@ class Trainer:
         return self._g_out
 
     def _step_body(self, images, target):
-        x = self.normalize(images) if images.dtype == torch.uint8 else images
+        pt = self.phase_timer
+        with maybe_phase(pt, "normalize"):
+            x = self.normalize(images) if images.dtype == torch.uint8 else images
         out, loss = self.forward_backward(x, target)
-        self.exchanger.exchange()
-        self._attach_master_grads()
-        self.optimizer.step()
-        self.zero_grad()
+        with maybe_phase(pt, "exchange (exposed: join + receive)"):
+            self.exchanger.exchange()
+        with maybe_phase(pt, "optimizer"):
+            self._attach_master_grads()
+            self.optimizer.step()
+            self.zero_grad()
         self.steps += 1
         return out, loss
+
+    def profile_phases(self, images, target, steps: int = 5) -> str:
+        """Run ``steps`` eager training steps with CUDA-event timing of every phase (also NVTX ranges) and return the
+        per-phase table, max over ranks (the reference has only wall-clock meters, meter.py:49-60)."""
+        from ..utils.timing import PhaseTimer
+        graph, self._graph = self._graph, None
+        cg, self.cuda_graph = self.cuda_graph, False
+        self.phase_timer = PhaseTimer()
+        try:
+            for _ in range(steps):
+                self.train_step(images, target)
+            return self.phase_timer.table(steps)
+        finally:
+            self.phase_timer = None
+            self._graph, self.cuda_graph = graph, cg
 
     def train_step(self, images: torch.Tensor, target: torch.Tensor):
         """``images``: uint8 NCHW (host pinned or device) or already-normalised float; returns (logits, loss)."""

@@ -52,6 +52,9 @@ def get_parser():
     p.add_argument("--logdir", default="", type=str)
     p.add_argument("--name", type=str, default="imagenet")
     p.add_argument("--short-epoch", action="store_true")
+    p.add_argument("--phase-times", type=int, default=0, metavar="STEPS",
+                   help="before training, time STEPS eager steps phase by phase (CUDA events + NVTX ranges, max over "
+                        "ranks) on the first batch and log the table")
     p.add_argument("--log_all_workers", type=int, default=0)
     p.add_argument("--sparsification", action="store_true")
     p.add_argument("--randk", type=float, default=1)
@@ -199,6 +202,11 @@ def main(argv=None):
     log.event("~~epoch\thours\ttop1\ttop5\n")
     last_epoch = scheduler.tot_epochs if args.epochs is None else min(scheduler.tot_epochs, args.start_epoch + args.epochs)
     top1 = top5 = 0.0
+    if args.phase_times > 0:
+        dm.set_epoch(args.start_epoch)
+        images, target = next(iter(dm.trn_dl))
+        table = trainer.profile_phases(images, target, steps=args.phase_times)
+        log.console("per-phase device time, max over ranks:\n" + table)
     for epoch in range(args.start_epoch, last_epoch):
         phase = dm.get_phase(epoch)      # looked up before set_epoch consumes it (the reference looks
         dm.set_epoch(epoch)              # afterwards and therefore never writes its phase checkpoints)

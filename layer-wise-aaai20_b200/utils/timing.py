@@ -8,6 +8,7 @@ as a max over ranks.
 """
 from __future__ import annotations
 
+import contextlib
 import time
 from collections import defaultdict
 from typing import Callable, Dict, Optional
@@ -118,3 +119,33 @@ class PhaseTimer:
         self._pending.clear()
         self._wall.clear()
         self._open.clear()
+
+    @contextlib.contextmanager
+    def phase(self, name: str, stream=None):
+        """``with timer.phase('forward'):`` -- a device-timed phase that is also an NVTX range."""
+        from .nvtx import nvtx_range
+        with nvtx_range(name):
+            self.start(name, stream)
+            try:
+                yield
+            finally:
+                self.stop(name, stream)
+
+    def table(self, steps: int = 1, reduce_max: bool = True) -> str:
+        """Per-phase milliseconds per step (max over ranks) as a fixed-width table."""
+        s = self.summary(reduce_max)
+        tot = sum(s.values()) or 1.0
+        lines = [f"{'phase':<28s}{'ms/step':>10s}{'share':>8s}"]
+        for k, v in sorted(s.items(), key=lambda kv: -kv[1]):
+            lines.append(f"{k:<28s}{v / max(steps, 1):10.3f}{100.0 * v / tot:7.1f}%")
+        return "\n".join(lines)
+
+
+@contextlib.contextmanager
+def maybe_phase(timer: Optional["PhaseTimer"], name: str):
+    """No-op without a timer: the hot loops call this unconditionally."""
+    if timer is None:
+        yield
+    else:
+        with timer.phase(name):
+            yield

@@ -57,6 +57,36 @@ def test_noalloc_topk_matches_workspace_variant_twice_in_a_row():
         assert torch.equal(idx_new.long(), want)
 
 
+def test_noalloc_topk_allocates_nothing_even_at_its_maximum_size():
+    """The point of the entry point is that it obtains no device memory: free memory as the driver reports it, and
+    torch's allocator statistics, must be the same before and after a call -- including a call at the documented
+    maximum n = 2**24, which also shows that the selection state of such a tensor fits the built-in scratch."""
+    from layerwise_b200 import _native
+    lib = _native.lib()
+    n, keep = 1 << 24, 4096
+    cap = keep + 64
+    g = torch.Generator(device="cuda").manual_seed(7)
+    x = torch.randn(n, device="cuda", generator=g)
+    idx = torch.full((cap,), -1, dtype=torch.int32, device="cuda")
+    val = torch.zeros(cap, dtype=torch.float32, device="cuda")
+    cnt = torch.zeros(1, dtype=torch.int64, device="cuda")
+    st = C.c_void_p(torch.cuda.current_stream().cuda_stream)
+    # first call outside the measured window: it looks the scratch address up (once per device)
+    assert lib.lwc_topk_select_f32_noalloc(x.data_ptr(), n, keep, cap, idx.data_ptr(), val.data_ptr(), cnt.data_ptr(), st) == 0
+    torch.cuda.synchronize()
+    free0, _ = torch.cuda.mem_get_info()
+    alloc0, reserved0 = torch.cuda.memory_allocated(), torch.cuda.memory_reserved()
+    assert lib.lwc_topk_select_f32_noalloc(x.data_ptr(), n, keep, cap, idx.data_ptr(), val.data_ptr(), cnt.data_ptr(), st) == 0
+    torch.cuda.synchronize()
+    free1, _ = torch.cuda.mem_get_info()
+    assert free1 == free0
+    assert torch.cuda.memory_allocated() == alloc0 and torch.cuda.memory_reserved() == reserved0
+    k = int(cnt.item())
+    assert k == keep
+    want = x.abs().topk(keep).indices.sort().values
+    assert torch.equal(idx[:k].long(), want)
+
+
 def test_noalloc_topk_rejects_oversize_without_touching_outputs():
     from layerwise_b200 import _native
     lib = _native.lib()
