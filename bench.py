@@ -53,6 +53,8 @@ def parse():
     p.add_argument("--engine", default="auto")
     p.add_argument("--ref-dtype", default="fp16", choices=["fp16", "fp32"])
     p.add_argument("--skip-e2e", action="store_true")
+    p.add_argument("--cifar-dtype", default="bf16", choices=["bf16", "fp32"],
+                   help="compute dtype of our arm for the CIFAR architectures (the reference's CIFAR code is fp32)")
     p.add_argument("--nvls", action="store_true", help="NVSwitch-multicast payload stores (N > 1)")
     p.add_argument("--phase-times", action="store_true", help="also report compress+comm ms/step")
     p.add_argument("--graph", action="store_true", default=True,
@@ -191,6 +193,14 @@ def build_reference(args, world, rank):
         mean, std = mean.half(), std.half()
     wsize = float(world)
 
+    def exchange():
+        if args.compress == "layerwise":
+            layerwise_compressed_comm(model, wsize, args.method, args.ratio, 0.001, 255)
+        else:       # --compress none: the reference's plain per-tensor all-reduce (train_imagenet_nv.py:382-386)
+            for param in model.parameters():
+                dist.all_reduce(param.grad.data)
+                param.grad.data /= wsize
+
     def step(images_u8, target):
         # BatchTransformDataLoader.process_tensors (dataloader.py:88-93)
         x = images_u8.cuda(non_blocking=True)
@@ -203,7 +213,7 @@ def build_reference(args, world, rank):
             loss = loss * loss_scale
             model.zero_grad()
             loss.backward()
-            layerwise_compressed_comm(model, wsize, args.method, args.ratio, 0.001, 255)
+            exchange()
             ref_fp16.model_grads_to_master_grads(model_params, master_params)
             for p in master_params:
                 p.grad.data = p.grad.data / loss_scale
@@ -213,9 +223,109 @@ def build_reference(args, world, rank):
         else:                                          # :429-441
             opt.zero_grad()
             loss.backward()
-            layerwise_compressed_comm(model, wsize, args.method, args.ratio, 0.001, 255)
+            exchange()
             opt.step()
         return loss
+    return step
+
+
+CIFAR_ARCHS = ("resnet9", "alexnet", "alexnet_graph", "vgg16")
+
+
+class _CifarStep:
+    """Adapter: one CIFAR training step (dawn.py recipe) behind the ``train_step(images, target) -> (out, loss)``
+    interface that the timing code drives.  ``images``: float32 NCHW batch (host pinned or device), as the
+    reference's ``Batches`` hands them over (CIFAR10/torch_backend.py:57-60)."""
+
+    def __init__(self, args, world, rank):
+        import layerwise_b200  # noqa: F401
+        from layerwise_b200.models import build_cifar_model
+        from layerwise_b200 import _native
+        from layerwise_b200.models.graph import trainable_params
+        from layerwise_b200.ops.sgd import SGD
+        from layerwise_b200.parallel.exchange import CompressionConfig, GradientExchanger
+        from layerwise_b200.train.cifar import GraphedTrainStep
+        from layerwise_b200.utils.mixed import bn_to_float
+        _native.require()
+        self.device = torch.device("cuda", torch.cuda.current_device())
+        self.dtype = {"fp32": torch.float32, "bf16": torch.bfloat16}[args.cifar_dtype]
+        name = {"alexnet": "alexnet1", "alexnet_graph": "alexnet"}.get(args.arch, args.arch)
+        model = build_cifar_model(name).to(self.device).to(memory_format=torch.channels_last)
+        if self.dtype != torch.float32:
+            model = bn_to_float(model.to(self.dtype))
+        self.model = model
+        bs = args.batch
+        cfg = CompressionConfig(compress=args.compress, method=args.method, ratio=args.ratio, qstates=255,
+                                threshold=0.001, error_feedback=not args.no_ef, nvls=args.nvls)
+        self.exchanger = GradientExchanger(trainable_params(model), cfg, engine=args.engine)
+        self.opt = SGD(trainable_params(model), lr=lambda step: 0.1 / bs, momentum=0.9, weight_decay=5e-4 * bs, nesterov=True)
+        self.graphed = GraphedTrainStep(model, self.exchanger, self.opt) if args.graph else None
+        self._graph = None
+        self.cuda_graph = False
+        self.phase_timer = None
+
+    def _batch(self, images, target):
+        x = images.to(self.device, non_blocking=True).to(self.dtype).contiguous(memory_format=torch.channels_last)
+        return {"input": x, "target": target.to(self.device, non_blocking=True)}
+
+    def train_step(self, images, target):
+        from layerwise_b200.train.cifar import _zero_grads
+        batch = self._batch(images, target)
+        if self.graphed is not None:
+            out = self.graphed(batch)
+        else:
+            self.model.train(True)
+            out = self.model(batch)
+            out["loss"].sum().backward()
+            self.exchanger.exchange()
+            self.opt.step()
+            _zero_grads(self.model, self.exchanger)
+        return None, out["loss"].detach().sum()
+
+
+def build_reference_cifar(args, world, rank):
+    """The reference's own CIFAR-10 code (CIFAR10/core.py run_batches body :303-321 with its models, its
+    TorchOptimiser/SGD and its layerwise_compressed_comm), fp32 as committed.  ``entiremodel`` raises TypeError in the
+    reference as committed (``for param in model.parameters:``, core.py:230) and is reported as unavailable."""
+    ref = os.path.join(ROOT, "baseline", "_ref")
+    if not os.path.isdir(os.path.join(ref, "CIFAR10")):
+        raise FileNotFoundError("baseline/_ref missing (cp -r /root/reference/. baseline/_ref)")
+    sys.path.insert(0, ref)
+    from CIFAR10 import core as rcore
+    from CIFAR10 import torch_backend as rtb
+    if args.arch == "alexnet":
+        from CIFAR10.alexnet import AlexNet
+        model = AlexNet().cuda()
+    elif args.arch == "vgg16":
+        from CIFAR10.vgg16 import vgg16model
+        model = vgg16model.cuda()
+    else:
+        # dawn.py runs main() at import: execute only its definitions (the text above ``def main``), unmodified
+        src = open(os.path.join(ref, "CIFAR10", "dawn.py")).read().split("def main")[0]
+        ns = {}
+        exec(compile(src, "dawn_defs", "exec"), ns)
+        builder = ns["resnet9"] if args.arch == "resnet9" else ns["alexnet"]
+        model = rtb.Network(rcore.union(builder(), ns["losses"])).cuda()
+    bs = args.batch
+    opt = rtb.SGD(rtb.trainable_params(model), lr=lambda step: 0.1 / bs, momentum=0.9, weight_decay=5e-4 * bs, nesterov=True)
+    wsize = float(world)
+    model.train(True)
+
+    def step(images, target):
+        batch = {"input": images.cuda(non_blocking=True), "target": target.cuda(non_blocking=True).long()}
+        output = model(batch)
+        output["loss"].sum().backward()
+        if args.compress == "layerwise":
+            rcore.layerwise_compressed_comm(model, wsize, args.method, args.ratio, 0.001, 255)
+        elif args.compress == "entiremodel":
+            rcore.entiremodel_compressed_comm(model, wsize, args.method, args.ratio, 0.001, 255)
+        else:
+            for layer in model.parameters():
+                dist.all_reduce(layer.grad.data)
+                layer.grad.data /= wsize
+        opt.step()
+        model.zero_grad()
+        return output["loss"].sum()
     return step
 
 
@@ -239,25 +349,41 @@ def main():
         print(json.dumps({"impl": args.impl, "unavailable": "no CUDA device"}))
         return 0
     world, rank, local = setup_dist(args)
+    cifar = args.arch in CIFAR_ARCHS
+    if cifar and args.size == 224:
+        args.size = 32
+        if args.batch == 224:
+            args.batch = 512
     B, S = args.batch, args.size
     g = torch.Generator().manual_seed(1234 + rank)
     nbuf = 4
-    host_x = [torch.randint(0, 256, (B, 3, S, S), dtype=torch.uint8, generator=g).pin_memory() for _ in range(nbuf)]
-    host_y = [torch.randint(0, 1000, (B,), generator=g).pin_memory() for _ in range(nbuf)]
+    if cifar:       # normalised float32 batches, 10 classes (what the reference's Batches yields)
+        host_x = [torch.randn(B, 3, S, S, generator=g).pin_memory() for _ in range(nbuf)]
+        host_y = [torch.randint(0, 10, (B,), generator=g).pin_memory() for _ in range(nbuf)]
+    else:
+        host_x = [torch.randint(0, 256, (B, 3, S, S), dtype=torch.uint8, generator=g).pin_memory() for _ in range(nbuf)]
+        host_y = [torch.randint(0, 1000, (B,), generator=g).pin_memory() for _ in range(nbuf)]
     dev_x = [t.cuda() for t in host_x]
     dev_y = [t.cuda() for t in host_y]
 
     launches = {"n": 0}
     if args.impl == "reference":
         try:
-            ref_step = build_reference(args, world, rank)
+            ref_step = build_reference_cifar(args, world, rank) if cifar else build_reference(args, world, rank)
+            ref_step(dev_x[0], dev_y[0])               # the reference as committed may raise here (entiremodel: D1)
+            torch.cuda.synchronize()
         except Exception as e:      # noqa: BLE001
             if rank == 0:
                 print(json.dumps({"impl": "reference", "unavailable": f"{type(e).__name__}: {e}"[:300]}))
             return 0
         step_dev = lambda i: ref_step(dev_x[i % nbuf], dev_y[i % nbuf])      # noqa: E731
         step_e2e = lambda i: ref_step(host_x[i % nbuf], host_y[i % nbuf])    # noqa: E731
-        dtype, par = args.ref_dtype, f"dp{world}"
+        dtype, par = ("fp32" if cifar else args.ref_dtype), f"dp{world}"
+    elif cifar:
+        tr = _CifarStep(args, world, rank)
+        step_dev = lambda i: tr.train_step(dev_x[i % nbuf], dev_y[i % nbuf])[1]     # noqa: E731
+        step_e2e = lambda i: tr.train_step(host_x[i % nbuf], host_y[i % nbuf])[1]   # noqa: E731
+        dtype, par = args.cifar_dtype, f"dp{world}"
     else:
         tr = build_ours(args, world, rank)
         args.graph = args.graph and hasattr(tr.exchanger.engine, "enable_graph_mode")
@@ -305,7 +431,8 @@ def main():
             e2e_step(i)
         ms2, _ = timed(e2e_step, args.steps)
         e2e = {"value": imgs / (ms2 / 1e3), "unit": "img/s",
-               "h2d_bytes_per_step": host_x[0].numel() + host_y[0].numel() * 8, "d2h_bytes_per_step": 4,
+               "h2d_bytes_per_step": host_x[0].numel() * host_x[0].element_size() + host_y[0].numel() * 8,
+               "d2h_bytes_per_step": 4,
                "ms_per_step": ms2 / args.steps}
 
     extra = {}
@@ -319,17 +446,22 @@ def main():
         extra["phases_ms_per_step"] = {k: v / 5 for k, v in _phase_summary(tr, (dev_x[0], dev_y[0]), 5).items()}
     if rank == 0:
         out = {
-            "metric": "ResNet-50 img/s, layerwise Top-k 1% (train step incl. compress+exchange+SGD)",
+            "metric": ("ResNet-50 img/s, layerwise Top-k 1% (train step incl. compress+exchange+SGD)"
+                       if (args.arch == "resnet50" and args.method == "Topk" and args.compress == "layerwise") else
+                       f"{args.arch} img/s, {args.compress} {args.method} {args.ratio:g} (train step incl. compress+exchange+SGD)"),
             "value": value, "unit": "img/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak",
             "vs_baseline": (value / BASELINE_PUBLISHED) if BASELINE_PUBLISHED else None,
-            "dtype": dtype, "data": "synthetic (uint8 224x224 images, random-init weights)",
+            "dtype": dtype,
+            "data": (f"synthetic (float32 {S}x{S} normalised images, 10 classes, random-init weights)" if cifar
+                     else f"synthetic (uint8 {S}x{S} images, random-init weights)"),
             "impl": args.impl,
             "config": {"model": args.arch, "global_batch": B * world, "per_gpu_batch": B, "seq_len": None,
                        "image_size": S, "parallelism": par, "compress": args.compress, "method": args.method,
                        "ratio": args.ratio, "error_feedback": (not args.no_ef) if args.impl == "ours" else False,
                        "l2_policy": "inputs+activations per step (>1 GB) exceed the 126 MB L2; 4 rotating input buffers",
-                       "optimizer": "SGD momentum 0.9 nesterov wd 1e-4, fp32 masters",
+                       "optimizer": ("SGD momentum 0.9 nesterov wd 5e-4*bs, lr/bs (dawn.py recipe)" if cifar
+                                     else "SGD momentum 0.9 nesterov wd 1e-4, fp32 masters"),
                        "cuda_graph": bool(args.graph and args.impl == "ours")},
             "clocks": clocks, "e2e": e2e, "gpu_launches": launches["n"],
         }
