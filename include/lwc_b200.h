@@ -102,6 +102,10 @@ size_t lwc_plan_region_bytes(const LwcPlan* plan);
 int lwc_plan_bind(LwcPlan* plan, void* const* region_dev, void* const* flags_dev);
 /* optional: uniforms in [0,1) (quantisers) or integer keys (Random-k) injected per tensor
  * for bit-exact tests; NULL restores the counter-based generator */
+/* Shared-seed Random-k: ship values only (4 bytes per kept element instead of (index, value) pairs); every rank selects
+ * the same positions, the receiver recomputes them from the hash keys (IMAGENET/training/sparsified_ddp.py:410-412
+ * packs k values the same way, relying on identical randperm streams). */
+int lwc_plan_set_values_only(LwcPlan* plan, int enable);
 int lwc_plan_set_random(LwcPlan* plan, const void* const* rand_dev);
 /* Sender side: error-feedback accumulate, select / quantise, residual update, pack,
  * store into every rank's slot, release flags.  step must increase by 1 per call. */

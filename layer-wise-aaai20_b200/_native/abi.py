@@ -73,6 +73,7 @@ def declare(lib: C.CDLL):
     sig("lwc_plan_use_device_step", C.c_int, vp, C.c_int, u64)
     sig("lwc_plan_bind_multicast", C.c_int, vp, vp)
     sig("lwc_plan_set_random", C.c_int, vp, c_void_pp)
+    sig("lwc_plan_set_values_only", C.c_int, vp, C.c_int)
     sig("lwc_plan_update_grads", C.c_int, vp, c_void_pp, vp)
     sig("lwc_plan_send", C.c_int, vp, u64, vp)
     sig("lwc_plan_recv", C.c_int, vp, u64, vp)

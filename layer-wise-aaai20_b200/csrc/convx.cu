@@ -474,34 +474,40 @@ __global__ void __launch_bounds__(WX_THREADS, 1) k_wx(const __grid_constant__ CU
 }
 
 // Sum the split partials in a fixed order and transpose [box = (tap, chunk)][64 ci][Cout] -> [Cout][tap][Cin].
-// grid = (nboxes * 8, Cout / 64), block = 256 = 64 output channels x 4 split lanes: a CTA owns 8 input channels x 64
-// output channels of one box; lane z sums splits z, z + 4, ... (8 independent loads in flight per step), the four
-// lane sums are combined in a fixed order.
+// grid = (nboxes * 8, Cout / 64), block = 256 = 16 column quads (float4 = 4 output channels) x 16 split lanes: a CTA
+// owns 8 input channels x 64 output channels of one box; lane z sums splits z, z + 16, ... (8 independent 16-byte
+// loads in flight per step, at most ceil(ksplit / 16) dependent steps), the lane sums are combined in a fixed order.
 template <typename OutT>
 __global__ void __launch_bounds__(256) k_wx_reduce(const float* __restrict__ ws, OutT* __restrict__ out, int ksplit, int nboxes,
                                                    int cchunks, int Cout, int Cin, int ntaps, float scale) {
-    __shared__ float part[4][8][65];
+    __shared__ float part[16][8][68];
     const int bx = blockIdx.x >> 3, i0 = (blockIdx.x & 7) * 8, co0 = blockIdx.y * 64;
     const int tap = bx / cchunks, cc = bx - tap * cchunks;
-    const int tx = threadIdx.x & 63, zl = threadIdx.x >> 6;
-    float s[8];
+    const int tq = threadIdx.x & 15, zl = threadIdx.x >> 4;
+    float4 s[8];
 #pragma unroll
-    for (int i = 0; i < 8; ++i) s[i] = 0.0f;
+    for (int i = 0; i < 8; ++i) s[i] = make_float4(0.f, 0.f, 0.f, 0.f);
     const size_t zstride = (size_t)nboxes * 64 * Cout;
-    const float* src = ws + ((size_t)bx * 64 + i0) * Cout + co0 + tx;
-    for (int zz = zl; zz < ksplit; zz += 4) {
+    const float* src = ws + ((size_t)bx * 64 + i0) * Cout + co0 + tq * 4;
+    for (int zz = zl; zz < ksplit; zz += 16) {
         const float* q = src + (size_t)zz * zstride;
 #pragma unroll
-        for (int i = 0; i < 8; ++i) s[i] += q[(size_t)i * Cout];
+        for (int i = 0; i < 8; ++i) {
+            const float4 v = __ldcg(reinterpret_cast<const float4*>(q + (size_t)i * Cout));
+            s[i].x += v.x; s[i].y += v.y; s[i].z += v.z; s[i].w += v.w;
+        }
     }
 #pragma unroll
-    for (int i = 0; i < 8; ++i) part[zl][i][tx] = s[i];
+    for (int i = 0; i < 8; ++i) *reinterpret_cast<float4*>(&part[zl][i][tq * 4]) = s[i];
     __syncthreads();
     for (int idx = threadIdx.x; idx < 512; idx += 256) {
         const int i = idx & 7, o = idx >> 3;
         const int ci = cc * 64 + i0 + i;
         if (ci < Cin) {
-            const float v = ((part[0][i][o] + part[1][i][o]) + (part[2][i][o] + part[3][i][o])) * scale;
+            float v = 0.0f;
+#pragma unroll
+            for (int z = 0; z < 16; ++z) v += part[z][i][o];
+            v *= scale;
             OutT* dst = out + ((size_t)(co0 + o) * ntaps + tap) * Cin + ci;
             if constexpr (sizeof(OutT) == 4) *dst = v; else *dst = __float2bfloat16_rn(v);
         }

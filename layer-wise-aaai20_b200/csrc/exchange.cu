@@ -123,6 +123,9 @@ struct DevPlan {     // passed by value to kernels
     // NVLS variant: multicast address of this plan's region (one store lands in every rank's slot through the
     // NVSwitch); NULL -> one unicast store per destination
     char* mc_region;
+    // shared-seed Random-k: the mask is a function of (seed, step, tensor, index) alone, so every rank selects the same
+    // positions; only values travel and the receiver recomputes the positions (reference: sparsified_ddp.py:410-412)
+    int values_only;
     // stand-alone selection: write (idx, val, count) here instead of into exchange slots
     uint32_t* direct_idx;
     float* direct_val;
@@ -498,7 +501,7 @@ __global__ void __launch_bounds__(kThreads) k_count(DevPlan p) {
 #pragma unroll
         for (int k = 0; k < 4; ++k) {
             if (j + k >= c.len) break;
-            if (v[k] == 0.0f) continue;
+            if (v[k] == 0.0f && !p.values_only) continue;
             const long long i = c.start + j + k;
             const uint32_t key = make_key(p.method, v[k], t.rnd, i, t.goff + i, salt);
             cnt += (key > T) ? 1u : (key == T ? 0x10000u : 0u);
@@ -590,7 +593,7 @@ __global__ void __launch_bounds__(kThreads) k_compact_send(DevPlan p) {
                 load_acc<GradT>(t, c.start, j, c.len, v[it]);
 #pragma unroll
                 for (int k = 0; k < 4; ++k) {
-                    if (j + k >= c.len || v[it][k] == 0.0f) continue;
+                    if (j + k >= c.len || (v[it][k] == 0.0f && !p.values_only)) continue;
                     const long long i = c.start + j + k;
                     const uint32_t key = make_key(p.method, v[it][k], t.rnd, i, t.goff + i, salt);
                     f |= (key > T) ? (1u << k) : (key == T ? (16u << k) : 0u);
@@ -628,19 +631,19 @@ __global__ void __launch_bounds__(kThreads) k_compact_send(DevPlan p) {
                 const long long i = c.start + j + k;
                 const uint32_t gidx = (uint32_t)(t.goff + i);
                 if (staged) {
-                    st_idx[pos - pos_begin] = gidx;
+                    st_idx[pos - pos_begin] = gidx;           // (unused in values-only mode)
                     st_val[pos - pos_begin] = v[it][k];
                 } else if (p.direct_idx) {
                     p.direct_idx[cfg.pay_off + pos] = gidx;
                     p.direct_val[cfg.pay_off + pos] = v[it][k];
                 } else if (p.mc_region) {
                     char* s = mc_slot_ptr(p, p.rank);
-                    mm_st_u32(reinterpret_cast<uint32_t*>(s + p.idx_off) + cfg.pay_off + pos, gidx);
+                    if (!p.values_only) mm_st_u32(reinterpret_cast<uint32_t*>(s + p.idx_off) + cfg.pay_off + pos, gidx);
                     mm_st_f32(reinterpret_cast<float*>(s + p.val_off) + cfg.pay_off + pos, v[it][k]);
                 } else {
                     for (int d = 0; d < p.world; ++d) {
                         char* s = slot_ptr(p, d, p.rank);
-                        reinterpret_cast<uint32_t*>(s + p.idx_off)[cfg.pay_off + pos] = gidx;
+                        if (!p.values_only) reinterpret_cast<uint32_t*>(s + p.idx_off)[cfg.pay_off + pos] = gidx;
                         reinterpret_cast<float*>(s + p.val_off)[cfg.pay_off + pos] = v[it][k];
                     }
                 }
@@ -654,7 +657,7 @@ __global__ void __launch_bounds__(kThreads) k_compact_send(DevPlan p) {
         uint32_t* di = reinterpret_cast<uint32_t*>(s + p.idx_off) + cfg.pay_off + pos_begin;
         float* dv = reinterpret_cast<float*>(s + p.val_off) + cfg.pay_off + pos_begin;
         for (unsigned e = tid; e < n_out; e += kThreads) {
-            mm_st_u32(di + e, st_idx[e]);
+            if (!p.values_only) mm_st_u32(di + e, st_idx[e]);
             mm_st_f32(dv + e, st_val[e]);
         }
     } else if (n_out > 0 && staged) {
@@ -664,7 +667,7 @@ __global__ void __launch_bounds__(kThreads) k_compact_send(DevPlan p) {
             uint32_t* di = (p.direct_idx ? p.direct_idx : reinterpret_cast<uint32_t*>(s + p.idx_off)) + cfg.pay_off + pos_begin;
             float* dv = (p.direct_val ? p.direct_val : reinterpret_cast<float*>(s + p.val_off)) + cfg.pay_off + pos_begin;
             for (unsigned e = tid; e < n_out; e += kThreads) {
-                di[e] = st_idx[e];
+                if (!p.values_only) di[e] = st_idx[e];
                 dv[e] = st_val[e];
             }
         }
@@ -696,6 +699,94 @@ __device__ __forceinline__ void wait_sources(const DevPlan& p) {
         }
     }
     __syncthreads();
+}
+
+// ---- receiver, shared-seed Random-k (values only): every CTA owns one chunk of the dense output.  It recomputes which
+// of its elements were selected and at which payload position from the hash keys, the threshold and the chunk offsets of
+// this rank's OWN send of the same step (all ranks selected the same positions), then sums that position of every
+// source's value array.  No index ever crosses the link: 4 bytes per kept element instead of 8.
+template <typename OutT>
+__global__ void __launch_bounds__(kThreads) k_recv_values(DevPlan p) {
+    if (p.step_ptr) p.step = *p.step_ptr;
+    __shared__ unsigned sh_warp[kThreads / 32];
+    const ChunkRec c = p.chunks[blockIdx.x];
+    const TensorRec t = p.tensors[c.tensor];
+    const GroupCfg cfg = p.gcfg[t.group];
+    const GroupState& gs = p.gstate[t.group];
+    const unsigned T = group_threshold(p, gs);
+    const unsigned long long quota = group_quota(p, gs);
+    const unsigned long long cap = (unsigned long long)cfg.cap;
+    const uint64_t salt = group_salt(p, cfg.uid);
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const unsigned long long off = p.chunk_off[blockIdx.x];
+    const unsigned long long gt_off = off & 0xffffffffULL, eq_off = off >> 32;
+    constexpr int kWarps = kThreads / 32;
+    constexpr int kPerWarp = kChunk / kWarps;
+    constexpr int kIters = kPerWarp / 128;
+    unsigned fl[kIters], excl[kIters];
+    unsigned run_base = 0;
+#pragma unroll
+    for (int it = 0; it < kIters; ++it) {
+        const int j = warp * kPerWarp + it * 128 + lane * 4;
+        unsigned f = 0;
+        if (j < c.len) {
+#pragma unroll
+            for (int k = 0; k < 4; ++k) {
+                if (j + k >= c.len) continue;
+                const long long i = c.start + j + k;
+                const uint32_t key = make_key(p.method, 0.0f, t.rnd, i, t.goff + i, salt);
+                f |= (key > T) ? (1u << k) : (key == T ? (16u << k) : 0u);
+            }
+        }
+        fl[it] = f;
+        const unsigned mine = __popc(f & 0xfu) | (__popc(f >> 4) << 16);
+        const unsigned incl = warp_incl_scan(mine);
+        excl[it] = run_base + incl - mine;
+        run_base += __shfl_sync(0xffffffffu, incl, 31);
+    }
+    if (lane == 0) sh_warp[warp] = run_base;
+    wait_sources(p);                      // (contains the block barrier that publishes sh_warp)
+    unsigned wbase = 0;
+#pragma unroll
+    for (int w = 0; w < kWarps; ++w)
+        if (w < warp) wbase += sh_warp[w];
+    const float inv = 1.0f / (float)p.world;
+    OutT* o = reinterpret_cast<OutT*>(t.out) + c.start;
+    const bool ov = vec_ok(o);
+#pragma unroll
+    for (int it = 0; it < kIters; ++it) {
+        const int j = warp * kPerWarp + it * 128 + lane * 4;
+        if (j >= c.len) continue;
+        float v[4] = {0.0f, 0.0f, 0.0f, 0.0f};
+        unsigned run = wbase + excl[it];
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+            const bool is_gt = (fl[it] >> k) & 1u, is_eq = (fl[it] >> (4 + k)) & 1u;
+            if (!(is_gt || is_eq)) continue;
+            const unsigned long long g_before = gt_off + (run & 0xffffu);
+            const unsigned long long e_before = eq_off + (run >> 16);
+            const unsigned long long pos = g_before + (e_before < quota ? e_before : quota);
+            const bool keep = pos < cap && (is_gt || e_before < quota);
+            run += is_gt ? 1u : 0x10000u;
+            if (!keep) continue;
+            float a = 0.0f;
+            for (int src = 0; src < p.world; ++src)          // rank order: every replica sums in the same order
+                a += reinterpret_cast<const float*>(slot_ptr(p, p.rank, src) + p.val_off)[cfg.pay_off + pos];
+            v[k] = a * inv;
+        }
+        store_quad<OutT>(o, j, c.len, ov, v);
+    }
+    if (p.step_ptr) {      // the last CTA to finish advances the device-side step counter
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            const unsigned ticket = atomicAdd(&p.counters->done_recv, 1u);
+            if (ticket == gridDim.x - 1) {
+                p.counters->done_recv = 0;
+                __threadfence();
+                *p.step_ptr = p.step + 1;
+            }
+        }
+    }
 }
 
 // ---- receiver, sparse: every CTA owns one chunk of the dense output --------------------------------------
@@ -1119,8 +1210,18 @@ extern "C" int lwc_plan_bind_multicast(LwcPlan* P, void* mc_region_dev) {
     return 0;
 }
 
+// Shared-seed Random-k ships values only (4 bytes per kept element; indices are implied by the hash).  Call on every rank
+// alike, before the first send; injected random keys (lwc_plan_set_random) switch it off again.
+extern "C" int lwc_plan_set_values_only(LwcPlan* P, int enable) {
+    if (!P) return LWC_EINVAL;
+    if (enable && (P->dev.method != LWC_RANDOMK || P->dev.direct_idx)) return LWC_EINVAL;
+    P->dev.values_only = enable ? 1 : 0;
+    return 0;
+}
+
 extern "C" int lwc_plan_set_random(LwcPlan* P, const void* const* rand_dev) {
     if (!P) return LWC_EINVAL;
+    if (rand_dev) P->dev.values_only = 0;
     for (int t = 0; t < P->num_tensors; ++t) P->h_tensors[t].rnd = rand_dev ? rand_dev[t] : nullptr;
     LWC_CUDA_CHECK(cudaMemcpy(P->d_tensors, P->h_tensors.data(), sizeof(TensorRec) * P->h_tensors.size(),
                               cudaMemcpyHostToDevice));
@@ -1194,7 +1295,14 @@ extern "C" int lwc_plan_recv(LwcPlan* P, uint64_t step, void* stream_) {
     D.step_ptr = P->device_step ? &reinterpret_cast<Counters*>(P->d_counters)->dev_step : nullptr;
     D.timeout_ns = g_flag_timeout_ns;
     const int m = D.method;
-    if (m >= LWC_TOPK && m <= LWC_ADAPTIVE) {
+    if (m == LWC_RANDOMK && D.values_only) {
+        switch (P->out_dtype) {
+            case LWC_F32: k_recv_values<float><<<D.num_chunks, kThreads, 0, st>>>(D); break;
+            case LWC_BF16: k_recv_values<__nv_bfloat16><<<D.num_chunks, kThreads, 0, st>>>(D); break;
+            case LWC_F16: k_recv_values<__half><<<D.num_chunks, kThreads, 0, st>>>(D); break;
+            default: return LWC_EINVAL;
+        }
+    } else if (m >= LWC_TOPK && m <= LWC_ADAPTIVE) {
         switch (P->out_dtype) {
             case LWC_F32: k_recv_sparse<float><<<D.num_chunks, kThreads, 0, st>>>(D); break;
             case LWC_BF16: k_recv_sparse<__nv_bfloat16><<<D.num_chunks, kThreads, 0, st>>>(D); break;
@@ -1217,7 +1325,7 @@ extern "C" int lwc_plan_stats(LwcPlan* P, uint64_t out[4], void* stream_) {
     LWC_CUDA_CHECK(cudaStreamSynchronize(st));
     out[0] = c.sent; out[1] = c.dropped; out[2] = c.timeouts;
     const bool sparse = P->dev.method >= LWC_TOPK && P->dev.method <= LWC_ADAPTIVE;
-    out[3] = sparse ? c.sent * 8 : (uint64_t)(P->dev.slot_bytes - P->dev.hdr_bytes);
+    out[3] = sparse ? c.sent * (P->dev.values_only ? 4 : 8) : (uint64_t)(P->dev.slot_bytes - P->dev.hdr_bytes);
     return 0;
 }
 

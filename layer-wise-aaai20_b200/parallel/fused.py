@@ -90,7 +90,11 @@ class ExchangePlan:
         d.world, d.rank = world, rank
         d.qstates = int(cfg.qstates or 0) if self.method == cref.DITHERING else 0
         d.threshold = float(cfg.threshold or 0.0)
-        d.seed = int(cfg.seed) & 0xFFFFFFFFFFFFFFFF
+        shared = bool(getattr(cfg, "shared_seed", True))
+        # per-rank masks (the reference's CIFAR Random-k draws an independent randperm on every rank, core.py:186):
+        # mix the rank into the key; shared masks (sparsified DDP) keep one seed for all ranks
+        seed = int(cfg.seed) if shared else int(cfg.seed) + 0x9E3779B97F4A7C15 * (rank + 1)
+        d.seed = seed & 0xFFFFFFFFFFFFFFFF
         self._arrs = dict(
             grad=_ptr_array([g.data_ptr() for g in grads]),
             out=_ptr_array([o.data_ptr() for o in outs]),
@@ -107,6 +111,10 @@ class ExchangePlan:
         d.numel, d.group_of, d.uid, d.keep, d.cap = a["numel"], a["group_of"], a["uid"], a["keep"], a["cap"]
         self.handle = C.c_void_p()
         abi.check(self.lib.lwc_plan_create(C.byref(self.handle), C.byref(d)), "lwc_plan_create")
+        # shared-seed Random-k: values-only wire format (indices are implied by the hash, sparsified_ddp.py:410-412)
+        self.values_only = self.method == cref.RANDOMK and shared
+        if self.values_only:
+            abi.check(self.lib.lwc_plan_set_values_only(self.handle, 1), "lwc_plan_set_values_only")
         self.slot_bytes = int(self.lib.lwc_plan_slot_bytes(self.handle))
         self.region_bytes = int(self.lib.lwc_plan_region_bytes(self.handle))
         self.numel = sum(numel)

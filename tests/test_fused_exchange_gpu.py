@@ -332,3 +332,65 @@ def test_eight_virtual_ranks(method, kw):
             assert torch.allclose(e, o, atol=1e-6, rtol=1e-6)
     st = plans[0].stats()
     assert st["timeouts"] == 0 and st["dropped"] == 0
+
+
+@pytest.mark.parametrize("W", [1, 2, 4])
+@pytest.mark.parametrize("entire", [False, True])
+@pytest.mark.parametrize("ef", [False, True])
+def test_shared_seed_randomk_ships_values_only(W, entire, ef):
+    """Shared-seed Random-k: 4 bytes per kept element on the wire (no indices), zeros included, the receiver rebuilds
+    the positions from the hash (IMAGENET/training/sparsified_ddp.py:410-412).  Expected result: mean over ranks of
+    g_r * mask with the mask every rank derives for (seed, step, tensor)."""
+    cfg = CompressionConfig(compress="entiremodel" if entire else "layerwise", method="Randomk", ratio=0.02,
+                            error_feedback=ef, shared_seed=True)
+    sizes = [64, 8193, 100001]
+    grads, outs, resids, plans, lw = _world(W, sizes, cfg, entire, ef=ef)
+    assert all(p.values_only for p in plans)
+    for r in range(W):
+        grads[r][1][::3] = 0.0                      # exact zeros must travel too (positions are value-independent)
+    g0 = [[t.clone() for t in grads[r]] for r in range(W)]
+    for step in range(2):
+        # the mask of this step: a one-rank plan with all-ones gradients returns exactly the mask
+        ones = [torch.ones(n, device="cuda") for n in sizes]
+        mo = [torch.empty(n, device="cuda") for n in sizes]
+        from layerwise_b200.parallel.fused import ExchangePlan, bind_local_world
+        cfg1 = CompressionConfig(compress=cfg.compress, method="Randomk", ratio=0.02, shared_seed=True)
+        mp = ExchangePlan(ones, mo, None, cfg1, 1, 0, entire)
+        keep = bind_local_world([mp])
+        mp.send(step)
+        mp.recv(step)
+        _run(plans, step)
+        masks = [m != 0 for m in mo]
+        kept = sum(int(m.sum()) for m in masks)
+        for i, n in enumerate(sizes):
+            if not entire:
+                assert int(masks[i].sum()) == cr.randomk_keep_count(n, 0.02)
+            if ef and step == 1:
+                acc = [g0[r][i] + g0[r][i] * (~prev_masks[i]) for r in range(W)]     # residual of step 0 + new gradient
+            else:
+                acc = [g0[r][i] for r in range(W)]
+            exp = sum(a * masks[i] for a in acc) / W
+            for r in range(W):
+                assert torch.allclose(outs[r][i], exp, atol=1e-6, rtol=1e-6)
+                assert torch.equal(outs[r][i], outs[0][i])
+            if ef:
+                for r in range(W):
+                    assert torch.allclose(resids[r][i], acc[r] * (~masks[i]), atol=1e-6)
+        prev_masks = masks
+        st = plans[0].stats()
+        assert st["dropped"] == 0 and st["bytes"] == st["sent"] * 4
+        del keep
+
+
+def test_per_rank_seed_randomk_draws_different_masks_and_ships_indices():
+    cfg = CompressionConfig(compress="layerwise", method="Randomk", ratio=0.05, shared_seed=False)
+    grads, outs, _, plans, lw = _world(2, [50000], cfg, False)
+    assert not any(p.values_only for p in plans)
+    for r in range(2):
+        grads[r][0].fill_(1.0)
+    _run(plans, 0)
+    nz = int((outs[0][0] != 0).sum())
+    k = cr.randomk_keep_count(50000, 0.05)
+    assert k < nz <= 2 * k                      # two independent masks: union larger than one mask
+    assert torch.equal(outs[0][0], outs[1][0])
+    assert plans[0].stats()["bytes"] == plans[0].stats()["sent"] * 8
