@@ -178,6 +178,11 @@ typedef struct LwcSgdPlan LwcSgdPlan;
 int lwc_sgd_plan_create(LwcSgdPlan** out, const LwcSgdTensor* tensors_host, int32_t num_tensors);
 int lwc_sgd_plan_destroy(LwcSgdPlan* plan);
 int lwc_sgd_step(LwcSgdPlan* plan, const LwcSgdDesc* desc, void* stream);
+/* Peer-memory broadcast of a staging buffer from `root` into every rank's copy (NVLink peer stores + step flag;
+ * receivers wait with a bound).  Stands in for the coalesced NCCL broadcasts of the reference's DDP wrappers
+ * (IMAGENET/training/sparsified_ddp.py:199-203,:366-375; ddp.py:190-194,:373-377). */
+int lwc_peer_broadcast(void* const* buf_dev, void* const* flags_dev, void* ticket_dev, long long nbytes, long long cap,
+                       int world, int rank, int root, uint64_t step, void* stream);
 /* Fail-closed word of this device: set by receivers / the dense all-reduce when a peer's flag wait ran out (no
  * reference counterpart beyond the try/except of IMAGENET/training/train_imagenet_nv.py:704-716). */
 int lwc_poison_ptr(void** out_dev);

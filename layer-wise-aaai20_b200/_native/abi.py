@@ -127,6 +127,7 @@ def declare(lib: C.CDLL):
     sig("lwc_sgd_plan_create", C.c_int, c_void_pp, C.POINTER(LwcSgdTensor), i32)
     sig("lwc_sgd_plan_destroy", C.c_int, vp)
     sig("lwc_sgd_step", C.c_int, vp, C.POINTER(LwcSgdDesc), vp)
+    sig("lwc_peer_broadcast", C.c_int, c_void_pp, c_void_pp, vp, C.c_longlong, C.c_longlong, C.c_int, C.c_int, C.c_int, u64, vp)
     sig("lwc_poison_ptr", C.c_int, c_void_pp)
     sig("lwc_poison_read", C.c_int, C.POINTER(C.c_uint))
     sig("lwc_poison_clear", C.c_int)

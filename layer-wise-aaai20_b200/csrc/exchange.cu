@@ -1646,3 +1646,92 @@ extern "C" int lwc_plan_use_device_step(LwcPlan* P, int enable, uint64_t start_s
     P->device_step = enable != 0;
     return 0;
 }
+
+// =====================================================================================================
+// Peer-memory broadcast: rank `root` stores a staging buffer into every rank's copy over NVLink (plain peer stores,
+// 16 bytes per thread), the last CTA publishes a step flag; the other ranks run a one-CTA kernel that waits for it
+// (bounded spin -> poison word, never a hang).  Staging is double-buffered by step parity, so the root may be one
+// broadcast ahead of a receiver.  Replaces the coalesced NCCL broadcasts of the DDP wrappers: parameters + buffers at
+// wrap time and the batch-norm buffers before every training forward
+// (IMAGENET/training/sparsified_ddp.py:199-203,:366-375; ddp.py:190-194,:373-377).
+// =====================================================================================================
+namespace lwc {
+struct DevBcast {
+    char* buf[LWC_MAX_WORLD];           // per rank: staging [2][nbytes_cap]
+    uint64_t* flags[LWC_MAX_WORLD];     // per rank: LWC_MAX_WORLD words, index = root
+    unsigned int* ticket;               // local
+    long long nbytes, cap;
+    int world, rank, root;
+    unsigned long long step, timeout_ns;
+};
+
+__global__ void __launch_bounds__(512) k_bcast_push(DevBcast p) {
+    const size_t par = (size_t)(p.step & 1ULL) * (size_t)p.cap;
+    const uint4* src = reinterpret_cast<const uint4*>(p.buf[p.rank] + par);
+    const long long nvec = (p.nbytes + 15) / 16;
+    for (long long v = (long long)blockIdx.x * blockDim.x + threadIdx.x; v < nvec; v += (long long)gridDim.x * blockDim.x) {
+        const uint4 x = src[v];
+#pragma unroll
+        for (int d = 0; d < LWC_MAX_WORLD; ++d)
+            if (d < p.world && d != p.rank) reinterpret_cast<uint4*>(p.buf[d] + par)[v] = x;
+    }
+    __threadfence_system();
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        const unsigned t = atomicAdd(p.ticket, 1u);
+        if (t == gridDim.x - 1) {
+            __threadfence_system();
+            *p.ticket = 0;
+            for (int d = 0; d < p.world; ++d)
+                if (d != p.rank) st_release_sys(p.flags[d] + p.root, p.step + 1);
+        }
+    }
+}
+
+__global__ void k_bcast_wait(DevBcast p) {
+    if (threadIdx.x == 0) {
+        const uint64_t* f = p.flags[p.rank] + p.root;
+        const uint64_t want = p.step + 1;
+        const uint64_t t0 = global_timer_ns();
+        unsigned spins = 0;
+        while (ld_acquire_sys(f) < want) {
+            if ((++spins & 63u) == 0 && global_timer_ns() - t0 > p.timeout_ns) {
+                atomicExch(&g_lwc_poison, 1u);
+                break;
+            }
+            __nanosleep(64);
+        }
+    }
+}
+}  // namespace lwc
+
+// buf_dev[r] / flags_dev[r]: rank r's staging base (2 * cap bytes, cap a multiple of 16) and flag block
+// (LWC_MAX_WORLD uint64, zeroed) as seen from this rank; ticket_dev: one local uint32 (zeroed).  The root has filled
+// its own staging half (step & 1) before the call; on return (stream order) every other rank's half holds the same
+// nbytes.  `step` must advance by one per broadcast of this (buffers, root) pair.
+extern "C" int lwc_peer_broadcast(void* const* buf_dev, void* const* flags_dev, void* ticket_dev, long long nbytes, long long cap,
+                                  int world, int rank, int root, uint64_t step, void* stream) {
+    if (!buf_dev || !flags_dev || !ticket_dev || nbytes <= 0 || nbytes > cap || (cap & 15) || world < 1 || world > LWC_MAX_WORLD ||
+        rank < 0 || rank >= world || root < 0 || root >= world)
+        return LWC_EINVAL;
+    DevBcast p;
+    memset(&p, 0, sizeof(p));
+    for (int r = 0; r < world; ++r) {
+        if (!buf_dev[r] || !flags_dev[r]) return LWC_EINVAL;
+        p.buf[r] = (char*)buf_dev[r];
+        p.flags[r] = (uint64_t*)flags_dev[r];
+    }
+    p.ticket = (unsigned int*)ticket_dev;
+    p.nbytes = nbytes; p.cap = cap; p.world = world; p.rank = rank; p.root = root; p.step = step; p.timeout_ns = g_flag_timeout_ns;
+    cudaStream_t st = (cudaStream_t)stream;
+    if (world == 1) return 0;
+    if (rank == root) {
+        long long blocks = ((nbytes + 15) / 16 + 511) / 512;
+        if (blocks > 148) blocks = 148;
+        if (blocks < 1) blocks = 1;
+        k_bcast_push<<<(int)blocks, 512, 0, st>>>(p);
+    } else {
+        k_bcast_wait<<<1, 32, 0, st>>>(p);
+    }
+    return (int)cudaGetLastError();
+}

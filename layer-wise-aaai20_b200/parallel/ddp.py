@@ -45,11 +45,23 @@ class _DDPBase(nn.Module):
         self.broadcast_buffers = broadcast_buffers
         self.check_reduction = check_reduction
         self.broadcast_bucket_size = 250 << 20
-        states = [t for t in module.state_dict().values() if torch.is_tensor(t)]
-        comm.broadcast_coalesced(states, 0, process_group, self.broadcast_bucket_size)
+        self._buffer_bcast = None
+        self._buffer_bcast_tried = False
         params = [p for p in module.parameters() if p.requires_grad]
         on_gpu = bool(params) and params[0].is_cuda
         self.exchanger = GradientExchanger(params, cfg, group=process_group, engine=engine, overlap=on_gpu)
+        # every replica starts from rank 0's parameters and buffers (reference sparsified_ddp.py:199-203): through peer
+        # memory when the ranks share it, else one coalesced collective
+        states = [t for t in module.state_dict().values() if torch.is_tensor(t)]
+        if comm.world_size(process_group) > 1 and states:
+            init_bcast = self._peer_broadcaster(states)
+            if init_bcast is not None:
+                init_bcast.broadcast()
+                torch.cuda.synchronize()
+                comm.barrier(process_group)
+                init_bcast.close()
+            else:
+                comm.broadcast_coalesced(states, 0, process_group, self.broadcast_bucket_size)
         self._hook_driven = getattr(self.exchanger.engine, "overlap", False)
         self._awaiting_reduction = False
         if not self._hook_driven and params:
@@ -67,10 +79,40 @@ class _DDPBase(nn.Module):
             self.exchanger.exchange()
             self._awaiting_reduction = False
 
+    def _peer_broadcaster(self, tensors):
+        """A peer-memory broadcaster for ``tensors`` when the ranks share NVLink peer memory (CUDA tensors, fused / dense
+        engine, i.e. one node), else None (NCCL / gloo broadcast)."""
+        if not tensors or not all(t.is_cuda for t in tensors):
+            return None
+        if getattr(self.exchanger, "engine_name", "torch") not in ("fused", "dense"):
+            return None
+        bc = None
+        try:
+            from .peer import PeerBroadcaster
+            bc = PeerBroadcaster(tensors, self.process_group, root=0)
+        except Exception:           # no peer access between the ranks: keep the collective
+            bc = None
+        # all ranks must take the same path: one that could not map the heaps sends everybody to the collective
+        ok = comm.sum_tensor(torch.tensor([1.0 if bc is not None else 0.0], device=tensors[0].device), self.process_group)
+        if int(ok.item()) != comm.world_size(self.process_group):
+            if bc is not None:
+                bc.close()
+            return None
+        return bc
+
     def _sync_buffers(self):
+        """Batch-norm running statistics follow rank 0 before every training forward (reference ddp.py:373-377): one
+        ``lwc_peer_broadcast`` launch on the step path, no NCCL call."""
         if self.broadcast_buffers and comm.world_size(self.process_group) > 1:
             bufs = list(self.module.buffers())
-            if bufs:
+            if not bufs:
+                return
+            if self._buffer_bcast is None and not self._buffer_bcast_tried:
+                self._buffer_bcast_tried = True
+                self._buffer_bcast = self._peer_broadcaster(bufs)
+            if self._buffer_bcast is not None:
+                self._buffer_bcast.broadcast()
+            else:
                 comm.broadcast_coalesced(bufs, 0, self.process_group, self.broadcast_bucket_size)
 
     def forward(self, *inputs, **kwargs):

@@ -91,8 +91,15 @@ class PeerHeap:
         self.nbytes = int(nbytes)
         self.mc_ptr = 0          # NVLS multicast mapping of the heap (0 = not available / not requested)
         self._symm = None
-        if multicast and self.world > 1 and self._init_symmetric(device):
-            return
+        if multicast and self.world > 1:
+            ok = self._init_symmetric(device)
+            # every rank must end up on the same allocation path: one failure sends all of them to the cudaIpc heap
+            flag = torch.tensor([1 if ok else 0], device=torch.device("cuda", torch.cuda.current_device()))
+            dist.all_reduce(flag, op=dist.ReduceOp.MIN, group=group)
+            if int(flag.item()) == 1:
+                return
+            self._symm = None
+            self.mc_ptr = 0
         # whole 2 MiB pages: the heap gets driver blocks of its own (and maps with large pages on the peers)
         self.local = DeviceBuffer.allocate((self.nbytes + (2 << 20) - 1) // (2 << 20) * (2 << 20), device)
         self.ptrs: List[int] = [0] * self.world
@@ -162,3 +169,74 @@ class LocalWorld:
     def close(self):
         for h in self.heaps:
             h.free()
+
+
+class PeerBroadcaster:
+    """Broadcast a fixed set of CUDA tensors from one rank to all others through peer memory.
+
+    The tensors are packed into a staging area of the symmetric heap, the root's kernel stores the staging area into
+    every other rank's copy over NVLink and raises a step flag (``lwc_peer_broadcast`` in ``csrc/exchange.cu``), the
+    other ranks wait for the flag on the device and unpack.  No NCCL call, no host synchronisation; a receiver whose
+    root never shows up leaves its wait after the flag time-out and poisons the step.  Stands in for
+    ``dist._dist_broadcast_coalesced`` of the reference's DDP wrappers: parameters and buffers at wrap time and the
+    batch-norm buffers before every training forward (IMAGENET/training/sparsified_ddp.py:199-203,:366-375;
+    ddp.py:190-194,:373-377).
+    """
+
+    def __init__(self, tensors, group=None, root: int = 0, heap=None, world: Optional[int] = None, rank: Optional[int] = None):
+        self.tensors = [t for t in tensors]
+        self.root = root
+        self.sizes = [t.numel() * t.element_size() for t in self.tensors]
+        self.offsets, off = [], 0
+        for n in self.sizes:
+            self.offsets.append(off)
+            off += (n + 15) // 16 * 16
+        self.nbytes = max(off, 16)
+        self.cap = (self.nbytes + 255) // 256 * 256
+        flag_bytes = 256
+        if heap is None:
+            heap = PeerHeap(2 * self.cap + flag_bytes + 256, group)
+            self._own_heap = True
+        else:
+            self._own_heap = False
+        self.heap = heap
+        self.world = heap.world if world is None else world
+        self.rank = heap.rank if rank is None else rank
+        self.step = 0
+        lib = _native.lib()
+        self.lib = lib
+        self._buf = (C.c_void_p * self.world)(*[p for p in heap.ptrs])
+        self._flags = (C.c_void_p * self.world)(*[p + 2 * self.cap for p in heap.ptrs])
+        base = heap.ptrs[self.rank]
+        self._ticket = base + 2 * self.cap + flag_bytes
+        dev = self.tensors[0].device if self.tensors else torch.device("cuda", torch.cuda.current_device())
+        local = DeviceBuffer(base, 2 * self.cap, dev, owner=False)
+        local._keep = heap
+        self._stage = [local.view(torch.uint8, self.cap, 0), local.view(torch.uint8, self.cap, self.cap)]
+
+    def _views(self, parity):
+        st = self._stage[parity]
+        return [st[o:o + n] for o, n in zip(self.offsets, self.sizes)]
+
+    @torch.no_grad()
+    def broadcast(self, stream=None):
+        """One broadcast of the current tensor contents (stream-ordered)."""
+        if self.world == 1 or not self.tensors:
+            return
+        parity = self.step & 1
+        flat = [t.detach().reshape(-1).view(torch.uint8) for t in self.tensors]
+        views = self._views(parity)
+        if self.rank == self.root:
+            torch._foreach_copy_(views, flat)
+        st = (stream or torch.cuda.current_stream()).cuda_stream
+        abi.check(self.lib.lwc_peer_broadcast(self._buf, self._flags, C.c_void_p(self._ticket), self.nbytes, self.cap,
+                                              self.world, self.rank, self.root, C.c_uint64(self.step), C.c_void_p(st)),
+                  "lwc_peer_broadcast")
+        _native.counters.add(1)
+        if self.rank != self.root:
+            torch._foreach_copy_(flat, views)
+        self.step += 1
+
+    def close(self):
+        if self._own_heap:
+            self.heap.close()

@@ -394,3 +394,40 @@ def test_per_rank_seed_randomk_draws_different_masks_and_ships_indices():
     assert k < nz <= 2 * k                      # two independent masks: union larger than one mask
     assert torch.equal(outs[0][0], outs[1][0])
     assert plans[0].stats()["bytes"] == plans[0].stats()["sent"] * 8
+
+
+def test_peer_broadcast_virtual_ranks():
+    """lwc_peer_broadcast with W = 4 virtual ranks on one GPU: the root's tensors (mixed dtypes, odd sizes) arrive in every
+    other rank's tensors, twice in a row (both staging parities)."""
+    from layerwise_b200.parallel.peer import LocalWorld, PeerBroadcaster
+
+    class _Heap:
+        def __init__(self, ptrs, rank):
+            self.ptrs, self.world, self.rank = ptrs, len(ptrs), rank
+
+        def close(self):
+            pass
+
+    W = 4
+    shapes = [((64,), torch.float32), ((3, 5, 7), torch.float32), ((1,), torch.int64), ((1000, 33), torch.bfloat16), ((17,), torch.float16)]
+    ranks = [[(torch.randn(s, device="cuda") * (r + 1)).to(dt) if dt.is_floating_point else torch.full(s, r + 7, device="cuda", dtype=dt)
+              for s, dt in shapes] for r in range(W)]
+    nbytes = sum((t.numel() * t.element_size() + 15) // 16 * 16 for t in ranks[0])
+    cap = (nbytes + 255) // 256 * 256
+    lw = LocalWorld(W, 2 * cap + 512)
+    bcs = [PeerBroadcaster(ranks[r], heap=_Heap(lw.ptrs, r), root=1) for r in range(W)]
+    for rep in range(2):
+        want = [t.clone() for t in ranks[1]]
+        bcs[1].broadcast()                       # the root first: nothing waits on an unlaunched kernel
+        for r in (0, 2, 3):
+            bcs[r].broadcast()
+        torch.cuda.synchronize()
+        for r in range(W):
+            for a, b in zip(ranks[r], want):
+                assert torch.equal(a, b)
+        for t in ranks[1]:
+            if t.dtype.is_floating_point:
+                t.mul_(-0.5)
+            else:
+                t.add_(1)
+    lw.close()
