@@ -59,6 +59,20 @@ def main():
                     dist.all_reduce(e)
                     e /= world
                 good = all(torch.allclose(a, b, atol=1e-6, rtol=1e-5) for a, b in zip(exp, got))
+            elif method == "Randomk":
+                # shared seed: values-only wire format; every rank selected the same positions, so the result is the
+                # rank average of g * mask with exactly ceil(n K) survivors per selection group
+                good = True
+                for lg, gt in zip(local_g, got):
+                    mask = gt != 0
+                    e = lg * mask
+                    dist.all_reduce(e)
+                    e /= world
+                    good = good and torch.allclose(e, gt, atol=1e-6, rtol=1e-5)
+                kept = sum(int((t != 0).sum()) for t in got)
+                want = (sum(cr.randomk_keep_count(n, cfg.ratio) for n in sizes) if compress == "layerwise"
+                        else cr.randomk_keep_count(sum(sizes), cfg.ratio))
+                good = good and abs(kept - want) <= 2        # an exact-zero average is possible but vanishingly rare
             else:
                 good = all(torch.isfinite(t).all().item() for t in got)
             # replicas must agree bit for bit
@@ -104,6 +118,65 @@ def main():
     dist.barrier(device_ids=[local])
     for h in heaps:
         h.close()
+    # peer-memory broadcast (N5 / N6) and the DDP wrappers that use it: batch-norm buffers must follow rank 0, the
+    # replicas must stay bit-identical
+    from layerwise_b200.parallel.ddp import DistributedDataParallel, RandomKSparsifiedDDP
+    from layerwise_b200.parallel.peer import PeerBroadcaster
+    ts = [torch.full((1000, 33), float(rank + 1), device="cuda"), torch.full((7,), rank + 3, device="cuda", dtype=torch.int64)]
+    bc = PeerBroadcaster(ts, root=0)
+    good = True
+    for rep in range(3):
+        bc.broadcast()
+        torch.cuda.synchronize()
+        good = good and bool((ts[0] == 1.0 + rep).all().item()) and bool((ts[1] == 3 + rep).all().item())
+        dist.barrier(device_ids=[local])
+        if rank == 0:
+            ts[0] += 1
+            ts[1] += 1
+    bc.close()
+    flag = torch.tensor([1.0 if good else 0.0], device="cuda")
+    dist.all_reduce(flag, op=dist.ReduceOp.MIN)
+    results["peer_broadcast"] = {"ok": bool(flag.item())}
+    ok = ok and bool(flag.item())
+    for wname, mk in (("ddp_dense", lambda m: DistributedDataParallel(m, device_ids=[local])),
+                      ("ddp_randk", lambda m: RandomKSparsifiedDDP(m, device_ids=[local], randk=0.1))):
+        torch.manual_seed(100 + rank)               # different initial weights: the wrapper must align them with rank 0
+        net = torch.nn.Sequential(torch.nn.Conv2d(3, 16, 3, padding=1), torch.nn.BatchNorm2d(16), torch.nn.ReLU(),
+                                  torch.nn.Flatten(), torch.nn.Linear(16 * 8 * 8, 10)).cuda()
+        w = mk(net)
+        opt = torch.optim.SGD(net.parameters(), lr=0.05)
+        used_peer = None
+        for it in range(3):
+            x = torch.randn(8, 3, 8, 8, device="cuda", generator=g)
+            loss = w(x).square().mean()
+            loss.backward()
+            w.finish_reduction()
+            opt.step()
+            opt.zero_grad()
+            used_peer = w._buffer_bcast is not None
+        torch.cuda.synchronize()
+        good = True
+        for t in list(net.state_dict().values()):
+            ref = t.clone()
+            dist.broadcast(ref, 0)
+            if "running" in str(t.dtype) or t.dtype.is_floating_point:
+                # running statistics are re-synchronised at the NEXT forward; parameters must already agree
+                pass
+        for p_ in net.parameters():
+            ref = p_.detach().clone()
+            dist.broadcast(ref, 0)
+            good = good and torch.equal(ref, p_.detach())
+        w._sync_buffers()
+        torch.cuda.synchronize()
+        for b_ in net.buffers():
+            ref = b_.clone()
+            dist.broadcast(ref, 0)
+            good = good and torch.equal(ref, b_)
+        flag = torch.tensor([1.0 if good else 0.0], device="cuda")
+        dist.all_reduce(flag, op=dist.ReduceOp.MIN)
+        results[wname] = {"ok": bool(flag.item()), "peer_broadcast_used": bool(used_peer), "engine": w.exchanger.engine_name}
+        ok = ok and bool(flag.item())
+        w.exchanger.engine.close() if hasattr(w.exchanger.engine, "close") else None
     if rank == 0:
         print(json.dumps({"world": world, "ok": ok, "numel": sum(sizes), "results": results}, indent=1))
     dist.destroy_process_group()
