@@ -35,6 +35,9 @@ class AlexNet(nn.Module):
             lnn.Dropout(dropout), lnn.Linear(4096, 4096), lnn.ReLU(True),
             lnn.Linear(4096, num_classes),
         )
+        for i in (1, 4):                 # bias + ReLU in the GEMM epilogue; the ReLU nodes stay for the module names
+            self.classifier[i].fuse_relu = True
+            self.classifier[i + 1].already_applied = True
         self.criterion = lnn.CrossEntropyLoss(reduction="none")
         self.correct = Correct()
 

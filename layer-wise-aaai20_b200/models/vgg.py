@@ -54,6 +54,9 @@ class VGG(nn.Module):
             lnn.Linear(4096, 4096), lnn.ReLU(True), lnn.Dropout(dropout),
             lnn.Linear(4096, num_classes),
         )
+        for i in (0, 3):                 # bias + ReLU in the GEMM epilogue; the ReLU nodes stay for the module names
+            self.classifier[i].fuse_relu = True
+            self.classifier[i + 1].already_applied = True
         self.criterion = lnn.CrossEntropyLoss(reduction="none")
         self.correct = Correct()
         if init_weights:

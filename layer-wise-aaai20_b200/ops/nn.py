@@ -52,7 +52,8 @@ class Linear(nn.Linear):
             y = _gemm.maybe_linear(self, x)
             if y is not None:
                 return y
-        return super().forward(x)
+        y = super().forward(x)
+        return F.relu(y) if getattr(self, "fuse_relu", False) else y
 
 
 class BatchNorm2d(nn.BatchNorm2d):
