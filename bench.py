@@ -393,7 +393,8 @@ def main():
         step_e2e = lambda i: tr.train_step(host_x[i % nbuf], host_y[i % nbuf])[1]   # noqa: E731
         dtype, par = "bf16", f"dp{world}"
 
-    for i in range(args.warmup):
+    # (the CIFAR step captures its CUDA graph at its 4th call of a shape: keep the capture out of the timed region)
+    for i in range(args.warmup + (4 if (cifar and args.impl == "ours" and args.graph) else 0)):
         step_dev(i)
     torch.cuda.synchronize()
     if args.impl == "ours":
