@@ -132,9 +132,21 @@ struct DevPlan {     // passed by value to kernels
     long long* direct_count;
 };
 
+// Per-rank pointer tables live in the kernel parameter block.  Indexing them with a run-time rank makes the compiler copy
+// the whole block to local memory (k_compact_send had 1047 local loads); a compare chain over constant indices keeps the
+// reads in the constant bank.
+template <typename T>
+__device__ __forceinline__ T pick_rank(T const (&tab)[LWC_MAX_WORLD], int r) {
+    T x = tab[0];
+#pragma unroll
+    for (int i = 1; i < LWC_MAX_WORLD; ++i)
+        if (r == i) x = tab[i];
+    return x;
+}
+
 __device__ __forceinline__ char* slot_ptr(const DevPlan& p, int dst, int src) {
     const unsigned long long parity = p.step & 1ULL;
-    return p.region[dst] + (parity * p.world + src) * p.slot_bytes;
+    return pick_rank(p.region, dst) + (parity * p.world + src) * p.slot_bytes;
 }
 
 __device__ __forceinline__ char* mc_slot_ptr(const DevPlan& p, int src) {
@@ -530,7 +542,7 @@ __device__ __forceinline__ void publish_when_last(const DevPlan& p) {
         if (ticket == gridDim.x - 1) {
             __threadfence_system();
             p.counters->done = 0;
-            for (int d = 0; d < p.world; ++d) st_release_sys(p.flags[d] + p.rank, p.step + 1);
+            for (int d = 0; d < p.world; ++d) st_release_sys(pick_rank(p.flags, d) + p.rank, p.step + 1);
         }
     }
 }
@@ -685,7 +697,7 @@ __device__ unsigned int g_lwc_poison = 0;
 // ---- wait for every source's flag (bounded spin) -------------------------------------------------------
 __device__ __forceinline__ void wait_sources(const DevPlan& p) {
     if (threadIdx.x < p.world && (int)threadIdx.x != p.rank) {
-        const uint64_t* f = p.flags[p.rank] + threadIdx.x;
+        const uint64_t* f = pick_rank(p.flags, p.rank) + threadIdx.x;
         const uint64_t want = p.step + 1;
         const uint64_t t0 = global_timer_ns();
         unsigned spins = 0;
@@ -1495,7 +1507,7 @@ struct DevAR {
 
 __device__ __forceinline__ void ar_wait(const DevAR& p, int row) {
     if (threadIdx.x < p.world && (int)threadIdx.x != p.rank) {
-        const uint64_t* f = p.flags[p.rank] + row * LWC_MAX_WORLD + threadIdx.x;
+        const uint64_t* f = pick_rank(p.flags, p.rank) + row * LWC_MAX_WORLD + threadIdx.x;
         const uint64_t want = p.step + 1;
         const uint64_t t0 = global_timer_ns();
         unsigned spins = 0;
@@ -1515,7 +1527,7 @@ template <typename T>
 __global__ void __launch_bounds__(512) k_allreduce_two_shot(DevAR p) {
     constexpr int V = 16 / sizeof(T);         // elements per 16-byte vector
     if (blockIdx.x == 0 && threadIdx.x < p.world)
-        st_release_sys(p.flags[threadIdx.x] + 0 * LWC_MAX_WORLD + p.rank, p.step + 1);     // READY
+        st_release_sys(pick_rank(p.flags, (int)threadIdx.x) + 0 * LWC_MAX_WORLD + p.rank, p.step + 1);     // READY
     ar_wait(p, 0);
     // slice of this rank, in vectors
     const long long nvec = (p.n + V - 1) / V;                 // arena padding makes the tail vector addressable
@@ -1553,7 +1565,7 @@ __global__ void __launch_bounds__(512) k_allreduce_two_shot(DevAR p) {
         if (ticket == gridDim.x - 1) {
             __threadfence_system();
             p.counters[0] = 0;
-            for (int d = 0; d < p.world; ++d) st_release_sys(p.flags[d] + 1 * LWC_MAX_WORLD + p.rank, p.step + 1);   // DONE
+            for (int d = 0; d < p.world; ++d) st_release_sys(pick_rank(p.flags, d) + 1 * LWC_MAX_WORLD + p.rank, p.step + 1);   // DONE
         }
     }
 }
@@ -1667,7 +1679,7 @@ struct DevBcast {
 
 __global__ void __launch_bounds__(512) k_bcast_push(DevBcast p) {
     const size_t par = (size_t)(p.step & 1ULL) * (size_t)p.cap;
-    const uint4* src = reinterpret_cast<const uint4*>(p.buf[p.rank] + par);
+    const uint4* src = reinterpret_cast<const uint4*>(pick_rank(p.buf, p.rank) + par);
     const long long nvec = (p.nbytes + 15) / 16;
     for (long long v = (long long)blockIdx.x * blockDim.x + threadIdx.x; v < nvec; v += (long long)gridDim.x * blockDim.x) {
         const uint4 x = src[v];
@@ -1683,14 +1695,14 @@ __global__ void __launch_bounds__(512) k_bcast_push(DevBcast p) {
             __threadfence_system();
             *p.ticket = 0;
             for (int d = 0; d < p.world; ++d)
-                if (d != p.rank) st_release_sys(p.flags[d] + p.root, p.step + 1);
+                if (d != p.rank) st_release_sys(pick_rank(p.flags, d) + p.root, p.step + 1);
         }
     }
 }
 
 __global__ void k_bcast_wait(DevBcast p) {
     if (threadIdx.x == 0) {
-        const uint64_t* f = p.flags[p.rank] + p.root;
+        const uint64_t* f = pick_rank(p.flags, p.rank) + p.root;
         const uint64_t want = p.step + 1;
         const uint64_t t0 = global_timer_ns();
         unsigned spins = 0;
