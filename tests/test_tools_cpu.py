@@ -77,3 +77,19 @@ def test_launch_tensorboard_dry_run(tmp_path, capsys):
     cmd = tb.main([str(tmp_path), "--port", "6123", "--dry-run"])
     assert "--logdir" in cmd and str(tmp_path) in cmd and "6123" in cmd
     assert "Tensorboard at http://" in capsys.readouterr().out
+
+
+def test_batch_norm_studies_smoke():
+    """Script counterparts of the reference's batch-norm notebook run end to end on CPU (tiny settings)."""
+    import importlib.util
+    import os
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    spec = importlib.util.spec_from_file_location("bn_studies", os.path.join(root, "examples", "batch_norm_studies.py"))
+    mod = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(mod)
+    res = mod.main(["all", "--steps", "4", "--samples", "256", "--width", "8", "--lanczos", "5", "--device", "cpu"])
+    assert set(res) == {"lr-stress", "channel-stats", "hessian", "lars"}
+    assert len(res["lr-stress"]) == 7 and all(len(r) == 3 for r in res["lr-stress"])
+    ev_bn, ev_plain = res["hessian"][True], res["hessian"][False]
+    assert len(ev_bn) == 3 and ev_bn[0] >= ev_bn[1] >= ev_bn[2] and len(ev_plain) == 3
+    assert all(len(v) == 4 for v in res["lars"].values())
