@@ -287,6 +287,15 @@ int lwc_convx_stem_forward(const void* xs, const void* w4, void* y, int N, int O
 size_t lwc_convx_wgrad_workspace_bytes(int N, int H, int W, int Cx, int Cout, int k, int stride, int pad, int bn_hint);
 int lwc_convx_wgrad(const void* x, const void* dy, void* dw, float* workspace, int N, int H, int W, int Cx, int Cout,
                     int Cin_out, int k, int stride, int pad, int out_dtype, float scale, int bn_hint, void* stream);
+/* Stride-1 data gradient that also produces the batch-norm BACKWARD reduction sums of the layer whose output it
+ * differentiates (per-CTA partials of sum d and sum d * x), and the batch-norm backward that consumes them
+ * (IMAGENET/training/resnet.py:72-92: conv -> bn -> relu -> conv chains). */
+int lwc_convx_dgrad_bnstats(const void* dy, const void* wt, void* dx, int N, int H, int W, int Cin, int Cout, int k, int pad,
+                            const void* x_bn, const float* gamma, const float* beta, const float* mean, const float* invstd,
+                            int relu, float* partials, int* nparts_out, int bn_hint, void* stream);
+int lwc_bn_backward_from_partials(const void* dy, const void* x, void* dx, const float* gamma, const float* beta,
+                                  const float* mean, const float* invstd, float* dgamma, float* dbeta,
+                                  const float* partials, int nparts, long long M, int C, int dtype, int relu, void* stream);
 /* Batch-norm mean / inverse std (+ running statistics, + num_batches_tracked) from those partials, and the
  * apply-only batch-norm pass that consumes them (IMAGENET/training/resnet.py:72-92 conv -> bn -> relu chains). */
 int lwc_convx_stats_finalize(const float* partials, int nparts, int C, long long count, float eps, float momentum,

@@ -655,3 +655,49 @@ extern "C" int lwc_bn_apply_stats(const void* x, void* y, const void* res, const
     LWC_BN_DISPATCH(dtype, k_bn_apply<T><<<grid, THREADS, 0, st>>>(p, 0));
     return (int)cudaGetLastError();
 }
+
+// Batch-norm backward whose reduction sums were produced elsewhere (the data-gradient epilogue of the consuming
+// convolution, lwc_convx_dgrad_bnstats): partials [nparts][2][C] = per-CTA (sum d, sum d * x).  Sums them in a fixed
+// order (double), writes dbeta / dgamma and runs the apply pass.
+namespace lwc { namespace bn {
+__global__ void __launch_bounds__(256) k_bn_bwd_finalize_partials(const float* __restrict__ part, int nparts, int C,
+                                                                  const float* __restrict__ mean, const float* __restrict__ invstd,
+                                                                  float* __restrict__ dgamma, float* __restrict__ dbeta) {
+    const int c = blockIdx.x * 8 + (threadIdx.x >> 5), lane = threadIdx.x & 31;
+    if (c >= C) return;
+    double s = 0.0, q = 0.0;
+    for (int b = lane; b < nparts; b += 32) {
+        s += (double)part[(size_t)b * 2 * C + c];
+        q += (double)part[(size_t)b * 2 * C + C + c];
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        s += __shfl_xor_sync(0xffffffffu, s, o);
+        q += __shfl_xor_sync(0xffffffffu, q, o);
+    }
+    if (lane == 0) {
+        dbeta[c] = (float)s;
+        dgamma[c] = invstd[c] * (float)(q - (double)mean[c] * s);
+    }
+}
+} }
+
+extern "C" int lwc_bn_backward_from_partials(const void* dy, const void* x, void* dx, const float* gamma, const float* beta,
+                                             const float* mean, const float* invstd, float* dgamma, float* dbeta,
+                                             const float* partials, int nparts, long long M, int C, int dtype, int relu,
+                                             void* stream) {
+    if (!dy || !x || !dx || !mean || !invstd || !dgamma || !dbeta || !partials || nparts <= 0) return LWC_EINVAL;
+    if (M <= 0 || C <= 0 || (C % VEC)) return LWC_EINVAL;
+    cudaStream_t st = (cudaStream_t)stream;
+    k_bn_bwd_finalize_partials<<<(C + 7) / 8, 256, 0, st>>>(partials, nparts, C, mean, invstd, dgamma, dbeta);
+    Params p;
+    memset(&p, 0, sizeof(p));
+    p.x = x; p.dy = dy; p.dx = dx; p.gamma = gamma; p.beta = beta;
+    p.mean = const_cast<float*>(mean); p.invstd = const_cast<float*>(invstd);
+    p.dgamma = dgamma; p.dbeta = dbeta;
+    p.M = M; p.C = C; p.relu = relu;
+    dim3 grid;
+    plan_grid(M, C, &p.nblk, &p.rows_per_blk, &grid);
+    LWC_BN_DISPATCH(dtype, k_bn_bwd_apply<T><<<grid, THREADS, 0, st>>>(p));
+    return (int)cudaGetLastError();
+}

@@ -65,6 +65,11 @@ struct FxParams {
     int c_off, stat_off, bar_off;            // shared-memory offsets
     const float* bias;
     float* stats;                            // [gridDim.x][2][N] per-CTA sums / sums of squares, or NULL
+    // batch-norm BACKWARD sums instead (data-gradient launches whose output dz is the gradient of a batch-norm + ReLU
+    // output): the matching tile of the batch norm's input x is TMA-prefetched next to the staged dz tile and the
+    // epilogue accumulates S1 = sum d, S2 = sum d * x with d = dz * [gamma * invstd * (x - mean) + beta > 0]
+    int bnb, bnb_relu, x_off;
+    const float *bn_gamma, *bn_beta, *bn_mean, *bn_invstd;
     short dw[MAXT], dh[MAXT];
     int a_c0[MAXT], b_k0[MAXT], b_n0[MAXT];   // b_n0: column offset of the tap in an MN-major weight matrix
 };
@@ -83,7 +88,8 @@ __device__ __forceinline__ TileCoord tile_coord(const FxParams& p, int tile) {
 
 template <int BN, bool B_MN>
 __global__ void __launch_bounds__(THREADS, 1) k_fx(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
-                                                   const __grid_constant__ CUtensorMap tmC, const FxParams p) {
+                                                   const __grid_constant__ CUtensorMap tmC, const __grid_constant__ CUtensorMap tmX,
+                                                   const FxParams p) {
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
     constexpr int A_BYTES = BM * BK * 2;
@@ -94,7 +100,8 @@ __global__ void __launch_bounds__(THREADS, 1) k_fx(const __grid_constant__ CUten
     uint64_t* empty = full + MAXS;
     uint64_t* tmem_full = empty + MAXS;        // [2]
     uint64_t* tmem_empty = tmem_full + 2;      // [2]
-    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_empty + 2);
+    uint64_t* xfull = tmem_empty + 2;          // [4] x tile of a chunk has landed (batch-norm backward sums)
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(xfull + 4);
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int num_tiles = p.tiles_m * p.tiles_n;
@@ -106,6 +113,8 @@ __global__ void __launch_bounds__(THREADS, 1) k_fx(const __grid_constant__ CUten
         prefetch_tensormap(&tmA); prefetch_tensormap(&tmB); prefetch_tensormap(&tmC);
         for (int s = 0; s < stages; ++s) { mbar_init(&full[s], 1); mbar_init(&empty[s], 1); }
         for (int a = 0; a < 2; ++a) { mbar_init(&tmem_full[a], 1); mbar_init(&tmem_empty[a], 8); }
+        for (int a = 0; a < 4; ++a) mbar_init(&xfull[a], 1);
+        if (p.bnb) prefetch_tensormap(&tmX);
         fence_barrier_init();
     }
     if (warp == 1) tmem_alloc<2 * BN>(tmem_slot);
@@ -172,6 +181,19 @@ __global__ void __launch_bounds__(THREADS, 1) k_fx(const __grid_constant__ CUten
         const int r_w = r % p.Wb, r_h = (r / p.Wb) % p.Hb, r_n = r / (p.Wb * p.Hb);
         const bool slow = p.bias != nullptr || p.relu != 0;
         constexpr int NCH = BN / 64;
+        // x-tile prefetch (batch-norm backward sums): the leader keeps the loads two chunks ahead of the epilogue
+        int pf_tile = blockIdx.x, pf_h = 0;
+        uint32_t pf_q = 0, q_cnt = 0;
+        auto prefetch_x = [&]() {
+            if (pf_tile >= num_tiles) return;
+            const TileCoord tt = tile_coord(p, pf_tile);
+            const uint32_t slot = pf_q % (uint32_t)p.ncs;
+            mbar_expect_tx(&xfull[slot], a_bytes);
+            tma_load_4d(smem + p.x_off + slot * SUB_BYTES, &tmX, &xfull[slot], tt.nt * BN + pf_h * 64, tt.w0, tt.h0, tt.n0);
+            ++pf_q;
+            if (++pf_h == NCH) { pf_h = 0; pf_tile += gridDim.x; }
+        };
+        if (p.bnb && leader) { prefetch_x(); prefetch_x(); }
         float sacc[NCH][16];                           // [chunk][sum x 8 channels | sum of squares x 8 channels]
 #pragma unroll
         for (int h = 0; h < NCH; ++h)
@@ -207,6 +229,7 @@ __global__ void __launch_bounds__(THREADS, 1) k_fx(const __grid_constant__ CUten
                     if (lane == 0) mbar_arrive(&tmem_empty[as]);
                 }
                 epi_bar_sync_n<256>();                         // staging buffer free (leader waited above)
+                if (p.bnb && leader) prefetch_x();      // chunk q + 2: its slot was last read two chunks ago
                 use_after_wait(v);
                 if (slow) {
 #pragma unroll
@@ -238,7 +261,43 @@ __global__ void __launch_bounds__(THREADS, 1) k_fx(const __grid_constant__ CUten
                     if (co0 + h * 64 < p.N) tma_store_4d(&tmC, cst, co0 + h * 64, t.w0, t.h0, t.n0);
                     tma_commit_group();                 // one group per chunk keeps the count in step with the ring
                 }
-                if (p.stats) {
+                if (p.bnb) {
+                    // batch-norm backward sums over this chunk: dz from the staging tile, x from the prefetched tile
+                    const uint32_t slot = q_cnt % (uint32_t)p.ncs;
+                    mbar_wait(&xfull[slot], (q_cnt / (uint32_t)p.ncs) & 1u);
+                    const uint8_t* xs = smem + p.x_off + slot * SUB_BYTES;
+                    const int c = et & 7, rg = et >> 3;
+                    float fa[8], fb[8];
+                    {
+                        const int ch0 = co0 + h * 64 + c * 8;
+#pragma unroll
+                        for (int k = 0; k < 8; ++k) {
+                            const int ch = ch0 + k < p.N ? ch0 + k : p.N - 1;
+                            fa[k] = (p.bn_gamma ? __ldg(p.bn_gamma + ch) : 1.0f) * __ldg(p.bn_invstd + ch);
+                            fb[k] = (p.bn_beta ? __ldg(p.bn_beta + ch) : 0.0f) - __ldg(p.bn_mean + ch) * fa[k];
+                        }
+                    }
+#pragma unroll
+                    for (int i = 0; i < 4; ++i) {
+                        const int row = rg * 4 + i;
+                        const int off = row * 128 + ((c ^ (row & 7)) * 16);
+                        const uint4 ud = *reinterpret_cast<const uint4*>(cst + off);
+                        const uint4 ux = *reinterpret_cast<const uint4*>(xs + off);
+                        const uint32_t dw4[4] = {ud.x, ud.y, ud.z, ud.w}, xw4[4] = {ux.x, ux.y, ux.z, ux.w};
+#pragma unroll
+                        for (int e = 0; e < 4; ++e) {
+                            float d0 = __uint_as_float(dw4[e] << 16), d1 = __uint_as_float(dw4[e] & 0xffff0000u);
+                            const float x0 = __uint_as_float(xw4[e] << 16), x1 = __uint_as_float(xw4[e] & 0xffff0000u);
+                            if (p.bnb_relu) {
+                                if (!(fmaf(x0, fa[2 * e], fb[2 * e]) > 0.0f)) d0 = 0.0f;
+                                if (!(fmaf(x1, fa[2 * e + 1], fb[2 * e + 1]) > 0.0f)) d1 = 0.0f;
+                            }
+                            sacc[h][2 * e] += d0; sacc[h][8 + 2 * e] = fmaf(d0, x0, sacc[h][8 + 2 * e]);
+                            sacc[h][2 * e + 1] += d1; sacc[h][8 + 2 * e + 1] = fmaf(d1, x1, sacc[h][8 + 2 * e + 1]);
+                        }
+                    }
+                    ++q_cnt;
+                } else if (p.stats) {
                     // column sums of the rounded 128 x 64 sub-tile, kept in registers for the whole kernel: thread =
                     // (group of 4 rows, 16-byte chunk of 8 channels); the host sizes the grid so that a CTA always
                     // works on the same BN output channels, i.e. chunk h means the same channels in every tile
@@ -638,16 +697,19 @@ struct FxGeom {
     int ntaps, kchunks;
     short dw[MAXT], dh[MAXT]; int a_c0[MAXT], b_k0[MAXT], b_n0[MAXT];
     const float* bias; int relu; float* stats; int bn_hint;
+    // batch-norm backward sums (see FxParams::bnb): x = the batch norm's input, same shape and layout as the output
+    const void* bnx; const float *bn_gamma, *bn_beta, *bn_mean, *bn_invstd; int bnb_relu;
 };
 
 template <int BN, bool B_MN>
-int launch_fx(const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMap& tc_, const FxParams& p, int smem, int grid, cudaStream_t st) {
+int launch_fx(const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMap& tc_, const CUtensorMap& tx, const FxParams& p, int smem,
+              int grid, cudaStream_t st) {
     static bool attr = false;
     if (!attr) {
         LWC_CUDA_CHECK(cudaFuncSetAttribute(k_fx<BN, B_MN>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BUDGET));
         attr = true;
     }
-    k_fx<BN, B_MN><<<grid, THREADS, smem, st>>>(ta, tb, tc_, p);
+    k_fx<BN, B_MN><<<grid, THREADS, smem, st>>>(ta, tb, tc_, tx, p);
     return 0;
 }
 
@@ -661,7 +723,9 @@ int pick_bn(int Cout, int hint) {
 int run_fx(const FxGeom& g, cudaStream_t st, int* grid_out) {
     if (g.Cout % 64 || g.ntaps < 1 || g.ntaps > MAXT || g.kchunks < 1) return LWC_EINVAL;
     ensure_context();
-    const int BN = pick_bn(g.Cout, g.bn_hint);
+    int BN = pick_bn(g.Cout, g.bn_hint);
+    if (g.bnx && BN == 256) BN = 128;        // the x-tile ring takes the shared memory of one 256-wide operand stage
+    if (g.bnx && !g.stats) return LWC_EINVAL;
     FxParams p;
     memset(&p, 0, sizeof(p));
     const Patch pt = pick_patch(g.OW, g.OH, g.ON, BM, 1, 256 / g.stride);
@@ -675,15 +739,22 @@ int run_fx(const FxGeom& g, cudaStream_t st, int* grid_out) {
     const int stage_bytes = BM * BK * 2 + BN * BK * 2;
     const int stat_bytes = 0;       // statistics live in registers; their final reduction reuses the staging ring
     int ncs = 4;
+    const int rings = g.bnx ? 2 : 1;         // staging ring (+ x-tile ring of the same depth)
     const int fixed = 1024 + 256 + stat_bytes;
-    int stages = (SMEM_BUDGET - fixed - ncs * SUB_BYTES) / stage_bytes;
-    if (stages < 3) { ncs = 2; stages = (SMEM_BUDGET - fixed - ncs * SUB_BYTES) / stage_bytes; }
+    int stages = (SMEM_BUDGET - fixed - rings * ncs * SUB_BYTES) / stage_bytes;
+    if (stages < 3) {
+        ncs = g.bnx ? 3 : 2;                 // the x prefetch runs two chunks ahead: it needs >= 3 slots
+        stages = (SMEM_BUDGET - fixed - rings * ncs * SUB_BYTES) / stage_bytes;
+    }
     if (stages > 8) stages = 8;
     if (stages < 2) return LWC_ETOOBIG;
     p.stages = stages; p.ncs = ncs;
     p.c_off = stages * stage_bytes;
-    p.stat_off = p.c_off + ncs * SUB_BYTES;
+    p.x_off = p.c_off + ncs * SUB_BYTES;
+    p.stat_off = p.x_off + (g.bnx ? ncs * SUB_BYTES : 0);
     p.bar_off = p.stat_off + stat_bytes;
+    p.bnb = g.bnx ? 1 : 0; p.bnb_relu = g.bnb_relu;
+    p.bn_gamma = g.bn_gamma; p.bn_beta = g.bn_beta; p.bn_mean = g.bn_mean; p.bn_invstd = g.bn_invstd;
     const int smem = p.bar_off + 256 + 1024;
 
     CUtensorMap ta, tb, tc_;
@@ -716,15 +787,24 @@ int run_fx(const FxGeom& g, cudaStream_t st, int* grid_out) {
         rc = encode(&tc_, g.y, 4, cd, cs, cb, nullptr);
         if (rc) return rc;
     }
+    CUtensorMap tx = tc_;
+    if (g.bnx) {
+        if (!g.bn_mean || !g.bn_invstd) return LWC_EINVAL;
+        cuuint64_t cd[4] = {(cuuint64_t)g.Cout, (cuuint64_t)g.OW, (cuuint64_t)g.OH, (cuuint64_t)g.ON};
+        cuuint64_t cs[3] = {(cuuint64_t)g.y_wpitch * 2, (cuuint64_t)g.y_hpitch * 2, (cuuint64_t)g.y_npitch * 2};
+        cuuint32_t cb[4] = {64, (cuuint32_t)pt.Wb, (cuuint32_t)pt.Hb, (cuuint32_t)pt.Nb};
+        rc = encode(&tx, g.bnx, 4, cd, cs, cb, nullptr);
+        if (rc) return rc;
+    }
     int grid = p.tiles_m * p.tiles_n;
     if (grid > sm_count()) grid = sm_count();
     // with statistics a CTA must stay on one column of output-channel tiles (tile = mt * tiles_n + nt, stride = grid)
     if (g.stats && grid % p.tiles_n) grid = grid > p.tiles_n ? grid / p.tiles_n * p.tiles_n : p.tiles_n;
     if (g.stats && p.tiles_n > sm_count()) return LWC_ETOOBIG;
     if (grid_out) *grid_out = grid;
-    if (BN == 256) rc = g.b_mn ? launch_fx<256, true>(ta, tb, tc_, p, smem, grid, st) : launch_fx<256, false>(ta, tb, tc_, p, smem, grid, st);
-    else if (BN == 128) rc = g.b_mn ? launch_fx<128, true>(ta, tb, tc_, p, smem, grid, st) : launch_fx<128, false>(ta, tb, tc_, p, smem, grid, st);
-    else rc = g.b_mn ? launch_fx<64, true>(ta, tb, tc_, p, smem, grid, st) : launch_fx<64, false>(ta, tb, tc_, p, smem, grid, st);
+    if (BN == 256) rc = g.b_mn ? launch_fx<256, true>(ta, tb, tc_, tx, p, smem, grid, st) : launch_fx<256, false>(ta, tb, tc_, tx, p, smem, grid, st);
+    else if (BN == 128) rc = g.b_mn ? launch_fx<128, true>(ta, tb, tc_, tx, p, smem, grid, st) : launch_fx<128, false>(ta, tb, tc_, tx, p, smem, grid, st);
+    else rc = g.b_mn ? launch_fx<64, true>(ta, tb, tc_, tx, p, smem, grid, st) : launch_fx<64, false>(ta, tb, tc_, tx, p, smem, grid, st);
     if (rc) return rc;
     return (int)cudaGetLastError();
 }
@@ -833,6 +913,44 @@ extern "C" int lwc_convx_dgrad(const void* dy, const void* wt, void* dx, int N, 
             if (rc) return rc;
         }
     return 0;
+}
+
+// Stride-1 data gradient whose output dz is the gradient of a batch-norm (+ ReLU) output: the same launch also sums
+// S1 = sum d and S2 = sum d * x per channel (d = dz * [bn(x) > 0] with relu, else dz) into per-CTA partials
+// [lwc_convx_max_partials()][2][Cin] -- the batch norm's backward then needs no reduction pass over dz and x
+// (lwc_bn_backward_from_partials).  k = 1 / pad 0 uses the forward weight as stored, like lwc_convx_dgrad1x1.
+//   x_bn : the batch norm's input [N][H][W][Cin] bf16; gamma / beta nullable; mean / invstd its batch statistics
+extern "C" int lwc_convx_dgrad_bnstats(const void* dy, const void* wt, void* dx, int N, int H, int W, int Cin, int Cout, int k, int pad,
+                                       const void* x_bn, const float* gamma, const float* beta, const float* mean, const float* invstd,
+                                       int relu, float* partials, int* nparts_out, int bn_hint, void* stream) {
+    if (!dy || !wt || !dx || !x_bn || !mean || !invstd || !partials || N <= 0 || (Cin % 64) || (Cout % 64) || k < 1 || k * k > MAXT)
+        return LWC_EINVAL;
+    FxGeom g;
+    memset(&g, 0, sizeof(g));
+    const int OH = H + 2 * pad - k + 1, OW = W + 2 * pad - k + 1;
+    if (OH <= 0 || OW <= 0) return LWC_EINVAL;
+    g.x = dy; g.C = Cout; g.cpitch = Cout; g.W = OW; g.H = OH; g.N = N;
+    g.w = wt; g.Ktot = Cout; g.b_mn = 1; g.b_ncols = k * k * Cin;
+    g.y = dx; g.OW = W; g.OH = H; g.ON = N; g.Cout = Cin;
+    g.y_wpitch = Cin; g.y_hpitch = (long long)W * Cin; g.y_npitch = (long long)H * W * Cin;
+    g.stride = 1; g.kchunks = Cout / 64; g.bn_hint = bn_hint;
+    g.stats = partials; g.bnx = x_bn; g.bn_gamma = gamma; g.bn_beta = beta; g.bn_mean = mean; g.bn_invstd = invstd; g.bnb_relu = relu;
+    if (k == 1 && pad == 0) {
+        const long long M = (long long)N * H * W;
+        if (M > 0x7fffffffLL) return LWC_ETOOBIG;
+        g.W = (int)M; g.H = 1; g.N = 1; g.OW = (int)M; g.OH = 1; g.ON = 1;
+        g.y_hpitch = M * Cin; g.y_npitch = M * Cin;
+        g.ntaps = 1;
+    } else {
+        int n = 0;
+        for (int a = 0; a < k; ++a)
+            for (int b = 0; b < k; ++b) {
+                g.dh[n] = (short)(pad - a); g.dw[n] = (short)(pad - b); g.b_n0[n] = (a * k + b) * Cin;
+                ++n;
+            }
+        g.ntaps = n;
+    }
+    return run_fx(g, (cudaStream_t)stream, nparts_out);
 }
 
 // The 7x7/2 ResNet stem on the 2x2 space-to-depth input (see lwc_normalize_u8 mode 1): a dense 4x4/1 convolution
