@@ -58,7 +58,7 @@ class BasicBlock(nn.Module):
 
     def forward(self, x):
         identity = x if self.downsample is None else self.downsample(x)
-        out = self.bn1(self.conv1(x), relu=True)
+        out = self.bn1(self.conv1(x), relu=True, fuse_bwd=True)
         return self.bn2(self.conv2(out), residual=identity, relu=True)
 
 
@@ -88,8 +88,9 @@ class Bottleneck(nn.Module):
         out, identity = fork_conv1x1(self.conv1, x)
         if self.downsample is not None:
             identity = self.downsample(identity)
-        out = self.bn1(out, relu=True)
-        out = self.bn2(self.conv2(out), relu=True)
+        # bn1 / bn2 feed exactly one convolution each: its data gradient sums their backward reductions (fuse_bwd)
+        out = self.bn1(out, relu=True, fuse_bwd=True)
+        out = self.bn2(self.conv2(out), relu=True, fuse_bwd=True)
         return self.bn3(self.conv3(out), residual=identity, relu=True)
 
 

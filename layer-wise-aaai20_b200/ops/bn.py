@@ -62,7 +62,7 @@ class _BatchNormAct(torch.autograd.Function):
 
     @staticmethod
     def forward(ctx, x, weight, bias, running_mean, running_var, residual, training, momentum, eps, relu,
-                num_batches_tracked=None, stat_partials=None, stat_nparts=0, stat_count=0):
+                num_batches_tracked=None, stat_partials=None, stat_nparts=0, stat_count=0, link=None):
         lib = _native.lib()
         M, Cc = _rows_channels(x)
         y = torch.empty_like(x)       # preserves the channels-last strides
@@ -96,6 +96,12 @@ class _BatchNormAct(torch.autograd.Function):
             _native.counters.add(3 if training else 1)
         ctx.training, ctx.relu, ctx.has_res = training, relu, residual is not None
         ctx.eps = eps
+        # the single consumer of y (a stride-1 convolution) may compute this layer's backward reduction sums in its
+        # data-gradient epilogue: it finds what it needs in `link` and leaves the partials there (ops/conv.py)
+        ctx.link = None
+        if link is not None and training and residual is None and x.dim() == 4 and x.dtype == torch.bfloat16:
+            link.update(x=x, gamma=weight, beta=bias, mean=mean, invstd=invstd, relu=bool(relu))
+            ctx.link = link
         # the ReLU mask is recomputed from x unless a residual was fused (then it depends on y)
         need_y = relu and (residual is not None or not training) and mask is None
         # a consumer (ops.conv.fork_conv1x1) may take over the masking of the incoming gradient: it flips taken[0]
@@ -123,7 +129,22 @@ class _BatchNormAct(torch.autograd.Function):
             xhat = (x.float() - mean.view(shape)) * torch.rsqrt(invstd + ctx.eps).view(shape)
             dims = (0, 2, 3) if x.dim() == 4 else (0,)
             return (dx, (g.float() * xhat).sum(dims), g.float().sum(dims), None, None,
-                    g if ctx.has_res else None, None, None, None, None, None, None, None, None)
+                    g if ctx.has_res else None, None, None, None, None, None, None, None, None, None)
+        link = getattr(ctx, "link", None)
+        if link is not None and "partials" in link:
+            part, nparts = link.pop("partials")
+            dx = torch.empty_like(x)
+            dgamma = torch.empty(Cc, dtype=torch.float32, device=x.device)
+            dbeta = torch.empty(Cc, dtype=torch.float32, device=x.device)
+            st = torch.cuda.current_stream().cuda_stream
+            rc = lib.lwc_bn_backward_from_partials(dy.data_ptr(), x.data_ptr(), dx.data_ptr(), _ptr(weight), _ptr(bias),
+                                                   mean.data_ptr(), invstd.data_ptr(), dgamma.data_ptr(), dbeta.data_ptr(),
+                                                   part.data_ptr(), int(nparts), M, Cc, abi.dtype_code(x.dtype), int(ctx.relu),
+                                                   C.c_void_p(st))
+            abi.check(rc, "lwc_bn_backward_from_partials")
+            _native.counters.add(2)
+            return (dx, dgamma if weight is not None else None, dbeta if weight is not None else None, None, None,
+                    None, None, None, None, None, None, None, None, None, None)
         dx = torch.empty_like(x)
         premasked = ctx.mask_taken is not None and ctx.mask_taken[0]
         if premasked:
@@ -145,20 +166,23 @@ class _BatchNormAct(torch.autograd.Function):
             dres = dy
         _native.counters.add(3)
         return (dx, dgamma if weight is not None else None, dbeta if weight is not None else None, None, None,
-                dres, None, None, None, None, None, None, None, None)
+                dres, None, None, None, None, None, None, None, None, None)
 
 
 def batch_norm_act(x, weight, bias, running_mean, running_var, residual=None, training=True,
-                   momentum=0.1, eps=1e-5, relu=False, num_batches_tracked=None, stats=None):
+                   momentum=0.1, eps=1e-5, relu=False, num_batches_tracked=None, stats=None, fuse_bwd=False):
     """``relu?(batch_norm(x) + residual?)`` in one fused pass structure (see module docstring).
     ``num_batches_tracked`` (int64 CUDA scalar) is incremented inside the statistics-finalize kernel."""
     _BatchNormAct.last_mask = (None, None)
+    link = {} if (fuse_bwd and training and residual is None and torch.is_grad_enabled()) else None
     if stats is not None and training:
         y = _BatchNormAct.apply(x, weight, bias, running_mean, running_var, residual, training, momentum, eps, relu,
-                                num_batches_tracked, stats.partials, stats.nparts, stats.count)
+                                num_batches_tracked, stats.partials, stats.nparts, stats.count, link)
     else:
         y = _BatchNormAct.apply(x, weight, bias, running_mean, running_var, residual, training, momentum, eps, relu,
-                                num_batches_tracked)
+                                num_batches_tracked, None, 0, 0, link)
+    if link:
+        y.bn_link = link               # picked up by the consuming ops.nn.Conv2d
     mask, taken = _BatchNormAct.last_mask
     if mask is not None:
         y.relu_mask, y.relu_mask_taken = mask, taken       # see ops.conv.fork_conv1x1
@@ -166,7 +190,7 @@ def batch_norm_act(x, weight, bias, running_mean, running_var, residual=None, tr
     return y
 
 
-def maybe_batch_norm(module, x, residual=None, relu=False):
+def maybe_batch_norm(module, x, residual=None, relu=False, fuse_bwd=False):
     """Module dispatch; returns ``None`` when the stock implementation must run."""
     if module.momentum is None:          # cumulative moving average: stock implementation
         return None
@@ -181,4 +205,4 @@ def maybe_batch_norm(module, x, residual=None, relu=False):
             nbt = None
     return batch_norm_act(x, module.weight, module.bias, module.running_mean, module.running_var,
                           residual, training, module.momentum, module.eps, relu, nbt,
-                          stats=getattr(x, "bn_stats", None))
+                          stats=getattr(x, "bn_stats", None), fuse_bwd=fuse_bwd)

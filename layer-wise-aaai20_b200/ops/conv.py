@@ -191,6 +191,44 @@ def conv_dgrad(dy: torch.Tensor, weight: torch.Tensor, in_hw: Tuple[int, int], s
     return dx
 
 
+def conv_dgrad_bnstats(dy: torch.Tensor, weight: torch.Tensor, in_hw: Tuple[int, int], padding: int, link: dict,
+                       bn_hint: Optional[int] = None) -> torch.Tensor:
+    """Stride-1 data gradient whose output is the gradient of a batch-norm (+ ReLU) output: the same launch sums the
+    batch norm's backward reductions (sum d, sum d * x) into per-CTA partials, left in ``link['partials']`` for the batch
+    norm's backward (``ops/bn.py``), which then skips its reduction pass over dz and x."""
+    lib = _native.lib()
+    co, ci, k, _ = weight.shape
+    if not _nhwc(dy):
+        dy = dy.contiguous(memory_format=torch.channels_last)
+    n = dy.shape[0]
+    h, w = in_hw
+    dx = torch.empty((n, ci, h, w), dtype=dy.dtype, device=dy.device, memory_format=torch.channels_last)
+    wt = weight.detach().permute(0, 2, 3, 1).contiguous()
+    part = torch.empty((int(lib.lwc_convx_max_partials()), 2, ci), dtype=torch.float32, device=dy.device)
+    nparts = C.c_int(0)
+    xb, gamma, beta, mean, invstd = link["x"], link["gamma"], link["beta"], link["mean"], link["invstd"]
+
+    def run(hint):
+        abi.check(lib.lwc_convx_dgrad_bnstats(dy.data_ptr(), wt.data_ptr(), dx.data_ptr(), n, h, w, ci, co, k, int(padding),
+                                              xb.data_ptr(), 0 if gamma is None else gamma.data_ptr(),
+                                              0 if beta is None else beta.data_ptr(), mean.data_ptr(), invstd.data_ptr(),
+                                              int(link["relu"]), part.data_ptr(), C.byref(nparts), hint, _stream()),
+                  "lwc_convx_dgrad_bnstats")
+
+    if bn_hint is None:
+        bn_hint = _tuned(("db", n, h, w, ci, co, k, padding), ci, run, [b for b in (64, 128) if ci % b == 0])
+    run(bn_hint)
+    _native.counters.add(1)
+    link["partials"] = (part, int(nparts.value))
+    return dx
+
+
+def bn_link_usable(link, x: torch.Tensor, weight: torch.Tensor, stride: int) -> bool:
+    """Can this convolution's data gradient produce the backward sums of the batch norm described by ``link``?"""
+    return (link is not None and _ENABLED["on"] and _FUSE_BNB["on"] and stride == 1 and weight.shape[1] % 64 == 0
+            and weight.shape[0] % 64 == 0 and link["x"].shape == x.shape and link["x"].dtype == torch.bfloat16 and _nhwc(link["x"]))
+
+
 _WS: Dict[tuple, torch.Tensor] = {}
 
 
@@ -235,10 +273,11 @@ class _ConvFn(torch.autograd.Function):
     last_stats = None
 
     @staticmethod
-    def forward(ctx, x, weight, bias, stride, padding, relu, want_stats):
+    def forward(ctx, x, weight, bias, stride, padding, relu, want_stats, bn_link=None):
         y, stats = conv_forward(x, weight, bias, relu=relu, want_stats=want_stats, stride=stride, padding=padding)
         ctx.save_for_backward(x, weight, y if relu else None)
         ctx.conf = (stride, padding, relu, bias is not None)
+        ctx.bn_link = bn_link if bn_link_usable(bn_link, x, weight, stride) else None
         _ConvFn.last_stats = stats
         return y
 
@@ -252,7 +291,9 @@ class _ConvFn(torch.autograd.Function):
             dy = dy.contiguous(memory_format=torch.channels_last)
         dx = dw = db = None
         if ctx.needs_input_grad[0]:
-            if weight.shape[1] % 64 == 0:
+            if ctx.bn_link is not None:
+                dx = conv_dgrad_bnstats(dy, weight, (x.shape[2], x.shape[3]), padding, ctx.bn_link)
+            elif weight.shape[1] % 64 == 0:
                 dx = conv_dgrad(dy, weight, (x.shape[2], x.shape[3]), stride, padding)
             else:       # not reached by the model zoo (only first layers have such inputs, and they need no dX)
                 dx = torch.ops.aten.convolution_backward(dy, x, weight, None, [stride] * 2, [padding] * 2, [1, 1], False,
@@ -261,15 +302,16 @@ class _ConvFn(torch.autograd.Function):
             dw = conv_wgrad(x, dy, weight.shape, stride, padding, out_dtype=weight.dtype)
         if has_bias and ctx.needs_input_grad[2]:
             db = dy.float().sum((0, 2, 3)).to(dy.dtype)
-        return dx, dw, db, None, None, None, None
+        return dx, dw, db, None, None, None, None, None
 
 
 def conv2d(x, weight, bias=None, want_stats: bool = False, stride: int = 1, padding: Optional[int] = None,
-           relu: bool = False):
-    """Autograd-aware native convolution; returns ``(y, Stats | None)``."""
+           relu: bool = False, bn_link=None):
+    """Autograd-aware native convolution; returns ``(y, Stats | None)``.  ``bn_link``: see ``ops.bn`` (the input is the
+    output of a batch norm whose backward sums this layer's data gradient can produce)."""
     pad = weight.shape[2] // 2 if padding is None else int(padding)
     _ConvFn.last_stats = None
-    y = _ConvFn.apply(x, weight, bias, int(stride), pad, bool(relu), bool(want_stats))
+    y = _ConvFn.apply(x, weight, bias, int(stride), pad, bool(relu), bool(want_stats), bn_link)
     stats, _ConvFn.last_stats = _ConvFn.last_stats, None
     return y, stats
 
@@ -294,6 +336,14 @@ def fuse_bn_stats(flag: bool = True):
     _FUSE_STATS["on"] = bool(flag)
 
 
+_FUSE_BNB = {"on": os.environ.get("LWC_CONV_BN_BWD", "1") != "0"}
+
+
+def fuse_bn_backward(flag: bool = True):
+    """Let stride-1 data gradients sum the backward reductions of the batch norm that produced their layer's input."""
+    _FUSE_BNB["on"] = bool(flag)
+
+
 def maybe_conv2d(module, x, relu: bool = False):
     """Module dispatch; returns ``None`` when the stock implementation must run."""
     if not _ENABLED["on"]:
@@ -303,7 +353,7 @@ def maybe_conv2d(module, x, relu: bool = False):
     want = (_FUSE_STATS["on"] and bool(getattr(module, "emit_bn_stats", False)) and module.training
             and torch.is_grad_enabled() and module.bias is None)
     y, stats = conv2d(x, module.weight, module.bias, want_stats=want, stride=module.stride[0], padding=module.padding[0],
-                      relu=relu)
+                      relu=relu, bn_link=getattr(x, "bn_link", None))
     if stats is not None:
         y.bn_stats = stats
     return y

@@ -65,11 +65,13 @@ class BatchNorm2d(nn.BatchNorm2d):
     layouts the same math runs with stock ops.
     """
 
-    def forward(self, x, residual=None, relu=False):
+    def forward(self, x, residual=None, relu=False, fuse_bwd=False):
+        """``fuse_bwd``: the output has exactly ONE consumer, a convolution -- its data gradient may then produce this
+        layer's backward reduction sums in its epilogue (``ops/conv.py::conv_dgrad_bnstats``)."""
         relu = relu or getattr(self, "fuse_relu", False)      # graph nets mark conv-bn-relu triples
         if _native_ok(x):
             from . import bn as _bn
-            y = _bn.maybe_batch_norm(self, x, residual, relu)
+            y = _bn.maybe_batch_norm(self, x, residual, relu, fuse_bwd=fuse_bwd)
             if y is not None:
                 return y
         y = super().forward(x)

@@ -249,3 +249,64 @@ def test_conv_emitted_statistics_feed_the_batch_norm():
     assert na == nb == 1
     assert torch.allclose(ma, mb, rtol=1e-4, atol=1e-5) and torch.allclose(va, vb, rtol=1e-3, atol=1e-5)
     assert _rel(ya, yb) <= 1e-2 and _rel(ga, gb) <= 2e-2
+
+
+@pytest.mark.parametrize("n,ci,co,hw,k", [(4, 64, 64, 56, 3), (6, 128, 512, 28, 1), (3, 256, 256, 14, 3), (5, 512, 128, 7, 1), (2, 64, 256, 9, 1)])
+@pytest.mark.parametrize("relu", [True, False])
+def test_dgrad_epilogue_sums_batch_norm_backward_reductions(n, ci, co, hw, k, relu):
+    """lwc_convx_dgrad_bnstats: dX and, from the same launch, S1 = sum d and S2 = sum d * x with d = dX * [bn(x) > 0]."""
+    from layerwise_b200.ops.conv import conv_dgrad, conv_dgrad_bnstats
+    torch.manual_seed(0)
+    _, wt = _mk(n, ci, co, hw, hw, k)
+    dy = torch.randn(n, co, hw, hw, device="cuda").to(torch.bfloat16).contiguous(memory_format=torch.channels_last)
+    xb = torch.randn(n, ci, hw, hw, device="cuda").to(torch.bfloat16).contiguous(memory_format=torch.channels_last)
+    gamma, beta = torch.rand(ci, device="cuda") + 0.5, torch.randn(ci, device="cuda") * 0.3
+    mean, invstd = torch.randn(ci, device="cuda") * 0.2, torch.rand(ci, device="cuda") + 0.5
+    link = dict(x=xb, gamma=gamma, beta=beta, mean=mean, invstd=invstd, relu=relu)
+    dx = conv_dgrad_bnstats(dy, wt, (hw, hw), k // 2, link)
+    ref = conv_dgrad(dy, wt, (hw, hw), 1, k // 2)
+    assert torch.equal(dx, ref)                                   # same kernel, same arithmetic
+    part, nparts = link["partials"]
+    s = part[:nparts].sum(0)
+    a = gamma * invstd
+    b = beta - mean * a
+    d = dx.float()
+    if relu:
+        d = d * (torch.addcmul(b.view(1, -1, 1, 1), xb.float(), a.view(1, -1, 1, 1)) > 0)
+    s1, s2 = d.sum((0, 2, 3)), (d * xb.float()).sum((0, 2, 3))
+    scale = float(d.abs().sum((0, 2, 3)).max())
+    assert (s[0] - s1).abs().max() <= 2e-3 * scale and (s[1] - s2).abs().max() <= 4e-3 * scale
+
+
+def test_bottleneck_with_fused_batch_norm_backward_matches_unfused():
+    """Two bottlenecks: bn1 / bn2 get their backward sums from the data-gradient epilogue of conv2 / conv3; gradients
+    must agree with the path that runs the separate reduction kernel."""
+    import copy
+    from layerwise_b200.models import resnet as zoo
+    from layerwise_b200.ops import conv as C_
+    torch.manual_seed(0)
+    blocks = torch.nn.Sequential(zoo.Bottleneck(256, 64), zoo.Bottleneck(256, 64)).cuda().to(memory_format=torch.channels_last).to(torch.bfloat16)
+    for m in blocks.modules():
+        if isinstance(m, torch.nn.modules.batchnorm._BatchNorm):
+            m.float()
+            torch.nn.init.uniform_(m.weight, 0.5, 1.5)
+            torch.nn.init.normal_(m.bias, 0.0, 0.5)
+    x0 = torch.randn(8, 256, 14, 14, device="cuda").to(torch.bfloat16).contiguous(memory_format=torch.channels_last)
+    g = torch.randn(8, 256, 14, 14, device="cuda").to(torch.bfloat16).contiguous(memory_format=torch.channels_last)
+    res = []
+    for fused in (True, False):
+        C_.fuse_bn_backward(fused)
+        try:
+            net = copy.deepcopy(blocks)
+            x = x0.clone().requires_grad_(True)
+            (net(x) * g).sum().backward()
+            res.append((x.grad.float(), [p.grad.float() for p in net.parameters()]))
+        finally:
+            C_.fuse_bn_backward(True)
+    (gx_a, gp_a), (gx_b, gp_b) = res
+
+    def relerr(a, b):
+        return float((a - b).norm() / (b.norm() + 1e-12))
+    assert relerr(gx_a, gx_b) < 2e-2
+    for a, b in zip(gp_a, gp_b):
+        assert relerr(a, b) < 2e-2, (a.shape, relerr(a, b))
