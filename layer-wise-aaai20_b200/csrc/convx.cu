@@ -280,6 +280,7 @@ __global__ void __launch_bounds__(THREADS, 1) k_fx(const __grid_constant__ CUten
 #pragma unroll
                     for (int i = 0; i < 4; ++i) {
                         const int row = rg * 4 + i;
+                        if (row >= p.rows_per_tile) continue;      // rows past the patch: the x tile holds nothing there
                         const int off = row * 128 + ((c ^ (row & 7)) * 16);
                         const uint4 ud = *reinterpret_cast<const uint4*>(cst + off);
                         const uint4 ux = *reinterpret_cast<const uint4*>(xs + off);
