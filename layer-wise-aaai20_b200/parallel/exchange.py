@@ -271,7 +271,7 @@ class GradientExchanger:
         if stats is None:
             return {}
         st = stats()
-        if self.engine_name in ("fused", "dense") and _native_poisoned():
+        if getattr(self.engine, "name", "") in ("fused", "dense") and _native_poisoned():
             st["poisoned"] = 1
             if raise_on_timeout:
                 _native_poison_clear()

@@ -103,7 +103,7 @@ def test_check_health_reports_new_timeouts():
     import torch
     from layerwise_b200.parallel.exchange import CompressionConfig, GradientExchanger
     p = torch.nn.Parameter(torch.zeros(8))
-    ex = GradientExchanger([p], CompressionConfig())
+    ex = GradientExchanger([p], CompressionConfig(error_feedback=True))
     assert ex.check_health() == {} or "timeouts" in ex.check_health()       # the torch engine keeps no counters
 
     class _Eng:                                                            # an engine with counters
@@ -120,3 +120,8 @@ def test_check_health_reports_new_timeouts():
     assert ex.check_health()["timeouts"] == 2                              # already reported: no second raise
     ex.engine.n = 3
     assert ex.check_health(raise_on_timeout=False)["timeouts"] == 3
+    # without error feedback a clamped entry would be lost for good: that is an error, not a statistic
+    ex2 = GradientExchanger([p], CompressionConfig(error_feedback=False))
+    ex2.engine = _Eng()
+    with pytest.raises(RuntimeError, match="did not fit"):
+        ex2.check_health()
