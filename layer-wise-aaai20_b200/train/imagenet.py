@@ -123,6 +123,7 @@ class Trainer:
         s2d = on_gpu and channels_last and isinstance(net, resnet_zoo.ResNet)
         self.normalize = InputNormalizer(self.dtype, channels_last and on_gpu, s2d=s2d).to(self.device)
         self.criterion = lnn.CrossEntropyLoss().to(self.device)
+        self.criterion.trust_targets = True       # labels come from the dataset / sampler: always class indices
         self.cfg = cfg or CompressionConfig()
         self.model_params = [p for p in net.parameters() if p.requires_grad]
         if comm.is_initialized() and comm.world_size() > 1:
@@ -333,10 +334,19 @@ class Trainer:
         return save_checkpoint(epoch, self.net, best_top5, self.optimizer, is_best=is_best, filename=filename,
                                logdir=logdir, exchanger=self.exchanger, masters=masters or None)
 
+    def save_rank_state(self, filename):
+        """Call on EVERY rank next to ``save`` (which only rank 0 calls): writes this rank's error-feedback residual
+        into a sidecar of the checkpoint (``utils.checkpoint.save_rank_residual``)."""
+        from ..utils.checkpoint import save_rank_residual
+        if comm.world_size() > 1:
+            return save_rank_residual(filename, self.exchanger, comm.rank())
+        return None
+
     def resume(self, path):
         masters = [m for m, p in zip(self.master_params, self.model_params) if m is not p]
         epoch, best = load_checkpoint(path, self.net, self.optimizer, map_location=self.device,
-                                      exchanger=self.exchanger, masters=masters or None)
+                                      exchanger=self.exchanger, masters=masters or None,
+                                      rank=comm.rank(), world=comm.world_size())
         if not masters:
             return epoch, best
         ck = torch.load(path, map_location="cpu", weights_only=False)

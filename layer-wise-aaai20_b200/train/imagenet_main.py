@@ -216,6 +216,11 @@ def main(argv=None):
         log.event(f"~~{epoch}\t{hours:.5f}\t\t{top1:.3f}\t\t{top5:.3f}\n")
         is_best = top5 > best_top5
         best_top5 = max(top5, best_top5)
+        # every rank keeps its own error-feedback residual next to the checkpoint that rank 0 writes
+        if is_best:
+            trainer.save_rank_state("model_best.pth.tar")
+        if phase:
+            trainer.save_rank_state(f'sz{phase["bs"]}_checkpoint.path.tar')
         if is_rank0:
             if is_best:
                 trainer.save(epoch, best_top5, "model_best.pth.tar", is_best=True, logdir=args.logdir or None)
