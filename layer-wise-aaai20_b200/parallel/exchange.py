@@ -226,6 +226,12 @@ class GradientExchanger:
             from .. import _native
             if _native.available():
                 use_fused = True
+                # the peer-memory engines need every rank on one node (CUDA-IPC / NVLink peer mappings): a world that
+                # spans nodes takes the collective engine when the choice is 'auto' (and says so when forced)
+                if comm.world_size(group) > 1 and not _single_node(group):
+                    if engine == "fused":
+                        raise RuntimeError("the fused engine exchanges through peer memory: all ranks must share a node")
+                    use_fused = False
             elif engine == "fused":
                 _native.require()
                 raise RuntimeError("fused engine requested but the native library is unavailable")
@@ -291,6 +297,17 @@ class GradientExchanger:
     @property
     def step(self):
         return self.engine.step
+
+
+def _single_node(group=None) -> bool:
+    """True when every rank of ``group`` runs on this host (setup-time collective)."""
+    import socket
+    import torch.distributed as dist
+    if not comm.is_initialized():
+        return True
+    names = [None] * comm.world_size(group)
+    dist.all_gather_object(names, socket.gethostname(), group=group)
+    return len(set(names)) == 1
 
 
 def _native_poisoned() -> bool:
