@@ -293,6 +293,14 @@ int lwc_convx_wgrad(const void* x, const void* dy, void* dw, float* workspace, i
 int lwc_convx_dgrad_bnstats(const void* dy, const void* wt, void* dx, int N, int H, int W, int Cin, int Cout, int k, int pad,
                             const void* x_bn, const float* gamma, const float* beta, const float* mean, const float* invstd,
                             int relu, float* partials, int* nparts_out, int bn_hint, void* stream);
+/* Residual fork (IMAGENET/training/resnet.py:72-94, `out += identity; relu`): dX = mask * (dY W + addend) for the block's
+ * first 1x1 convolution -- addend = the skip connection's gradient, mask = the producing batch norm's one-bit ReLU mask
+ * ([M][Cin / 8] bytes, nullable) -- and, with x_bn, that batch norm's backward sums of dX into per-CTA partials.
+ * bn_hint 1000 + BN on lwc_convx_forward / lwc_convx_dgrad selects the halo variant (64 input channels, stride 1):
+ * resident weights, one TMA box per tile, taps read from shifted start addresses. */
+int lwc_convx_dgrad1x1_fork(const void* dy, const void* w, const void* addend, const void* mask, void* dx, long long M,
+                            int Cout, int Cin, const void* x_bn, const float* mean, const float* invstd, float* partials,
+                            int* nparts_out, int bn_hint, void* stream);
 int lwc_bn_backward_from_partials(const void* dy, const void* x, void* dx, const float* gamma, const float* beta,
                                   const float* mean, const float* invstd, float* dgamma, float* dbeta,
                                   const float* partials, int nparts, long long M, int C, int dtype, int relu, void* stream);

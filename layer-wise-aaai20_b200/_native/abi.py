@@ -116,6 +116,7 @@ def declare(lib: C.CDLL):
     sig("lwc_convx_wgrad_workspace_bytes", sz, ci, ci, ci, ci, ci, ci, ci, ci, ci)
     sig("lwc_convx_wgrad", ci, vp, vp, vp, vp, ci, ci, ci, ci, ci, ci, ci, ci, ci, ci, cf, ci, vp)
     sig("lwc_convx_dgrad_bnstats", ci, vp, vp, vp, ci, ci, ci, ci, ci, ci, ci, vp, vp, vp, vp, vp, ci, vp, C.POINTER(ci), ci, vp)
+    sig("lwc_convx_dgrad1x1_fork", ci, vp, vp, vp, vp, vp, ll, ci, ci, vp, vp, vp, vp, C.POINTER(ci), ci, vp)
     sig("lwc_bn_backward_from_partials", ci, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, ci, ll, ci, ci, ci, vp)
     sig("lwc_convx_stats_finalize", ci, vp, ci, ci, ll, cf, cf, vp, vp, vp, vp, vp, vp)
     sig("lwc_bn_apply_stats", ci, vp, vp, vp, vp, vp, vp, vp, ll, ci, ci, ci, vp, vp)

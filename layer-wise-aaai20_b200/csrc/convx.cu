@@ -70,9 +70,21 @@ struct FxParams {
     // epilogue accumulates S1 = sum d, S2 = sum d * x with d = dz * [gamma * invstd * (x - mean) + beta > 0]
     int bnb, bnb_relu, x_off;
     const float *bn_gamma, *bn_beta, *bn_mean, *bn_invstd;
+    // residual fork (data gradient of the block's first 1x1 convolution): out = mask * (acc + addend), where addend is the
+    // skip connection's gradient (a tile of it is TMA-prefetched like the x tile, on the same barrier) and mask is the
+    // one-bit-per-element ReLU mask of the batch norm that produced the block input ([pixel][N / 8] bytes, or NULL)
+    int add, add_off;
+    const uint8_t* mask;
+    // halo mode (64 input channels, stride 1, several taps): the weights of all taps stay in shared memory for the whole
+    // kernel and ONE TMA box per tile brings the input patch with its halo (pixel pitch 16); every tap is then the same
+    // box read from a start address shifted by (dh * 16 + dw) rows -- the activation crosses L2 -> SM once, not per tap
+    int halo, halo_dw0, halo_dh0;            // on/off, offset of the halo origin from the output origin
+    int a_off, a_stage, halo_bytes;          // operand ring offset / stage size, bytes of one halo box
+    int halo_bo;                             // debugging only: also put (start >> 7) & 7 into the descriptor's base-offset field
     short dw[MAXT], dh[MAXT];
     int a_c0[MAXT], b_k0[MAXT], b_n0[MAXT];   // b_n0: column offset of the tap in an MN-major weight matrix
 };
+constexpr int HALO_PW = 16;                  // pixel pitch of a halo box: accumulator row r = (r / 16, r % 16)
 
 struct TileCoord { int mt, nt, w0, h0, n0; };
 __device__ __forceinline__ TileCoord tile_coord(const FxParams& p, int tile) {
@@ -86,10 +98,18 @@ __device__ __forceinline__ TileCoord tile_coord(const FxParams& p, int tile) {
     return t;
 }
 
-template <int BN, bool B_MN>
-__global__ void __launch_bounds__(THREADS, 1) k_fx(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
+// REGSUM: the variant that keeps per-channel sums in registers (batch statistics of the outputs, batch-norm backward
+// sums); the plain variant carries neither the registers nor the code.  (Tried and dropped: the statistics as one more
+// MMA per staged sub-tile, D += [Y^T ; 1^T] Y with both operands MN-major straight from the staging tile.  Correct, but
+// an MN-major A operand is read from shared memory at about a quarter of the K-major rate -- ~120 cycles per 128 x 16
+// slab, measured here and visible in k_wx's tensor-pipe utilisation -- which cost more than the CUDA-core sums it saved.)
+// TWO: compiled for two resident CTAs per SM (<= 96 registers; the host halves the shared-memory plan and the tensor
+// memory of both fits for BN <= 128).  The epilogue of one CTA is a chain of dependent steps with two barriers per
+// sub-tile, eight warps in step; a second CTA at another point of its chain fills the issue slots the first leaves idle.
+template <int BN, bool B_MN, bool FORK, bool REGSUM, bool TWO>
+__global__ void __launch_bounds__(THREADS, TWO ? 2 : 1) k_fx(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                                                    const __grid_constant__ CUtensorMap tmC, const __grid_constant__ CUtensorMap tmX,
-                                                   const FxParams p) {
+                                                   const __grid_constant__ CUtensorMap tmD, const FxParams p) {
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
     constexpr int A_BYTES = BM * BK * 2;
@@ -101,7 +121,9 @@ __global__ void __launch_bounds__(THREADS, 1) k_fx(const __grid_constant__ CUten
     uint64_t* tmem_full = empty + MAXS;        // [2]
     uint64_t* tmem_empty = tmem_full + 2;      // [2]
     uint64_t* xfull = tmem_empty + 2;          // [4] x tile of a chunk has landed (batch-norm backward sums)
-    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(xfull + 4);
+    uint64_t* wfull = xfull + 4;               // [1] resident weights have landed (halo mode)
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(wfull + 1);
+    constexpr int TCOLS = 2 * BN;
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int num_tiles = p.tiles_m * p.tiles_n;
@@ -114,10 +136,12 @@ __global__ void __launch_bounds__(THREADS, 1) k_fx(const __grid_constant__ CUten
         for (int s = 0; s < stages; ++s) { mbar_init(&full[s], 1); mbar_init(&empty[s], 1); }
         for (int a = 0; a < 2; ++a) { mbar_init(&tmem_full[a], 1); mbar_init(&tmem_empty[a], 8); }
         for (int a = 0; a < 4; ++a) mbar_init(&xfull[a], 1);
+        mbar_init(wfull, 1);
         if (p.bnb) prefetch_tensormap(&tmX);
+        if (FORK) prefetch_tensormap(&tmD);
         fence_barrier_init();
     }
-    if (warp == 1) tmem_alloc<2 * BN>(tmem_slot);
+    if (warp == 1) tmem_alloc<TCOLS>(tmem_slot);
     fence_before();
     __syncthreads();
     fence_after();
@@ -126,6 +150,27 @@ __global__ void __launch_bounds__(THREADS, 1) k_fx(const __grid_constant__ CUten
     if (warp == 0 && lane == 0) {
         // ---------------- TMA producer ----------------
         uint32_t s = 0, ph = 0;
+        if (p.halo) {
+            // the grid is a multiple of tiles_n: this CTA's output channels never change, its weights are loaded once
+            const int co0 = ((int)blockIdx.x % p.tiles_n) * BN;
+            mbar_expect_tx(wfull, (uint32_t)p.ntaps * B_BYTES);
+            for (int tap = 0; tap < p.ntaps; ++tap) {
+                uint8_t* b = smem + tap * B_BYTES;
+                if (B_MN) {
+#pragma unroll
+                    for (int h = 0; h < BN / 64; ++h) tma_load_2d(b + h * 8192, &tmB, wfull, p.b_n0[tap] + co0 + h * 64, p.b_k0[tap]);
+                } else {
+                    tma_load_2d(b, &tmB, wfull, p.b_k0[tap], co0);
+                }
+            }
+            for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+                const TileCoord t = tile_coord(p, tile);
+                mbar_wait(&empty[s], ph ^ 1);
+                mbar_expect_tx(&full[s], (uint32_t)p.halo_bytes);
+                tma_load_4d(smem + p.a_off + s * p.a_stage, &tmA, &full[s], p.a_c0[0], t.w0 + p.halo_dw0, t.h0 + p.halo_dh0, t.n0);
+                if (++s == (uint32_t)stages) { s = 0; ph ^= 1; }
+            }
+        } else
         for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
             const TileCoord t = tile_coord(p, tile);
             const int co0 = t.nt * BN;
@@ -152,6 +197,34 @@ __global__ void __launch_bounds__(THREADS, 1) k_fx(const __grid_constant__ CUten
         // ---------------- MMA issuer ----------------
         constexpr uint32_t idesc = make_idesc(BN, false, B_MN);
         uint32_t s = 0, ph = 0, tcount = 0;
+        if (p.halo) {
+            mbar_wait(wfull, 0);
+            const uint32_t wsm = smem_u32(smem);
+            for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++tcount) {
+                const uint32_t as = tcount & 1, aph = (tcount >> 1) & 1;
+                mbar_wait(&tmem_empty[as], aph ^ 1);
+                mbar_wait(&full[s], ph);
+                fence_after();
+                const uint32_t tacc = tmem_base + as * BN;
+                const uint32_t a = smem_u32(smem + p.a_off + s * p.a_stage);
+                for (int tap = 0; tap < p.ntaps; ++tap) {
+                    // tap = the same box, `off` pixel rows (128 bytes each) further on.  The start is then no longer
+                    // 1024-byte aligned, and that is fine as it stands: the 128-byte swizzle is applied to the shared-memory
+                    // ADDRESS (bits 4-6 ^= bits 7-9), by the TMA unit that wrote the box and by the tensor core that reads
+                    // it alike, so a row is found where it was put whatever row the descriptor starts at.  Measured on
+                    // B200: correct with the base-offset field left 0, wrong with (start >> 7) & 7 in it.
+                    const uint32_t off = (uint32_t)((p.dh[tap] - p.halo_dh0) * HALO_PW + (p.dw[tap] - p.halo_dw0));
+                    uint64_t da = make_desc(a + off * 128u, 16, 1024);
+                    if (p.halo_bo) da |= (uint64_t)(off & 7u) << 49;
+                    const uint32_t b = wsm + tap * B_BYTES;
+                    const uint64_t db = B_MN ? make_desc(b, 8192, 1024) : make_desc(b, 16, 1024);
+                    umma_x4<2, (B_MN ? 128 : 2)>(tacc, da, db, idesc, tap > 0 ? 1u : 0u);
+                }
+                umma_commit(&empty[s]);
+                umma_commit(&tmem_full[as]);
+                if (++s == (uint32_t)stages) { s = 0; ph ^= 1; }
+            }
+        } else
         for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++tcount) {
             const uint32_t as = tcount & 1, aph = (tcount >> 1) & 1;
             mbar_wait(&tmem_empty[as], aph ^ 1);
@@ -178,25 +251,37 @@ __global__ void __launch_bounds__(THREADS, 1) k_fx(const __grid_constant__ CUten
         const int r = q * 32 + lane;                   // accumulator row = pixel of the patch
         const int et = threadIdx.x - 64;               // 0..255
         const bool leader = et == 0;
-        const int r_w = r % p.Wb, r_h = (r / p.Wb) % p.Hb, r_n = r / (p.Wb * p.Hb);
+        // pixel of the patch this accumulator row is, and the row of the (compact) staging tile it goes to: in halo mode
+        // the accumulator has the box's 16-pixel pitch and the Wb-pixel-pitch staging tile drops the overhang columns
+        // (they land behind the patch, zeroed, where the TMA store does not look)
+        const int r_w = p.halo ? (r & (HALO_PW - 1)) : r % p.Wb;
+        const int r_h = p.halo ? (r / HALO_PW) : (r / p.Wb) % p.Hb;
+        const int r_n = p.halo ? 0 : r / (p.Wb * p.Hb);
+        const bool r_in = p.halo ? (r_w < p.Wb && r_h < p.Hb) : (r < p.rows_per_tile);
+        int dr = r;
+        if (p.halo) dr = r_in ? r_h * p.Wb + r_w : p.Wb * p.Hb + r_h * (HALO_PW - p.Wb) + (r_w < p.Wb ? 0 : r_w - p.Wb);
         const bool slow = p.bias != nullptr || p.relu != 0;
         constexpr int NCH = BN / 64;
-        // x-tile prefetch (batch-norm backward sums): the leader keeps the loads two chunks ahead of the epilogue
+        // auxiliary-tile prefetch (x tile of the batch-norm backward sums, addend tile of the residual fork): the leader
+        // keeps the loads two chunks ahead of the epilogue, one barrier per ring slot covers both tiles
+        const bool aux = p.bnb || FORK;
         int pf_tile = blockIdx.x, pf_h = 0;
         uint32_t pf_q = 0, q_cnt = 0;
         auto prefetch_x = [&]() {
             if (pf_tile >= num_tiles) return;
             const TileCoord tt = tile_coord(p, pf_tile);
             const uint32_t slot = pf_q % (uint32_t)p.ncs;
-            mbar_expect_tx(&xfull[slot], a_bytes);
-            tma_load_4d(smem + p.x_off + slot * SUB_BYTES, &tmX, &xfull[slot], tt.nt * BN + pf_h * 64, tt.w0, tt.h0, tt.n0);
+            mbar_expect_tx(&xfull[slot], (p.bnb && FORK) ? 2 * a_bytes : a_bytes);
+            if (p.bnb) tma_load_4d(smem + p.x_off + slot * SUB_BYTES, &tmX, &xfull[slot], tt.nt * BN + pf_h * 64, tt.w0, tt.h0, tt.n0);
+            if (FORK) tma_load_4d(smem + p.add_off + slot * SUB_BYTES, &tmD, &xfull[slot], tt.nt * BN + pf_h * 64, tt.w0, tt.h0, tt.n0);
             ++pf_q;
             if (++pf_h == NCH) { pf_h = 0; pf_tile += gridDim.x; }
         };
-        if (p.bnb && leader) { prefetch_x(); prefetch_x(); }
-        float sacc[NCH][16];                           // [chunk][sum x 8 channels | sum of squares x 8 channels]
+        if (aux && leader) { prefetch_x(); prefetch_x(); }
+        constexpr int NS = REGSUM ? NCH : 1;
+        float sacc[NS][16];                            // [chunk][sum x 8 channels | sum of squares x 8 channels]
 #pragma unroll
-        for (int h = 0; h < NCH; ++h)
+        for (int h = 0; h < NS; ++h)
 #pragma unroll
             for (int k = 0; k < 16; ++k) sacc[h][k] = 0.0f;
         uint32_t tcount = 0, sub = 0;
@@ -206,7 +291,17 @@ __global__ void __launch_bounds__(THREADS, 1) k_fx(const __grid_constant__ CUten
             const uint32_t as = tcount & 1, aph = (tcount >> 1) & 1;
             // rows of the patch that are not output pixels are zeroed in the staging tile: the TMA store clips them
             // anyway, and the statistics must not see them
-            const bool row_live = r < p.rows_per_tile && t.w0 + r_w < p.OW && t.h0 + r_h < p.OH && t.n0 + r_n < p.ON;
+            const bool row_live = r_in && t.w0 + r_w < p.OW && t.h0 + r_h < p.OH && t.n0 + r_n < p.ON;
+            // ReLU-mask bits of this thread's 32 channels of every chunk: fetched before the accumulator is waited for
+            uint32_t mbits[NCH];
+#pragma unroll
+            for (int h = 0; h < NCH; ++h) mbits[h] = 0xffffffffu;
+            if (FORK && p.mask && row_live) {
+                const size_t pix = ((size_t)(t.n0 + r_n) * p.OH + (t.h0 + r_h)) * p.OW + (t.w0 + r_w);
+                const uint8_t* mrow = p.mask + pix * (size_t)(p.N >> 3) + ((co0 + hsel * 32) >> 3);
+#pragma unroll
+                for (int h = 0; h < NCH; ++h) mbits[h] = __ldg(reinterpret_cast<const uint32_t*>(mrow + h * 8));
+            }
             mbar_wait(&tmem_full[as], aph);
             fence_after();
             const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + as * BN + (uint32_t)(hsel * 32);
@@ -229,8 +324,26 @@ __global__ void __launch_bounds__(THREADS, 1) k_fx(const __grid_constant__ CUten
                     if (lane == 0) mbar_arrive(&tmem_empty[as]);
                 }
                 epi_bar_sync_n<256>();                         // staging buffer free (leader waited above)
-                if (p.bnb && leader) prefetch_x();      // chunk q + 2: its slot was last read two chunks ago
+                if (aux && leader) prefetch_x();        // chunk q + 2: its slot was last read two chunks ago
                 use_after_wait(v);
+                const uint32_t slot = q_cnt % (uint32_t)p.ncs;
+                if (aux) mbar_wait(&xfull[slot], (q_cnt / (uint32_t)p.ncs) & 1u);
+                if (FORK) {
+                    const uint8_t* arow = smem + p.add_off + slot * SUB_BYTES + r * 128;
+                    const uint32_t mb = mbits[h];
+#pragma unroll
+                    for (int j = 0; j < 4; ++j) {
+                        const uint4 u = *reinterpret_cast<const uint4*>(arow + (((hsel * 4 + j) ^ (r & 7)) * 16));
+                        const uint32_t uw[4] = {u.x, u.y, u.z, u.w};
+#pragma unroll
+                        for (int e = 0; e < 4; ++e) {
+                            const float lo = __uint_as_float(v[j * 8 + 2 * e]) + __uint_as_float(uw[e] << 16);
+                            const float hi = __uint_as_float(v[j * 8 + 2 * e + 1]) + __uint_as_float(uw[e] & 0xffff0000u);
+                            v[j * 8 + 2 * e] = ((mb >> (j * 8 + 2 * e)) & 1u) ? __float_as_uint(lo) : 0u;
+                            v[j * 8 + 2 * e + 1] = ((mb >> (j * 8 + 2 * e + 1)) & 1u) ? __float_as_uint(hi) : 0u;
+                        }
+                    }
+                }
                 if (slow) {
 #pragma unroll
                     for (int e = 0; e < 32; ++e) {
@@ -244,7 +357,7 @@ __global__ void __launch_bounds__(THREADS, 1) k_fx(const __grid_constant__ CUten
 #pragma unroll
                     for (int e = 0; e < 32; ++e) v[e] = 0u;
                 }
-                uint8_t* rowp = cst + r * 128;
+                uint8_t* rowp = cst + dr * 128;
 #pragma unroll
                 for (int j = 0; j < 4; ++j) {           // four 16-byte chunks (8 bf16 each) of this thread's half row
                     uint32_t w[4];
@@ -253,7 +366,7 @@ __global__ void __launch_bounds__(THREADS, 1) k_fx(const __grid_constant__ CUten
                         __nv_bfloat162 hb = __floats2bfloat162_rn(__uint_as_float(v[j * 8 + 2 * e]), __uint_as_float(v[j * 8 + 2 * e + 1]));
                         w[e] = *reinterpret_cast<uint32_t*>(&hb);
                     }
-                    *reinterpret_cast<uint4*>(rowp + (((hsel * 4 + j) ^ (r & 7)) * 16)) = make_uint4(w[0], w[1], w[2], w[3]);
+                    *reinterpret_cast<uint4*>(rowp + (((hsel * 4 + j) ^ (dr & 7)) * 16)) = make_uint4(w[0], w[1], w[2], w[3]);
                 }
                 fence_proxy_async_smem();
                 epi_bar_sync_n<256>();
@@ -261,10 +374,9 @@ __global__ void __launch_bounds__(THREADS, 1) k_fx(const __grid_constant__ CUten
                     if (co0 + h * 64 < p.N) tma_store_4d(&tmC, cst, co0 + h * 64, t.w0, t.h0, t.n0);
                     tma_commit_group();                 // one group per chunk keeps the count in step with the ring
                 }
+                if constexpr (REGSUM) {
                 if (p.bnb) {
                     // batch-norm backward sums over this chunk: dz from the staging tile, x from the prefetched tile
-                    const uint32_t slot = q_cnt % (uint32_t)p.ncs;
-                    mbar_wait(&xfull[slot], (q_cnt / (uint32_t)p.ncs) & 1u);
                     const uint8_t* xs = smem + p.x_off + slot * SUB_BYTES;
                     const int c = et & 7, rg = et >> 3;
                     float fa[8], fb[8];
@@ -297,7 +409,6 @@ __global__ void __launch_bounds__(THREADS, 1) k_fx(const __grid_constant__ CUten
                             sacc[h][2 * e + 1] += d1; sacc[h][8 + 2 * e + 1] = fmaf(d1, x1, sacc[h][8 + 2 * e + 1]);
                         }
                     }
-                    ++q_cnt;
                 } else if (p.stats) {
                     // column sums of the rounded 128 x 64 sub-tile, kept in registers for the whole kernel: thread =
                     // (group of 4 rows, 16-byte chunk of 8 channels); the host sizes the grid so that a CTA always
@@ -316,10 +427,13 @@ __global__ void __launch_bounds__(THREADS, 1) k_fx(const __grid_constant__ CUten
                         }
                     }
                 }
+                }
+                if (aux) ++q_cnt;
                 if (++sub == (uint32_t)p.ncs) sub = 0;
             }
         }
         if (leader) tma_wait_group<0>();
+        if constexpr (REGSUM) {
         if (p.stats) {
             // once per kernel: row groups of a warp by shuffles, the eight warps through shared memory (the staging
             // ring is free now) in a fixed order, then one partial row [2][N] per CTA (zero outside its BN channels)
@@ -355,12 +469,13 @@ __global__ void __launch_bounds__(THREADS, 1) k_fx(const __grid_constant__ CUten
                 o[i] = tot;
             }
         }
+        }
     }
     fence_before();
     __syncthreads();
     if (warp == 1) {
         __syncwarp();
-        tmem_dealloc<2 * BN>(tmem_base);
+        tmem_dealloc<TCOLS>(tmem_base);
     }
 }
 
@@ -700,17 +815,19 @@ struct FxGeom {
     const float* bias; int relu; float* stats; int bn_hint;
     // batch-norm backward sums (see FxParams::bnb): x = the batch norm's input, same shape and layout as the output
     const void* bnx; const float *bn_gamma, *bn_beta, *bn_mean, *bn_invstd; int bnb_relu;
+    // residual fork (see FxParams::add): addend has the output's shape and layout, mask is [pixels][Cout / 8] bytes or NULL
+    const void* addend; const void* mask;
 };
 
-template <int BN, bool B_MN>
-int launch_fx(const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMap& tc_, const CUtensorMap& tx, const FxParams& p, int smem,
-              int grid, cudaStream_t st) {
+template <int BN, bool B_MN, bool FORK, bool REGSUM, bool TWO = false>
+int launch_fx(const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMap& tc_, const CUtensorMap& tx, const CUtensorMap& td,
+              const FxParams& p, int smem, int grid, cudaStream_t st) {
     static bool attr = false;
     if (!attr) {
-        LWC_CUDA_CHECK(cudaFuncSetAttribute(k_fx<BN, B_MN>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BUDGET));
+        LWC_CUDA_CHECK(cudaFuncSetAttribute(k_fx<BN, B_MN, FORK, REGSUM, TWO>, cudaFuncAttributeMaxDynamicSharedMemorySize, TWO ? SMEM_BUDGET / 2 - 1024 : SMEM_BUDGET));
         attr = true;
     }
-    k_fx<BN, B_MN><<<grid, THREADS, smem, st>>>(ta, tb, tc_, tx, p);
+    k_fx<BN, B_MN, FORK, REGSUM, TWO><<<grid, THREADS, smem, st>>>(ta, tb, tc_, tx, td, p);
     return 0;
 }
 
@@ -721,41 +838,92 @@ int pick_bn(int Cout, int hint) {
     return 64;
 }
 
+// Halo mode is asked for with bn_hint = 1000 + BN (ops/conv.py times it against the per-tap variants).
+bool halo_ok(const FxGeom& g, int* span_w, int* span_h, int* dw0, int* dh0) {
+    if (g.kchunks != 1 || g.window || g.stride != 1 || g.ntaps < 2 || g.addend) return false;
+    int lo_w = g.dw[0], hi_w = g.dw[0], lo_h = g.dh[0], hi_h = g.dh[0];
+    for (int t = 1; t < g.ntaps; ++t) {
+        if (g.a_c0[t] != g.a_c0[0]) return false;
+        lo_w = g.dw[t] < lo_w ? g.dw[t] : lo_w; hi_w = g.dw[t] > hi_w ? g.dw[t] : hi_w;
+        lo_h = g.dh[t] < lo_h ? g.dh[t] : lo_h; hi_h = g.dh[t] > hi_h ? g.dh[t] : hi_h;
+    }
+    *span_w = hi_w - lo_w + 1; *span_h = hi_h - lo_h + 1; *dw0 = lo_w; *dh0 = lo_h;
+    return *span_w <= 5 && *span_h <= 5;
+}
+
 int run_fx(const FxGeom& g, cudaStream_t st, int* grid_out) {
     if (g.Cout % 64 || g.ntaps < 1 || g.ntaps > MAXT || g.kchunks < 1) return LWC_EINVAL;
     ensure_context();
-    int BN = pick_bn(g.Cout, g.bn_hint);
-    if (g.bnx && BN == 256) BN = 128;        // the x-tile ring takes the shared memory of one 256-wide operand stage
+    // bn_hint = BN + 1000 (halo variant) + 2000 (two CTAs per SM)
+    const bool want_halo = (g.bn_hint / 1000) & 1;
+    const bool two = (g.bn_hint / 1000) & 2;
+    int BN = pick_bn(g.Cout, g.bn_hint % 1000);
+    if ((g.bnx || g.addend) && BN == 256) BN = 128;   // the auxiliary rings take the shared memory of a 256-wide operand stage
     if (g.bnx && !g.stats) return LWC_EINVAL;
+    if (g.mask && !g.addend) return LWC_EINVAL;
     FxParams p;
     memset(&p, 0, sizeof(p));
-    const Patch pt = pick_patch(g.OW, g.OH, g.ON, BM, 1, 256 / g.stride);
+    int span_w = 1, span_h = 1, dw0 = 0, dh0 = 0;
+    const bool halo = want_halo && halo_ok(g, &span_w, &span_h, &dw0, &dh0);
+    if (want_halo && !halo) return LWC_EINVAL;
+    Patch pt;
+    if (halo) {
+        // accumulator rows = 8 box rows x 16 box columns; the last span_w - 1 columns of every row are overhang
+        pt.Wb = HALO_PW - (span_w - 1); pt.Hb = BM / HALO_PW; pt.Nb = 1; pt.rows = pt.Wb * pt.Hb;
+        pt.tiles_w = (g.OW + pt.Wb - 1) / pt.Wb; pt.tiles_h = (g.OH + pt.Hb - 1) / pt.Hb; pt.tiles_n = g.ON;
+        if (BN == 256) BN = 128;
+    } else {
+        pt = pick_patch(g.OW, g.OH, g.ON, BM, 1, 256 / g.stride);
+    }
     p.N = g.Cout; p.ntaps = g.ntaps; p.kchunks = g.kchunks;
     p.Wb = pt.Wb; p.Hb = pt.Hb; p.Nb = pt.Nb; p.tiles_w = pt.tiles_w; p.tiles_h = pt.tiles_h;
     p.sw = g.stride; p.sh = g.stride; p.OW = g.OW; p.OH = g.OH; p.ON = g.ON;
     p.tiles_m = pt.tiles_w * pt.tiles_h * pt.tiles_n; p.tiles_n = g.Cout / BN; p.rows_per_tile = pt.rows;
     p.relu = g.relu; p.bias = g.bias; p.stats = g.stats;
     for (int t = 0; t < g.ntaps; ++t) { p.dw[t] = g.dw[t]; p.dh[t] = g.dh[t]; p.a_c0[t] = g.a_c0[t]; p.b_k0[t] = g.b_k0[t]; p.b_n0[t] = g.b_n0[t]; }
-    // shared-memory plan
-    const int stage_bytes = BM * BK * 2 + BN * BK * 2;
-    const int stat_bytes = 0;       // statistics live in registers; their final reduction reuses the staging ring
-    int ncs = 4;
-    const int rings = g.bnx ? 2 : 1;         // staging ring (+ x-tile ring of the same depth)
-    const int fixed = 1024 + 256 + stat_bytes;
-    int stages = (SMEM_BUDGET - fixed - rings * ncs * SUB_BYTES) / stage_bytes;
-    if (stages < 3) {
-        ncs = g.bnx ? 3 : 2;                 // the x prefetch runs two chunks ahead: it needs >= 3 slots
-        stages = (SMEM_BUDGET - fixed - rings * ncs * SUB_BYTES) / stage_bytes;
+    // shared-memory plan: [operand ring | resident weights + halo ring][staging ring][x ring][addend ring][barriers]
+    const int rings = 1 + (g.bnx ? 1 : 0) + (g.addend ? 1 : 0);
+    const bool aux = rings > 1;
+    const bool regsum = g.stats != nullptr;  // the variant with per-channel sums in registers
+    const int fixed = 1024 + 256;
+    if (two && (BN == 256 || g.addend || g.bnx || (BN == 128 && regsum))) return LWC_EINVAL;
+    const int budget = two ? SMEM_BUDGET / 2 - 1024 : SMEM_BUDGET;
+    int ncs = two ? 2 : 4, stages = 0, operand_bytes = 0;
+    const int halo_rows = BM / HALO_PW + span_h - 1;
+    if (halo) {
+        const int w_bytes = g.ntaps * BN * BK * 2;
+        // the shifted reads of the last tap run (span_h - 1) * 16 + span_w - 1 rows past the 128th row of the box
+        const int a_stage = ((BM + (span_h - 1) * HALO_PW + span_w) * 128 + 1023) / 1024 * 1024;
+        if (aux) ncs = 3;
+        stages = (budget - fixed - w_bytes - rings * ncs * SUB_BYTES) / a_stage;
+        if (stages < 2 && !aux) { ncs = 2; stages = (budget - fixed - w_bytes - rings * ncs * SUB_BYTES) / a_stage; }
+        if (stages > 8) stages = 8;
+        if (stages < 2) return LWC_ETOOBIG;
+        p.halo = 1; p.halo_dw0 = dw0; p.halo_dh0 = dh0; p.a_off = w_bytes; p.a_stage = a_stage;
+        p.halo_bytes = HALO_PW * halo_rows * 128;
+        const char* bo = getenv("LWC_HALO_BO");
+        p.halo_bo = bo ? atoi(bo) : 0;
+        operand_bytes = w_bytes + stages * a_stage;
+    } else {
+        const int stage_bytes = BM * BK * 2 + BN * BK * 2;
+        stages = (budget - fixed - rings * ncs * SUB_BYTES) / stage_bytes;
+        if (stages < 3) {
+            ncs = aux ? 3 : 2;                   // the auxiliary prefetch runs two chunks ahead: it needs >= 3 slots
+            stages = (budget - fixed - rings * ncs * SUB_BYTES) / stage_bytes;
+        }
+        if (stages > 8) stages = 8;
+        if (stages < 2) return LWC_ETOOBIG;
+        operand_bytes = stages * stage_bytes;
     }
-    if (stages > 8) stages = 8;
-    if (stages < 2) return LWC_ETOOBIG;
     p.stages = stages; p.ncs = ncs;
-    p.c_off = stages * stage_bytes;
+    p.c_off = operand_bytes;
     p.x_off = p.c_off + ncs * SUB_BYTES;
-    p.stat_off = p.x_off + (g.bnx ? ncs * SUB_BYTES : 0);
-    p.bar_off = p.stat_off + stat_bytes;
+    p.add_off = p.x_off + (g.bnx ? ncs * SUB_BYTES : 0);
+    p.stat_off = p.add_off + (g.addend ? ncs * SUB_BYTES : 0);
+    p.bar_off = p.stat_off;
     p.bnb = g.bnx ? 1 : 0; p.bnb_relu = g.bnb_relu;
     p.bn_gamma = g.bn_gamma; p.bn_beta = g.bn_beta; p.bn_mean = g.bn_mean; p.bn_invstd = g.bn_invstd;
+    p.add = g.addend ? 1 : 0; p.mask = static_cast<const uint8_t*>(g.mask);
     const int smem = p.bar_off + 256 + 1024;
 
     CUtensorMap ta, tb, tc_;
@@ -766,6 +934,8 @@ int run_fx(const FxGeom& g, cudaStream_t st, int* grid_out) {
         cuuint64_t gs[3] = {(cuuint64_t)g.wpitch * 2, (cuuint64_t)g.cpitch * 2, (cuuint64_t)g.H * g.cpitch * 2};
         cuuint32_t bx[4] = {64, (cuuint32_t)pt.Wb, (cuuint32_t)pt.Hb, (cuuint32_t)pt.Nb};
         rc = encode(&ta, g.x, 4, gd, gs, bx, nullptr);
+    } else if (halo) {
+        rc = encode_act(&ta, g.x, g.C, g.cpitch, g.W, g.H, g.N, HALO_PW, halo_rows, 1, 1);
     } else {
         rc = encode_act(&ta, g.x, g.C, g.cpitch, g.W, g.H, g.N, pt.Wb, pt.Hb, pt.Nb, g.stride);
     }
@@ -781,31 +951,55 @@ int run_fx(const FxGeom& g, cudaStream_t st, int* grid_out) {
         rc = encode(&tb, g.w, 2, bd, bs, bb, nullptr);
     }
     if (rc) return rc;
-    {
+    // output-shaped maps: the output itself, the batch norm's input, the addend
+    auto encode_out = [&](CUtensorMap* m, const void* ptr) {
         cuuint64_t cd[4] = {(cuuint64_t)g.Cout, (cuuint64_t)g.OW, (cuuint64_t)g.OH, (cuuint64_t)g.ON};
         cuuint64_t cs[3] = {(cuuint64_t)g.y_wpitch * 2, (cuuint64_t)g.y_hpitch * 2, (cuuint64_t)g.y_npitch * 2};
         cuuint32_t cb[4] = {64, (cuuint32_t)pt.Wb, (cuuint32_t)pt.Hb, (cuuint32_t)pt.Nb};
-        rc = encode(&tc_, g.y, 4, cd, cs, cb, nullptr);
-        if (rc) return rc;
-    }
-    CUtensorMap tx = tc_;
+        return encode(m, ptr, 4, cd, cs, cb, nullptr);
+    };
+    rc = encode_out(&tc_, g.y);
+    if (rc) return rc;
+    CUtensorMap tx = tc_, td = tc_;
     if (g.bnx) {
         if (!g.bn_mean || !g.bn_invstd) return LWC_EINVAL;
-        cuuint64_t cd[4] = {(cuuint64_t)g.Cout, (cuuint64_t)g.OW, (cuuint64_t)g.OH, (cuuint64_t)g.ON};
-        cuuint64_t cs[3] = {(cuuint64_t)g.y_wpitch * 2, (cuuint64_t)g.y_hpitch * 2, (cuuint64_t)g.y_npitch * 2};
-        cuuint32_t cb[4] = {64, (cuuint32_t)pt.Wb, (cuuint32_t)pt.Hb, (cuuint32_t)pt.Nb};
-        rc = encode(&tx, g.bnx, 4, cd, cs, cb, nullptr);
+        rc = encode_out(&tx, g.bnx);
+        if (rc) return rc;
+    }
+    if (g.addend) {
+        rc = encode_out(&td, g.addend);
         if (rc) return rc;
     }
     int grid = p.tiles_m * p.tiles_n;
-    if (grid > sm_count()) grid = sm_count();
-    // with statistics a CTA must stay on one column of output-channel tiles (tile = mt * tiles_n + nt, stride = grid)
-    if (g.stats && grid % p.tiles_n) grid = grid > p.tiles_n ? grid / p.tiles_n * p.tiles_n : p.tiles_n;
-    if (g.stats && p.tiles_n > sm_count()) return LWC_ETOOBIG;
+    const int max_grid = sm_count() * (two ? 2 : 1);
+    if (grid > max_grid) grid = max_grid;
+    // with statistics (and with resident weights) a CTA must stay on one column of output-channel tiles
+    // (tile = mt * tiles_n + nt, stride = grid)
+    const bool pinned = g.stats || halo;
+    if (pinned && grid % p.tiles_n) grid = grid > p.tiles_n ? grid / p.tiles_n * p.tiles_n : p.tiles_n;
+    if (pinned && p.tiles_n > sm_count()) return LWC_ETOOBIG;
     if (grid_out) *grid_out = grid;
-    if (BN == 256) rc = g.b_mn ? launch_fx<256, true>(ta, tb, tc_, tx, p, smem, grid, st) : launch_fx<256, false>(ta, tb, tc_, tx, p, smem, grid, st);
-    else if (BN == 128) rc = g.b_mn ? launch_fx<128, true>(ta, tb, tc_, tx, p, smem, grid, st) : launch_fx<128, false>(ta, tb, tc_, tx, p, smem, grid, st);
-    else rc = g.b_mn ? launch_fx<64, true>(ta, tb, tc_, tx, p, smem, grid, st) : launch_fx<64, false>(ta, tb, tc_, tx, p, smem, grid, st);
+#define LWC_FX(BN_, MN_, FK_, RS_) launch_fx<BN_, MN_, FK_, RS_>(ta, tb, tc_, tx, td, p, smem, grid, st)
+#define LWC_FX2(BN_, MN_, RS_) launch_fx<BN_, MN_, false, RS_, true>(ta, tb, tc_, tx, td, p, smem, grid, st)
+    if (two) {
+        if (BN == 128) rc = g.b_mn ? LWC_FX2(128, true, false) : LWC_FX2(128, false, false);
+        else if (regsum) rc = g.b_mn ? LWC_FX2(64, true, true) : LWC_FX2(64, false, true);
+        else rc = g.b_mn ? LWC_FX2(64, true, false) : LWC_FX2(64, false, false);
+    } else if (g.addend) {
+        // the fork variant exists for the MN-major weight (data gradients) and 64- / 128-wide tiles only
+        if (!g.b_mn) return LWC_EINVAL;
+        rc = BN == 128 ? LWC_FX(128, true, true, true) : LWC_FX(64, true, true, true);
+    } else if (regsum) {
+        if (BN == 256) rc = g.b_mn ? LWC_FX(256, true, false, true) : LWC_FX(256, false, false, true);
+        else if (BN == 128) rc = g.b_mn ? LWC_FX(128, true, false, true) : LWC_FX(128, false, false, true);
+        else rc = g.b_mn ? LWC_FX(64, true, false, true) : LWC_FX(64, false, false, true);
+    } else {
+        if (BN == 256) rc = g.b_mn ? LWC_FX(256, true, false, false) : LWC_FX(256, false, false, false);
+        else if (BN == 128) rc = g.b_mn ? LWC_FX(128, true, false, false) : LWC_FX(128, false, false, false);
+        else rc = g.b_mn ? LWC_FX(64, true, false, false) : LWC_FX(64, false, false, false);
+    }
+#undef LWC_FX
+#undef LWC_FX2
     if (rc) return rc;
     return (int)cudaGetLastError();
 }
@@ -813,7 +1007,7 @@ int run_fx(const FxGeom& g, cudaStream_t st, int* grid_out) {
 }  // namespace
 
 // Number of per-CTA statistics partials a forward call may write (callers size the buffer [this][2][Cout]).
-extern "C" int lwc_convx_max_partials(void) { return sm_count(); }
+extern "C" int lwc_convx_max_partials(void) { return 2 * sm_count(); }   // two CTAs per SM in the densest variant
 
 // Forward convolution, square kernel k (k * k <= 16), stride 1 or 2, symmetric padding `pad`.
 //   x    : [N][H][W][Cx] bf16 channels-last; Cx % 8 == 0 (3-channel inputs are stored with 8 channels)
@@ -951,6 +1145,29 @@ extern "C" int lwc_convx_dgrad_bnstats(const void* dy, const void* wt, void* dx,
             }
         g.ntaps = n;
     }
+    return run_fx(g, (cudaStream_t)stream, nparts_out);
+}
+
+// Residual fork: data gradient of the block's first 1x1 convolution with the skip connection's gradient added and the
+// producing batch norm's ReLU mask applied in the epilogue,  dX = mask * (dY W + addend),  W the forward weight as stored
+// ([Cout][Cin], MN-major B operand).  dX is then the gradient of that batch norm's (pre-masked) output AND of its
+// residual input; with x_bn (that batch norm's input) the launch also sums S1 = sum dX, S2 = sum dX * x per channel
+// into per-CTA partials for lwc_bn_backward_from_partials (relu = 0: the mask is already in dX).
+//   dy [M][Cout], addend / dx / x_bn [M][Cin] bf16; mask [M][Cin / 8] bytes (bit j of byte b = channel 8 b + j) or NULL
+extern "C" int lwc_convx_dgrad1x1_fork(const void* dy, const void* w, const void* addend, const void* mask, void* dx, long long M,
+                                       int Cout, int Cin, const void* x_bn, const float* mean, const float* invstd, float* partials,
+                                       int* nparts_out, int bn_hint, void* stream) {
+    if (!dy || !w || !addend || !dx || M <= 0 || M > 0x7fffffffLL || (Cout % 64) || (Cin % 64)) return LWC_EINVAL;
+    if (x_bn && (!mean || !invstd || !partials)) return LWC_EINVAL;
+    FxGeom g;
+    memset(&g, 0, sizeof(g));
+    g.x = dy; g.C = Cout; g.cpitch = Cout; g.W = (int)M; g.H = 1; g.N = 1;
+    g.w = w; g.Ktot = Cout; g.b_mn = 1;
+    g.y = dx; g.OW = (int)M; g.OH = 1; g.ON = 1; g.Cout = Cin;
+    g.y_wpitch = Cin; g.y_hpitch = M * Cin; g.y_npitch = M * Cin;
+    g.stride = 1; g.ntaps = 1; g.kchunks = Cout / 64; g.bn_hint = bn_hint;
+    g.addend = addend; g.mask = mask;
+    if (x_bn) { g.stats = partials; g.bnx = x_bn; g.bn_mean = mean; g.bn_invstd = invstd; g.bnb_relu = 0; }
     return run_fx(g, (cudaStream_t)stream, nparts_out);
 }
 

@@ -58,7 +58,7 @@ def _ptr(t):
 
 
 class _BatchNormAct(torch.autograd.Function):
-    last_mask = (None, None)      # (bit mask, taken-flag) of the most recent forward, picked up by batch_norm_act
+    last_mask = (None, None, None)      # (bit mask, taken-flag, link) of the most recent forward, picked up by batch_norm_act
 
     @staticmethod
     def forward(ctx, x, weight, bias, running_mean, running_var, residual, training, momentum, eps, relu,
@@ -106,7 +106,11 @@ class _BatchNormAct(torch.autograd.Function):
         need_y = relu and (residual is not None or not training) and mask is None
         # a consumer (ops.conv.fork_conv1x1) may take over the masking of the incoming gradient: it flips taken[0]
         ctx.mask_taken = [False] if mask is not None else None
-        _BatchNormAct.last_mask = (mask, ctx.mask_taken)
+        # ... and may then also sum this layer's backward reductions over the gradient it produces (fork_link['partials'])
+        ctx.fork_link = None
+        if mask is not None and x.dim() == 4 and x.dtype == torch.bfloat16:
+            ctx.fork_link = {"x": x, "mean": mean, "invstd": invstd}
+        _BatchNormAct.last_mask = (mask, ctx.mask_taken, ctx.fork_link)
         if training:
             ctx.save_for_backward(x, y if need_y else None, weight, mean, invstd, bias, mask)
         else:
@@ -147,6 +151,20 @@ class _BatchNormAct(torch.autograd.Function):
                     None, None, None, None, None, None, None, None, None, None)
         dx = torch.empty_like(x)
         premasked = ctx.mask_taken is not None and ctx.mask_taken[0]
+        flink = getattr(ctx, "fork_link", None)
+        if premasked and flink is not None and "partials" in flink:
+            # the fork's data-gradient kernel produced dy (mask applied) and summed it: finalize + apply only
+            part, nparts = flink.pop("partials")
+            dgamma = torch.empty(Cc, dtype=torch.float32, device=x.device)
+            dbeta = torch.empty(Cc, dtype=torch.float32, device=x.device)
+            st = torch.cuda.current_stream().cuda_stream
+            rc = lib.lwc_bn_backward_from_partials(dy.data_ptr(), x.data_ptr(), dx.data_ptr(), _ptr(weight), _ptr(bias),
+                                                   mean.data_ptr(), invstd.data_ptr(), dgamma.data_ptr(), dbeta.data_ptr(),
+                                                   part.data_ptr(), int(nparts), M, Cc, abi.dtype_code(x.dtype), 0, C.c_void_p(st))
+            abi.check(rc, "lwc_bn_backward_from_partials")
+            _native.counters.add(2)
+            return (dx, dgamma if weight is not None else None, dbeta if weight is not None else None, None, None,
+                    dy if ctx.has_res else None, None, None, None, None, None, None, None, None, None)
         if premasked:
             # the consumer's backward already multiplied dy with this layer's ReLU mask: no mask to read, and the
             # gradient of the residual branch IS dy -- nothing to write
@@ -173,7 +191,7 @@ def batch_norm_act(x, weight, bias, running_mean, running_var, residual=None, tr
                    momentum=0.1, eps=1e-5, relu=False, num_batches_tracked=None, stats=None, fuse_bwd=False):
     """``relu?(batch_norm(x) + residual?)`` in one fused pass structure (see module docstring).
     ``num_batches_tracked`` (int64 CUDA scalar) is incremented inside the statistics-finalize kernel."""
-    _BatchNormAct.last_mask = (None, None)
+    _BatchNormAct.last_mask = (None, None, None)
     link = {} if (fuse_bwd and training and residual is None and torch.is_grad_enabled()) else None
     if stats is not None and training:
         y = _BatchNormAct.apply(x, weight, bias, running_mean, running_var, residual, training, momentum, eps, relu,
@@ -183,10 +201,10 @@ def batch_norm_act(x, weight, bias, running_mean, running_var, residual=None, tr
                                 num_batches_tracked, None, 0, 0, link)
     if link:
         y.bn_link = link               # picked up by the consuming ops.nn.Conv2d
-    mask, taken = _BatchNormAct.last_mask
+    mask, taken, flink = _BatchNormAct.last_mask
     if mask is not None:
-        y.relu_mask, y.relu_mask_taken = mask, taken       # see ops.conv.fork_conv1x1
-        _BatchNormAct.last_mask = (None, None)
+        y.relu_mask, y.relu_mask_taken, y.relu_mask_link = mask, taken, flink       # see ops.conv.fork_conv1x1
+        _BatchNormAct.last_mask = (None, None, None)
     return y
 
 

@@ -48,6 +48,27 @@ def _candidates(cout: int):
     return [b for b in (64, 128, 256) if cout % b == 0] or [64]
 
 
+_HALO = {"on": os.environ.get("LWC_CONV_HALO", "1") != "0"}
+
+
+def _halo_candidates(kdim: int, nout: int, k: int, stride: int):
+    """Extra tile hints (1000 + width) that select the halo variant of the kernel: K dimension of one 64-channel chunk,
+    stride 1, several taps -- resident weights and one input box per tile instead of one per tap."""
+    if not _HALO["on"] or kdim > 64 or k < 2 or k * k > 16 or stride != 1:
+        return []
+    return [1000 + b for b in (64, 128) if nout % b == 0]
+
+
+_TWO = {"on": os.environ.get("LWC_CONV_TWO", "1") != "0"}
+
+
+def _two_candidates(nout: int, sums: bool):
+    """Tile hints 2000 + width: the variant compiled for two resident CTAs per SM (64-wide tiles; 128-wide without sums)."""
+    if not _TWO["on"]:
+        return []
+    return [2000 + b for b in ((64,) if sums else (64, 128)) if nout % b == 0]
+
+
 def _tuned(key: tuple, cout: int, run, cands=None) -> int:
     """``run(bn_hint)`` launches the kernel; returns the fastest hint for ``key`` (cached)."""
     hint = _TUNE.get(key)
@@ -58,7 +79,10 @@ def _tuned(key: tuple, cout: int, run, cands=None) -> int:
         return 0
     best, best_t = 0, float("inf")
     for b in cands:
-        run(b)                                      # warm-up (also sets the kernel's shared-memory attribute)
+        try:
+            run(b)                                  # warm-up (also sets the kernel's shared-memory attribute)
+        except RuntimeError:                        # a variant that does not fit this shape
+            continue
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         e0.record()
         for _ in range(3):
@@ -153,7 +177,8 @@ def conv_forward(x: torch.Tensor, weight: torch.Tensor, bias: Optional[torch.Ten
         abi.check(rc, "lwc_convx_forward")
 
     if bn_hint is None:
-        bn_hint = _tuned(("f", n, h, w, cx, co, k, stride, pad, want_stats), co, run)
+        bn_hint = _tuned(("f", n, h, w, cx, co, k, stride, pad, want_stats), co, run,
+                         _candidates(co) + _halo_candidates(cx, co, k, stride) + _two_candidates(co, want_stats))
     run(bn_hint)
     _native.counters.add(1)
     return y, (Stats(part, int(nparts.value), n * oh * ow) if want_stats else None)
@@ -185,7 +210,8 @@ def conv_dgrad(dy: torch.Tensor, weight: torch.Tensor, in_hw: Tuple[int, int], s
                                           _stream()), "lwc_convx_dgrad")
         nl = stride * stride
     if bn_hint is None:
-        bn_hint = _tuned(("d", n, h, w, ci, co, k, stride, pad), ci, run)
+        bn_hint = _tuned(("d", n, h, w, ci, co, k, stride, pad), ci, run,
+                         _candidates(ci) + _halo_candidates(co, ci, k, stride) + (_two_candidates(ci, False) if stride == 1 else []))
     run(bn_hint)
     _native.counters.add(nl)
     return dx
@@ -216,7 +242,8 @@ def conv_dgrad_bnstats(dy: torch.Tensor, weight: torch.Tensor, in_hw: Tuple[int,
                   "lwc_convx_dgrad_bnstats")
 
     if bn_hint is None:
-        bn_hint = _tuned(("db", n, h, w, ci, co, k, padding), ci, run, [b for b in (64, 128) if ci % b == 0])
+        bn_hint = _tuned(("db", n, h, w, ci, co, k, padding), ci, run,
+                         [b for b in (64, 128) if ci % b == 0] + _halo_candidates(co, ci, k, 1))
     run(bn_hint)
     _native.counters.add(1)
     link["partials"] = (part, int(nparts.value))
@@ -360,14 +387,45 @@ def maybe_conv2d(module, x, relu: bool = False):
 
 
 # ---- residual fork: conv1x1(x) and the identity branch share one fused backward --------------------------------
+# the k_fx fork variant (addend + mask + bn3 backward sums in one launch) is numerically validated but measures slower than
+# the older fork kernel + separate reduction (profiles/halo_probe_r2.json): opt-in
+_FORK_NEW = {"on": os.environ.get("LWC_FORK_NEW", "0") == "1"}
+
+
 def conv1x1_dgrad_add(dy: torch.Tensor, weight: torch.Tensor, addend: torch.Tensor,
-                      relu_mask: Optional[torch.Tensor] = None) -> torch.Tensor:
+                      relu_mask: Optional[torch.Tensor] = None, link: Optional[dict] = None,
+                      bn_hint: Optional[int] = None) -> torch.Tensor:
     """``dX = dY * W + addend`` in one pass of the native kernel (W = forward weight ``[Cout, Cin, 1, 1]``); with
-    ``relu_mask`` (the bit mask a fused batch-norm wrote for the tensor ``X``) also ``dX *= mask``."""
+    ``relu_mask`` (the bit mask a fused batch-norm wrote for the tensor ``X``) also ``dX *= mask``.  With ``link`` (left by
+    that batch norm, see ``ops/bn.py``) the same launch sums the batch norm's backward reductions over ``dX`` and its
+    input into ``link['partials']``."""
     lib = _native.lib()
     n, co, h, w = dy.shape
     ci = weight.shape[1]
     dx = torch.empty((n, ci, h, w), dtype=dy.dtype, device=dy.device, memory_format=torch.channels_last)
+    if _FORK_NEW["on"] and _ENABLED["on"]:
+        wv = weight.detach().reshape(co, ci).contiguous()
+        use_link = link is not None and relu_mask is not None and _FUSE_BNB["on"] and link["x"].shape == dx.shape
+        part, nparts = None, C.c_int(0)
+        if use_link:
+            part = torch.empty((int(lib.lwc_convx_max_partials()), 2, ci), dtype=torch.float32, device=dy.device)
+
+        def run(hint):
+            abi.check(lib.lwc_convx_dgrad1x1_fork(dy.data_ptr(), wv.data_ptr(), addend.data_ptr(),
+                                                  0 if relu_mask is None else relu_mask.data_ptr(), dx.data_ptr(), n * h * w, co, ci,
+                                                  link["x"].data_ptr() if use_link else 0,
+                                                  link["mean"].data_ptr() if use_link else 0,
+                                                  link["invstd"].data_ptr() if use_link else 0,
+                                                  0 if part is None else part.data_ptr(), C.byref(nparts), hint, _stream()),
+                      "lwc_convx_dgrad1x1_fork")
+
+        if bn_hint is None:
+            bn_hint = _tuned(("k", n, h, w, ci, co, relu_mask is not None, use_link), ci, run, [b for b in (64, 128) if ci % b == 0])
+        run(bn_hint)
+        _native.counters.add(1)
+        if use_link:
+            link["partials"] = (part, int(nparts.value))
+        return dx
     if relu_mask is not None:
         rc = lib.lwc_conv1x1_add_mask(dy.data_ptr(), weight.data_ptr(), addend.data_ptr(), relu_mask.data_ptr(), dx.data_ptr(),
                                       n, h, w, co, ci, 1, _stream())
@@ -394,8 +452,9 @@ class _ForkConv1x1(torch.autograd.Function):
     gradient runs on the tcgen05 kernel whose epilogue adds the skip-connection gradient on the way out."""
 
     @staticmethod
-    def forward(ctx, x, weight, relu_mask=None, want_stats=False):
+    def forward(ctx, x, weight, relu_mask=None, want_stats=False, link=None):
         ctx.save_for_backward(x, weight, relu_mask)
+        ctx.link = link
         if _ENABLED["on"]:
             y, stats = conv_forward(x, weight, want_stats=want_stats, stride=1, padding=0)
             _ConvFn.last_stats = stats
@@ -411,7 +470,7 @@ class _ForkConv1x1(torch.autograd.Function):
             dy = dy.contiguous(memory_format=torch.channels_last)
         if ctx.needs_input_grad[0]:
             if d_identity is not None and _nhwc(d_identity) and d_identity.dtype == dy.dtype:
-                dx = conv1x1_dgrad_add(dy, weight, d_identity, relu_mask)
+                dx = conv1x1_dgrad_add(dy, weight, d_identity, relu_mask, ctx.link)
             else:
                 dx = conv_dgrad(dy, weight, (x.shape[2], x.shape[3]), 1, 0)
                 if d_identity is not None:
@@ -424,7 +483,7 @@ class _ForkConv1x1(torch.autograd.Function):
             else:
                 dw = torch.ops.aten.convolution_backward(dy, x, weight, None, [1, 1], [0, 0], [1, 1], False, [0, 0], 1,
                                                          [False, True, False])[1]
-        return dx, dw, None, None
+        return dx, dw, None, None, None
 
 
 def fork_conv1x1(module, x):
@@ -447,9 +506,9 @@ def fork_conv1x1(module, x):
     _ConvFn.last_stats = None
     if mask is not None and taken is not None and w.shape[1] % 128 == 0 and not os.environ.get("LWC_NO_PREMASK"):
         taken[0] = True
-        y, ident = _ForkConv1x1.apply(x, w, mask, want)
+        y, ident = _ForkConv1x1.apply(x, w, mask, want, getattr(x, "relu_mask_link", None))
     else:
-        y, ident = _ForkConv1x1.apply(x, w, None, want)
+        y, ident = _ForkConv1x1.apply(x, w, None, want, None)
     stats, _ConvFn.last_stats = _ConvFn.last_stats, None
     if stats is not None:
         y.bn_stats = stats
