@@ -474,9 +474,9 @@ __device__ void group_step(const DevPlan& p, int g, int mode, unsigned long long
 __device__ void group_tail(const DevPlan& p, int group, int phase, int mode) {
     __shared__ unsigned long long sh_tail_scan[kThreads / 32 + 1];
     __shared__ int s_last;
-    __threadfence();
     __syncthreads();
     if (threadIdx.x == 0) {
+        __threadfence();                        // one cumulative fence per CTA (the barrier ordered the CTA's writes before it)
         const GroupCfg& cfg = p.gcfg[group];
         const unsigned nchunks = (unsigned)(cfg.chunk_end - cfg.chunk_begin);
         s_last = atomicAdd(&p.gstate[group].ticket[phase], 1u) == nchunks - 1 ? 1 : 0;
@@ -535,9 +535,12 @@ __global__ void __launch_bounds__(kThreads) k_count(DevPlan p) {
 // threads of every CTA of the sending kernel after their payload stores.
 __device__ __forceinline__ void publish_when_last(const DevPlan& p) {
     if (p.direct_idx) return;
-    __threadfence_system();
+    // The CTA barrier orders every thread's payload stores before thread 0's fence; the fence is cumulative, so ONE
+    // system-scope fence per CTA publishes them all (a fence in every thread cost a third of k_compact_send's time:
+    // 841 k membar.sys for 3288 CTAs, profiles/ncu_exchange_r2.csv).
     __syncthreads();
     if (threadIdx.x == 0) {
+        __threadfence_system();
         const unsigned ticket = atomicAdd(&p.counters->done, 1u);
         if (ticket == gridDim.x - 1) {
             __threadfence_system();
@@ -549,7 +552,7 @@ __device__ __forceinline__ void publish_when_last(const DevPlan& p) {
 
 // ---- ordered compaction + residual update + stores to every rank ---------------------------------------
 template <typename GradT>
-__global__ void __launch_bounds__(kThreads) k_compact_send(DevPlan p) {
+__global__ void __launch_bounds__(kThreads, 3) k_compact_send(DevPlan p) {
     if (p.step_ptr) p.step = *p.step_ptr;
     __shared__ uint32_t st_idx[kStage];
     __shared__ float st_val[kStage];
@@ -596,13 +599,18 @@ __global__ void __launch_bounds__(kThreads) k_compact_send(DevPlan p) {
     unsigned fl[kIters], excl[kIters];
     if (n_out > 0) {
         unsigned run_base = 0;        // packed (gt | eq << 16) count of this warp before iteration `it`
+        // all eight loads of the warp's range go out before the first key is computed (the kernel is latency-bound)
 #pragma unroll
         for (int it = 0; it < kIters; ++it) {
             const int j = warp * kPerWarp + it * 128 + lane * 4;
             v[it][0] = v[it][1] = v[it][2] = v[it][3] = 0.0f;
+            if (j < c.len) load_acc<GradT>(t, c.start, j, c.len, v[it]);
+        }
+#pragma unroll
+        for (int it = 0; it < kIters; ++it) {
+            const int j = warp * kPerWarp + it * 128 + lane * 4;
             unsigned f = 0;           // bit k: key > T, bit 4+k: key == T
             if (j < c.len) {
-                load_acc<GradT>(t, c.start, j, c.len, v[it]);
 #pragma unroll
                 for (int k = 0; k < 4; ++k) {
                     if (j + k >= c.len || (v[it][k] == 0.0f && !p.values_only)) continue;
@@ -1558,9 +1566,9 @@ __global__ void __launch_bounds__(512) k_allreduce_two_shot(DevAR p) {
         for (int d = 0; d < LWC_MAX_WORLD; ++d)
             if (d < p.world) *reinterpret_cast<uint4*>(p.arena[d] + byte) = outv;
     }
-    __threadfence_system();
     __syncthreads();
     if (threadIdx.x == 0) {
+        __threadfence_system();                 // cumulative: covers the whole CTA's stores (ordered by the barrier)
         const unsigned long long ticket = atomicAdd(p.counters, 1ULL);
         if (ticket == gridDim.x - 1) {
             __threadfence_system();
@@ -1687,9 +1695,9 @@ __global__ void __launch_bounds__(512) k_bcast_push(DevBcast p) {
         for (int d = 0; d < LWC_MAX_WORLD; ++d)
             if (d < p.world && d != p.rank) reinterpret_cast<uint4*>(p.buf[d] + par)[v] = x;
     }
-    __threadfence_system();
     __syncthreads();
     if (threadIdx.x == 0) {
+        __threadfence_system();                 // cumulative: covers the whole CTA's stores (ordered by the barrier)
         const unsigned t = atomicAdd(p.ticket, 1u);
         if (t == gridDim.x - 1) {
             __threadfence_system();

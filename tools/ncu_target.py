@@ -8,6 +8,7 @@
     python tools/ncu_target.py wx                   wgrad 128 -> 128 3x3 @ 28                              (k_wx)
     python tools/ncu_target.py bn_apply | bn_bwd    batch norm apply / backward apply on 256 ch @ 56
     python tools/ncu_target.py exchange             layer-wise Top-k 1 % send + receive over ResNet-50-sized tensors, one rank
+    python tools/ncu_target.py step                 one whole ResNet-50 training step, batch 64 (all remaining kernel families)
     python tools/ncu_target.py all [reps]           every target in turn
 """
 import os
@@ -79,6 +80,18 @@ def build(what):
             plan.send(step[0])
             plan.recv(step[0])
             step[0] += 1
+    elif what == "step":
+        # one whole ResNet-50 training step (batch 64 @ 224): every remaining kernel family -- input normalise, stem, max
+        # pool, batch norm, adaptive average pool, GEMM head, cross entropy, exchange, SGD
+        from layerwise_b200.parallel.exchange import CompressionConfig
+        from layerwise_b200.train.imagenet import Trainer
+        from layerwise_b200.ops import conv as C2
+        C2._TUNE_ON["on"] = False                       # no autotune sweeps under the profiler
+        cfg = CompressionConfig(compress="layerwise", method="Topk", ratio=0.01, error_feedback=True)
+        tr = Trainer(arch="resnet50", dtype="bf16", cfg=cfg, lr=0.1, device="cuda:0", overlap=True)
+        x = torch.randint(0, 256, (64, 3, 224, 224), dtype=torch.uint8, device="cuda")
+        y = torch.randint(0, 1000, (64,), device="cuda")
+        fn = lambda: tr.train_step(x, y)
     else:
         raise SystemExit(__doc__)
     return fn
