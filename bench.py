@@ -425,12 +425,29 @@ def main():
                 xd, yd = next(pf)
                 return tr.train_step(xd, yd)[1]
 
-        def e2e_step(i):
+        reader = None
+        if args.impl == "ours":
+            # every step's loss is copied device -> host (4 bytes, pinned) and read by the host, one step late: the host
+            # never waits for the step it has just launched (utils/hostread.py).  The last value is drained before the
+            # closing event, so all `steps` reads are inside the timed region.
+            from layerwise_b200.utils import LaggedReader
+            reader = LaggedReader(depth=1)
+
+        def e2e_step(i, last=False):
             loss = step_e2e(i)
-            sink.append(float(loss.detach() if hasattr(loss, 'detach') else loss))    # device -> host read of the step's result
+            if reader is None:
+                sink.append(float(loss.detach() if hasattr(loss, 'detach') else loss))    # device -> host read of the step's result
+                return
+            v = reader.push(loss)
+            if v is not None:
+                sink.append(v)
+            if last:
+                sink.extend(reader.drain())
         for i in range(2):
-            e2e_step(i)
-        ms2, _ = timed(e2e_step, args.steps)
+            e2e_step(i, last=(i == 1))
+        n_before = len(sink)
+        ms2, _ = timed(lambda i: e2e_step(i, last=(i == args.steps - 1)), args.steps)
+        assert len(sink) - n_before == args.steps, "every timed step's loss must have been read on the host"
         e2e = {"value": imgs / (ms2 / 1e3), "unit": "img/s",
                "h2d_bytes_per_step": host_x[0].numel() * host_x[0].element_size() + host_y[0].numel() * 8,
                "d2h_bytes_per_step": 4,

@@ -98,3 +98,16 @@ def test_models_route_small_ops_to_native_kernels():
     out["loss"].sum().backward()
     assert out["correct"].dtype == torch.bool and torch.isfinite(out["loss"]).all()
     assert _native.counters.kernels >= 5 + 2 + 2 + 1          # 5 convs, 2 dropouts, ReLUs, correct
+
+
+def test_lagged_reader_on_device_scalars():
+    from layerwise_b200.utils import LaggedReader
+    r = LaggedReader(depth=1)
+    got = []
+    for i in range(6):
+        v = r.push(torch.full((), float(i), device="cuda") * 2)
+        if v is not None:
+            got.append(v)
+    got += r.drain()
+    assert got == [0.0, 2.0, 4.0, 6.0, 8.0, 10.0]
+    assert all(s.is_pinned() for s in r._free)

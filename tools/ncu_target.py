@@ -9,6 +9,7 @@
     python tools/ncu_target.py bn_apply | bn_bwd    batch norm apply / backward apply on 256 ch @ 56
     python tools/ncu_target.py exchange             layer-wise Top-k 1 % send + receive over ResNet-50-sized tensors, one rank
     python tools/ncu_target.py step                 one whole ResNet-50 training step, batch 64 (all remaining kernel families)
+    python tools/ncu_target.py misc                 SGD / pool / loss / input / stem / head / quantiser / dense all-reduce / small ops
     python tools/ncu_target.py all [reps]           every target in turn
 """
 import os
@@ -92,6 +93,41 @@ def build(what):
         x = torch.randint(0, 256, (64, 3, 224, 224), dtype=torch.uint8, device="cuda")
         y = torch.randint(0, 1000, (64,), device="cuda")
         fn = lambda: tr.train_step(x, y)
+    elif what == "misc":
+        # the kernel families without a capture so far: SGD, pools, cross entropy, input normalise, stem weight gradient,
+        # GEMM head (one Top-k training step, batch 64), the quantiser send / dense receive, the dense two-shot all-reduce
+        # (a `--compress none` step), dropout / ReLU / accuracy counters
+        from layerwise_b200.parallel.exchange import CompressionConfig
+        from layerwise_b200.parallel.fused import ExchangePlan, bind_local_world
+        from layerwise_b200.train.imagenet import Trainer
+        from layerwise_b200.ops import conv as C2, misc as M
+        C2._TUNE_ON["on"] = False
+        x = torch.randint(0, 256, (64, 3, 224, 224), dtype=torch.uint8, device="cuda")
+        y = torch.randint(0, 1000, (64,), device="cuda")
+        trs = [Trainer(arch="resnet50", dtype="bf16", device="cuda:0", lr=0.1, overlap=True,
+                       cfg=CompressionConfig(compress=c, method="Topk", ratio=0.01, error_feedback=(c != "none")))
+               for c in ("layerwise", "none")]
+        sizes = [2048 * 1000, 512 * 2048, 512 * 512 * 9, 2048 * 512]
+        plans = []
+        for method in ("RandomDithering", "TernGrad"):
+            cfg = CompressionConfig(compress="layerwise", method=method, qstates=255)
+            grads = [torch.randn(k, device="cuda").to(torch.bfloat16) for k in sizes]
+            outs = [torch.empty(k, device="cuda", dtype=torch.bfloat16) for k in sizes]
+            pl = ExchangePlan(grads, outs, None, cfg, 1, 0, False)
+            plans.append((pl, bind_local_world([pl]), grads, outs))
+        act = torch.randn(64, 4096, device="cuda").to(torch.bfloat16).requires_grad_(True)
+        logits = torch.randn(256, 1000, device="cuda").to(torch.bfloat16)
+        step = [0]
+
+        def fn():
+            for tr in trs:
+                tr.train_step(x, y)
+            for pl, _, _, _ in plans:
+                pl.send(step[0])
+                pl.recv(step[0])
+            step[0] += 1
+            M.dropout(M.relu(act), 0.5).sum().backward()
+            M.topk_hits(logits, y.repeat(4))
     else:
         raise SystemExit(__doc__)
     return fn
