@@ -178,6 +178,10 @@ typedef struct LwcSgdPlan LwcSgdPlan;
 int lwc_sgd_plan_create(LwcSgdPlan** out, const LwcSgdTensor* tensors_host, int32_t num_tensors);
 int lwc_sgd_plan_destroy(LwcSgdPlan* plan);
 int lwc_sgd_step(LwcSgdPlan* plan, const LwcSgdDesc* desc, void* stream);
+/* Diagnostics (no reference counterpart): cycles per tcgen05.mma (M = 128, N = n, K = 16, bf16, both operands in shared
+ * memory) issued back to back by one thread per SM, for K-major / MN-major operand layouts.  tools/mma_rate_probe.py. */
+int lwc_probe_mma_rate(int a_mn, int b_mn, int n, int iters, double* cycles_per_mma);
+
 /* Peer-memory broadcast of a staging buffer from `root` into every rank's copy (NVLink peer stores + step flag;
  * receivers wait with a bound).  Stands in for the coalesced NCCL broadcasts of the reference's DDP wrappers
  * (IMAGENET/training/sparsified_ddp.py:199-203,:366-375; ddp.py:190-194,:373-377). */

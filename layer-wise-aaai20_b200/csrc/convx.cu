@@ -100,9 +100,12 @@ __device__ __forceinline__ TileCoord tile_coord(const FxParams& p, int tile) {
 
 // REGSUM: the variant that keeps per-channel sums in registers (batch statistics of the outputs, batch-norm backward
 // sums); the plain variant carries neither the registers nor the code.  (Tried and dropped: the statistics as one more
-// MMA per staged sub-tile, D += [Y^T ; 1^T] Y with both operands MN-major straight from the staging tile.  Correct, but
-// an MN-major A operand is read from shared memory at about a quarter of the K-major rate -- ~120 cycles per 128 x 16
-// slab, measured here and visible in k_wx's tensor-pipe utilisation -- which cost more than the CUDA-core sums it saved.)
+// MMA per staged sub-tile, D += [Y^T ; 1^T] Y with both operands MN-major straight from the staging tile, issued by the
+// epilogue's leader thread next to its TMA store.  Correct, but slower than the CUDA-core sums it saved: the eight
+// descriptor-building MMA issues sit on the one thread all eight epilogue warps wait for at the next barrier.  The
+// operand layout is not the reason -- tools/mma_rate_probe.py measures the same 48 / 64 / 128 cycles per MMA at
+// N = 64 / 128 / 256 for K-major and MN-major operands alike -- so a version issued from an otherwise idle warp remains
+// open.)
 // TWO: compiled for two resident CTAs per SM (<= 96 registers; the host halves the shared-memory plan and the tensor
 // memory of both fits for BN <= 128).  The epilogue of one CTA is a chain of dependent steps with two barriers per
 // sub-tile, eight warps in step; a second CTA at another point of its chain fills the issue slots the first leaves idle.
