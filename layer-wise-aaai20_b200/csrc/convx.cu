@@ -104,8 +104,10 @@ __device__ __forceinline__ TileCoord tile_coord(const FxParams& p, int tile) {
 // epilogue's leader thread next to its TMA store.  Correct, but slower than the CUDA-core sums it saved: the eight
 // descriptor-building MMA issues sit on the one thread all eight epilogue warps wait for at the next barrier.  The
 // operand layout is not the reason -- tools/mma_rate_probe.py measures the same 48 / 64 / 128 cycles per MMA at
-// N = 64 / 128 / 256 for K-major and MN-major operands alike -- so a version issued from an otherwise idle warp remains
-// open.)
+// N = 64 / 128 / 256 for K-major and MN-major operands alike.  Issued from an eleventh, otherwise idle warp instead
+// (mbarrier hand-shake per staging slot) the statistics cost 6 % less than the register sums at 128-wide tiles, still
+// more than the 64-wide two-CTAs-per-SM variant with register sums, and the extra warp slowed the plain path by 6-10 %:
+// dropped as well.)
 // TWO: compiled for two resident CTAs per SM (<= 96 registers; the host halves the shared-memory plan and the tensor
 // memory of both fits for BN <= 128).  The epilogue of one CTA is a chain of dependent steps with two barriers per
 // sub-tile, eight warps in step; a second CTA at another point of its chain fills the issue slots the first leaves idle.
