@@ -115,8 +115,10 @@ template <int BN, bool B_MN, bool FORK, bool REGSUM, bool TWO>
 __global__ void __launch_bounds__(THREADS, TWO ? 2 : 1) k_fx(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                                                    const __grid_constant__ CUtensorMap tmC, const __grid_constant__ CUtensorMap tmX,
                                                    const __grid_constant__ CUtensorMap tmD, const FxParams p) {
-    extern __shared__ uint8_t smem_raw[];
-    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+    // 1024-byte aligned by declaration (the 128-byte swizzle atoms need it): no alignment slack in the budget, which is
+    // what lets the two-CTAs-per-SM plans with an auxiliary ring fit
+    extern __shared__ __align__(1024) uint8_t smem_fx[];
+    uint8_t* smem = smem_fx;
     constexpr int A_BYTES = BM * BK * 2;
     constexpr int B_BYTES = BN * BK * 2;
     constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
@@ -282,7 +284,8 @@ __global__ void __launch_bounds__(THREADS, TWO ? 2 : 1) k_fx(const __grid_consta
             ++pf_q;
             if (++pf_h == NCH) { pf_h = 0; pf_tile += gridDim.x; }
         };
-        if (aux && leader) { prefetch_x(); prefetch_x(); }
+        // prefetch distance: two sub-tiles, one when the ring has only two slots
+        if (aux && leader) { prefetch_x(); if (p.ncs >= 3) prefetch_x(); }
         constexpr int NS = REGSUM ? NCH : 1;
         float sacc[NS][16];                            // [chunk][sum x 8 channels | sum of squares x 8 channels]
 #pragma unroll
@@ -890,8 +893,8 @@ int run_fx(const FxGeom& g, cudaStream_t st, int* grid_out) {
     const int rings = 1 + (g.bnx ? 1 : 0) + (g.addend ? 1 : 0);
     const bool aux = rings > 1;
     const bool regsum = g.stats != nullptr;  // the variant with per-channel sums in registers
-    const int fixed = 1024 + 256;
-    if (two && (BN == 256 || g.addend || g.bnx || (BN == 128 && regsum))) return LWC_EINVAL;
+    const int fixed = 256;
+    if (two && (BN == 256 || (g.addend && g.bnx) || (BN == 128 && (regsum || g.addend)))) return LWC_EINVAL;
     const int budget = two ? SMEM_BUDGET / 2 - 1024 : SMEM_BUDGET;
     int ncs = two ? 2 : 4, stages = 0, operand_bytes = 0;
     const int halo_rows = BM / HALO_PW + span_h - 1;
@@ -913,7 +916,7 @@ int run_fx(const FxGeom& g, cudaStream_t st, int* grid_out) {
         const int stage_bytes = BM * BK * 2 + BN * BK * 2;
         stages = (budget - fixed - rings * ncs * SUB_BYTES) / stage_bytes;
         if (stages < 3) {
-            ncs = aux ? 3 : 2;                   // the auxiliary prefetch runs two chunks ahead: it needs >= 3 slots
+            ncs = (aux && !two) ? 3 : 2;         // an auxiliary prefetch two chunks ahead needs >= 3 slots (one ahead: 2)
             stages = (budget - fixed - rings * ncs * SUB_BYTES) / stage_bytes;
         }
         if (stages > 8) stages = 8;
@@ -929,7 +932,7 @@ int run_fx(const FxGeom& g, cudaStream_t st, int* grid_out) {
     p.bnb = g.bnx ? 1 : 0; p.bnb_relu = g.bnb_relu;
     p.bn_gamma = g.bn_gamma; p.bn_beta = g.bn_beta; p.bn_mean = g.bn_mean; p.bn_invstd = g.bn_invstd;
     p.add = g.addend ? 1 : 0; p.mask = static_cast<const uint8_t*>(g.mask);
-    const int smem = p.bar_off + 256 + 1024;
+    const int smem = p.bar_off + 256;
 
     CUtensorMap ta, tb, tc_;
     int rc;
@@ -986,7 +989,10 @@ int run_fx(const FxGeom& g, cudaStream_t st, int* grid_out) {
     if (grid_out) *grid_out = grid;
 #define LWC_FX(BN_, MN_, FK_, RS_) launch_fx<BN_, MN_, FK_, RS_>(ta, tb, tc_, tx, td, p, smem, grid, st)
 #define LWC_FX2(BN_, MN_, RS_) launch_fx<BN_, MN_, false, RS_, true>(ta, tb, tc_, tx, td, p, smem, grid, st)
-    if (two) {
+    if (two && g.addend) {
+        if (!g.b_mn) return LWC_EINVAL;
+        rc = launch_fx<64, true, true, true, true>(ta, tb, tc_, tx, td, p, smem, grid, st);
+    } else if (two) {
         if (BN == 128) rc = g.b_mn ? LWC_FX2(128, true, false) : LWC_FX2(128, false, false);
         else if (regsum) rc = g.b_mn ? LWC_FX2(64, true, true) : LWC_FX2(64, false, true);
         else rc = g.b_mn ? LWC_FX2(64, true, false) : LWC_FX2(64, false, false);

@@ -243,7 +243,7 @@ def conv_dgrad_bnstats(dy: torch.Tensor, weight: torch.Tensor, in_hw: Tuple[int,
 
     if bn_hint is None:
         bn_hint = _tuned(("db", n, h, w, ci, co, k, padding), ci, run,
-                         [b for b in (64, 128) if ci % b == 0] + _halo_candidates(co, ci, k, 1))
+                         [b for b in (64, 128) if ci % b == 0] + _halo_candidates(co, ci, k, 1) + _two_candidates(ci, True))
     run(bn_hint)
     _native.counters.add(1)
     link["partials"] = (part, int(nparts.value))
@@ -387,9 +387,11 @@ def maybe_conv2d(module, x, relu: bool = False):
 
 
 # ---- residual fork: conv1x1(x) and the identity branch share one fused backward --------------------------------
-# the k_fx fork variant (addend + mask + bn3 backward sums in one launch) is numerically validated but measures slower than
-# the older fork kernel + separate reduction (profiles/halo_probe_r2.json): opt-in
-_FORK_NEW = {"on": os.environ.get("LWC_FORK_NEW", "0") == "1"}
+# Residual fork: the k_fx variant (two CTAs per SM at 56^2 / 28^2 / 14^2) and the round-1 kernel are timed against each
+# other per shape.  Also summing bn3's backward reductions in that launch (a third staged tile per sub-tile) measures
+# slower than the separate reduction pass it replaces (profiles/halo_probe_r2.json): LWC_FORK_LINK=1 to opt in.
+_FORK_NEW = {"on": os.environ.get("LWC_FORK_NEW", "1") != "0"}
+_FORK_LINK = {"on": os.environ.get("LWC_FORK_LINK", "0") == "1"}
 
 
 def conv1x1_dgrad_add(dy: torch.Tensor, weight: torch.Tensor, addend: torch.Tensor,
@@ -403,14 +405,25 @@ def conv1x1_dgrad_add(dy: torch.Tensor, weight: torch.Tensor, addend: torch.Tens
     n, co, h, w = dy.shape
     ci = weight.shape[1]
     dx = torch.empty((n, ci, h, w), dtype=dy.dtype, device=dy.device, memory_format=torch.channels_last)
+    def run_old():
+        if relu_mask is not None:
+            abi.check(lib.lwc_conv1x1_add_mask(dy.data_ptr(), weight.data_ptr(), addend.data_ptr(), relu_mask.data_ptr(),
+                                               dx.data_ptr(), n, h, w, co, ci, 1, _stream()), "lwc_conv1x1_add_mask")
+        else:
+            abi.check(lib.lwc_conv1x1_add(dy.data_ptr(), weight.data_ptr(), addend.data_ptr(), dx.data_ptr(), n, h, w, co, ci, 1,
+                                          _stream()), "lwc_conv1x1_add")
+
     if _FORK_NEW["on"] and _ENABLED["on"]:
         wv = weight.detach().reshape(co, ci).contiguous()
-        use_link = link is not None and relu_mask is not None and _FUSE_BNB["on"] and link["x"].shape == dx.shape
+        use_link = (link is not None and relu_mask is not None and _FUSE_BNB["on"] and _FORK_LINK["on"]
+                    and link["x"].shape == dx.shape)
         part, nparts = None, C.c_int(0)
         if use_link:
             part = torch.empty((int(lib.lwc_convx_max_partials()), 2, ci), dtype=torch.float32, device=dy.device)
 
         def run(hint):
+            if hint < 0:                                # the round-1 kernel, as one more candidate (no sums)
+                return run_old()
             abi.check(lib.lwc_convx_dgrad1x1_fork(dy.data_ptr(), wv.data_ptr(), addend.data_ptr(),
                                                   0 if relu_mask is None else relu_mask.data_ptr(), dx.data_ptr(), n * h * w, co, ci,
                                                   link["x"].data_ptr() if use_link else 0,
@@ -420,20 +433,17 @@ def conv1x1_dgrad_add(dy: torch.Tensor, weight: torch.Tensor, addend: torch.Tens
                       "lwc_convx_dgrad1x1_fork")
 
         if bn_hint is None:
-            bn_hint = _tuned(("k", n, h, w, ci, co, relu_mask is not None, use_link), ci, run, [b for b in (64, 128) if ci % b == 0])
+            bn_hint = _tuned(("k", n, h, w, ci, co, relu_mask is not None, use_link), ci, run,
+                             [b for b in (64, 128) if ci % b == 0]
+                             + ([] if use_link else _two_candidates(ci, True) + ([-1] if ci % 128 == 0 or relu_mask is None else [])))
+            if bn_hint == 0 and not _TUNE_ON["on"]:
+                bn_hint = 2064 if (n * h * w >= 100000 and not use_link) else 128 if ci % 128 == 0 else 64
         run(bn_hint)
         _native.counters.add(1)
         if use_link:
             link["partials"] = (part, int(nparts.value))
         return dx
-    if relu_mask is not None:
-        rc = lib.lwc_conv1x1_add_mask(dy.data_ptr(), weight.data_ptr(), addend.data_ptr(), relu_mask.data_ptr(), dx.data_ptr(),
-                                      n, h, w, co, ci, 1, _stream())
-        abi.check(rc, "lwc_conv1x1_add_mask")
-    else:
-        rc = lib.lwc_conv1x1_add(dy.data_ptr(), weight.data_ptr(), addend.data_ptr(), dx.data_ptr(), n, h, w, co, ci, 1,
-                                 _stream())
-        abi.check(rc, "lwc_conv1x1_add")
+    run_old()
     _native.counters.add(1)
     return dx
 

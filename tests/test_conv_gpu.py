@@ -130,7 +130,7 @@ def test_fork_premasks_gradient_for_the_producing_batchnorm():
     from layerwise_b200.ops import conv as C_
 
     def same(a, c):
-        if not (C_._FORK_NEW["on"] and C_._FUSE_BNB["on"]):
+        if not (C_._FORK_NEW["on"] and C_._FORK_LINK["on"] and C_._FUSE_BNB["on"]):
             return torch.equal(a, c)
         return float((a - c).norm() / (c.norm() + 1e-12)) < 5e-3
     assert same(gx_a, gx_c)
@@ -395,7 +395,10 @@ def test_fork_kernel_adds_masks_and_sums(n, co, ci, hw, masked, linked):
         mask = (bits << torch.arange(8, device="cuda", dtype=torch.uint8)).sum(1).to(torch.uint8).contiguous()
     link = dict(x=xb, mean=torch.randn(ci, device="cuda"), invstd=torch.rand(ci, device="cuda") + 0.5) if linked else None
     was, C_._FORK_NEW["on"] = C_._FORK_NEW["on"], True
-    request_restore = lambda: C_._FORK_NEW.__setitem__("on", was)
+    was_l, C_._FORK_LINK["on"] = C_._FORK_LINK["on"], True
+
+    def request_restore():
+        C_._FORK_NEW["on"], C_._FORK_LINK["on"] = was, was_l
     for hint in [b for b in (64, 128) if ci % b == 0]:
         try:
             dx = C_.conv1x1_dgrad_add(dy, wt, add, mask, link, bn_hint=hint)
@@ -434,16 +437,16 @@ def test_bottleneck_chain_new_fork_kernel_matches_old_path():
     x0 = torch.randn(8, 256, 14, 14, device="cuda").to(torch.bfloat16).contiguous(memory_format=torch.channels_last)
     g = torch.randn(8, 256, 14, 14, device="cuda").to(torch.bfloat16).contiguous(memory_format=torch.channels_last)
     res = []
-    was = C_._FORK_NEW["on"]
+    was, was_l = C_._FORK_NEW["on"], C_._FORK_LINK["on"]
     for new in (True, False):
-        C_._FORK_NEW["on"] = new
+        C_._FORK_NEW["on"] = C_._FORK_LINK["on"] = new
         try:
             net = copy.deepcopy(blocks)
             x = x0.clone().requires_grad_(True)
             (net(x) * g).sum().backward()
             res.append((x.grad.float(), [p.grad.float() for p in net.parameters()]))
         finally:
-            C_._FORK_NEW["on"] = was
+            C_._FORK_NEW["on"], C_._FORK_LINK["on"] = was, was_l
     (gx_a, gp_a), (gx_b, gp_b) = res
 
     def relerr(a, b):
@@ -473,3 +476,34 @@ def test_two_ctas_per_sm_variant(n, ci, co, h, w, k, bn):
     if ci % bn == 0:
         dy = torch.randn(n, co, h, w, device="cuda").to(torch.bfloat16).contiguous(memory_format=torch.channels_last)
         assert torch.equal(conv_dgrad(dy, wt, (h, w), 1, k // 2, bn_hint=2000 + bn), conv_dgrad(dy, wt, (h, w), 1, k // 2, bn_hint=bn))
+
+
+@pytest.mark.parametrize("n,ci,co,hw,k", [(4, 64, 256, 56, 1), (3, 128, 128, 28, 3), (2, 256, 64, 9, 1)])
+def test_two_ctas_per_sm_with_auxiliary_ring(n, ci, co, hw, k):
+    """Hint 2064 on the launches that prefetch a second tile per sub-tile (batch-norm backward sums; residual fork):
+    two-slot rings, prefetch distance one."""
+    from layerwise_b200.ops import conv as C_
+    torch.manual_seed(0)
+    _, wt = _mk(n, ci, co, hw, hw, k)
+    dy = torch.randn(n, co, hw, hw, device="cuda").to(torch.bfloat16).contiguous(memory_format=torch.channels_last)
+    xb = torch.randn(n, ci, hw, hw, device="cuda").to(torch.bfloat16).contiguous(memory_format=torch.channels_last)
+    gamma, beta = torch.rand(ci, device="cuda") + 0.5, torch.randn(ci, device="cuda") * 0.3
+    mean, invstd = torch.randn(ci, device="cuda") * 0.2, torch.rand(ci, device="cuda") + 0.5
+    outs = []
+    for hint in (64, 2064):
+        link = dict(x=xb, gamma=gamma, beta=beta, mean=mean, invstd=invstd, relu=True)
+        dx = C_.conv_dgrad_bnstats(dy, wt, (hw, hw), k // 2, link, bn_hint=hint)
+        part, nparts = link["partials"]
+        outs.append((dx, part[:nparts].sum(0)))
+    assert torch.equal(outs[0][0], outs[1][0])
+    assert (outs[0][1] - outs[1][1]).abs().max() <= 2e-3 * float(outs[0][1].abs().max())
+    if k == 1:
+        add = torch.randn(n, ci, hw, hw, device="cuda").to(torch.bfloat16).contiguous(memory_format=torch.channels_last)
+        mask = torch.randint(0, 256, (n * hw * hw * ci // 8,), device="cuda", dtype=torch.uint8)
+        was, C_._FORK_NEW["on"] = C_._FORK_NEW["on"], True
+        try:
+            a = C_.conv1x1_dgrad_add(dy, wt, add, mask, None, bn_hint=64)
+            b = C_.conv1x1_dgrad_add(dy, wt, add, mask, None, bn_hint=2064)
+        finally:
+            C_._FORK_NEW["on"] = was
+        assert torch.equal(a, b)

@@ -66,6 +66,7 @@ def main():
         out[f"fwd_stats_256to64_56_hint{hint}_ms"] = ms(lambda: C_.conv_forward(x2, w2, want_stats=True, bn_hint=hint))
     out["cudnn_fwd_64x64_56_bs224_ms"] = ms(lambda: F.conv2d(x, w, padding=1))
     # fork: layer1 (64 -> 256 @ 56) and layer3 (256 -> 1024 @ 14)
+    C_._FORK_NEW["on"] = True
     for co, ci, s in ((64, 256, 56), (128, 512, 28), (256, 1024, 14), (512, 2048, 7)):
         wt = (torch.randn(co, ci, 1, 1, device="cuda") / co ** 0.5).to(torch.bfloat16)
         d = torch.randn(n, co, s, s, device="cuda").to(torch.bfloat16).contiguous(memory_format=torch.channels_last)
@@ -73,6 +74,14 @@ def main():
         xb = torch.randn(n, ci, s, s, device="cuda").to(torch.bfloat16).contiguous(memory_format=torch.channels_last)
         mask = torch.randint(0, 256, (n * s * s * ci // 8,), device="cuda", dtype=torch.uint8)
         link = dict(x=xb, mean=torch.randn(ci, device="cuda"), invstd=torch.rand(ci, device="cuda") + 0.5)
+        out[f"fork_{co}to{ci}_{s}_new_hint2064_ms"] = ms(lambda: C_.conv1x1_dgrad_add(d, wt, add, mask, None, bn_hint=2064))
+        lk = dict(x=xb, gamma=None, beta=None, mean=link["mean"], invstd=link["invstd"], relu=True)
+        for hint in [b_ for b_ in (64, 128, 2064) if ci % (b_ % 1000) == 0]:
+            # data gradient of the block's LAST 1x1 (dy has ci channels, dx co channels) + bn2's backward sums
+            lk2 = dict(x=d, gamma=None, beta=None, mean=link["mean"][:co], invstd=link["invstd"][:co], relu=True)
+            wl = (torch.randn(ci, co, 1, 1, device="cuda") / ci ** 0.5).to(torch.bfloat16)
+            if co % (hint % 1000) == 0:
+                out[f"dgrad_bnb_{ci}to{co}_{s}_hint{hint}_ms"] = ms(lambda: C_.conv_dgrad_bnstats(add, wl, (s, s), 0, lk2, bn_hint=hint))
         for hint in (64, 128):
             out[f"fork_{co}to{ci}_{s}_new_link_hint{hint}_ms"] = ms(lambda: C_.conv1x1_dgrad_add(d, wt, add, mask, link, bn_hint=hint))
             out[f"fork_{co}to{ci}_{s}_new_hint{hint}_ms"] = ms(lambda: C_.conv1x1_dgrad_add(d, wt, add, mask, None, bn_hint=hint))

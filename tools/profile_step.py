@@ -23,6 +23,7 @@ def main():
     ap.add_argument("--arch", default="resnet50")
     ap.add_argument("--top", type=int, default=45)
     ap.add_argument("--out", default="gpurun_out/step_profile.json")
+    ap.add_argument("--timeline", default="", help="also write the kernels of the last profiled step in launch order (TSV)")
     args = ap.parse_args()
     torch.cuda.set_device(0)
     cfg = CompressionConfig(compress="layerwise", method="Topk", ratio=0.01, error_feedback=True)
@@ -38,6 +39,15 @@ def main():
             tr.train_step(x, y)
         torch.cuda.synchronize()
     agg = collections.defaultdict(lambda: [0, 0.0])
+    if args.timeline:
+        evs = sorted((e for e in prof.events() if e.device_type == torch.autograd.DeviceType.CUDA), key=lambda e: e.time_range.start)
+        starts = [i for i, e in enumerate(evs) if "k_normalize" in e.name]
+        last = evs[starts[-1]:] if starts else evs
+        t0 = last[0].time_range.start
+        with open(args.timeline, "w") as f:
+            for e in last:
+                dur = e.device_time if hasattr(e, "device_time") else e.cuda_time
+                f.write(f"{e.time_range.start - t0:10.1f}\t{dur:8.1f}\t{e.name[:110]}\n")
     for ev in prof.events():
         if ev.device_type == torch.autograd.DeviceType.CUDA:
             agg[ev.name][0] += 1
