@@ -313,19 +313,24 @@ __global__ void __launch_bounds__(THREADS, TWO ? 2 : 1) k_fx(const __grid_consta
             mbar_wait(&tmem_full[as], aph);
             fence_after();
             const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + as * BN + (uint32_t)(hsel * 32);
-            uint32_t vv[2][32];
+            // accumulator loads run one 64-column chunk ahead of the conversion -- except in the two-CTAs-per-SM variant
+            // with register sums at 128-wide tiles, where the second buffer does not fit in 96 registers (the other
+            // CTA covers the latency there)
+            constexpr int NVV = (TWO && REGSUM && BN >= 128) ? 1 : 2;
+            uint32_t vv[NVV][32];
             tmem_ld32_issue(taddr, vv[0]);
 #pragma unroll
             for (int h = 0; h < NCH; ++h) {
                 uint8_t* cst = smem + p.c_off + sub * SUB_BYTES;
-                uint32_t* v = vv[h & 1];
+                uint32_t* v = vv[h % NVV];
+                if (NVV == 1 && h > 0) tmem_ld32_issue(taddr + (uint32_t)(h * 64), vv[0]);
                 // the store that read this staging buffer `ncs` chunks ago must have finished reading it
                 if (leader) {
                     if (p.ncs >= 4) tma_wait_group_read<3>(); else if (p.ncs == 3) tma_wait_group_read<2>(); else tma_wait_group_read<1>();
                 }
                 tmem_ld_wait();
                 if (h + 1 < NCH) {
-                    tmem_ld32_issue(taddr + (uint32_t)((h + 1) * 64), vv[(h + 1) & 1]);     // next chunk in flight
+                    if (NVV == 2) tmem_ld32_issue(taddr + (uint32_t)((h + 1) * 64), vv[(h + 1) % NVV]);     // next chunk in flight
                 } else {                                // whole row is in registers: the accumulator may be overwritten
                     fence_before();
                     __syncwarp();
@@ -848,7 +853,7 @@ int pick_bn(int Cout, int hint) {
 
 // Halo mode is asked for with bn_hint = 1000 + BN (ops/conv.py times it against the per-tap variants).
 bool halo_ok(const FxGeom& g, int* span_w, int* span_h, int* dw0, int* dh0) {
-    if (g.kchunks != 1 || g.window || g.stride != 1 || g.ntaps < 2 || g.addend) return false;
+    if (g.kchunks != 1 || g.stride != 1 || g.ntaps < 2 || g.addend) return false;
     int lo_w = g.dw[0], hi_w = g.dw[0], lo_h = g.dh[0], hi_h = g.dh[0];
     for (int t = 1; t < g.ntaps; ++t) {
         if (g.a_c0[t] != g.a_c0[0]) return false;
@@ -894,7 +899,7 @@ int run_fx(const FxGeom& g, cudaStream_t st, int* grid_out) {
     const bool aux = rings > 1;
     const bool regsum = g.stats != nullptr;  // the variant with per-channel sums in registers
     const int fixed = 256;
-    if (two && (BN == 256 || (g.addend && g.bnx) || (BN == 128 && (regsum || g.addend)))) return LWC_EINVAL;
+    if (two && (BN == 256 || (g.addend && g.bnx) || (BN == 128 && (g.bnx || g.addend)))) return LWC_EINVAL;
     const int budget = two ? SMEM_BUDGET / 2 - 1024 : SMEM_BUDGET;
     int ncs = two ? 2 : 4, stages = 0, operand_bytes = 0;
     const int halo_rows = BM / HALO_PW + span_h - 1;
@@ -941,6 +946,7 @@ int run_fx(const FxGeom& g, cudaStream_t st, int* grid_out) {
         cuuint64_t gd[4] = {64, (cuuint64_t)g.W, (cuuint64_t)g.H, (cuuint64_t)g.N};
         cuuint64_t gs[3] = {(cuuint64_t)g.wpitch * 2, (cuuint64_t)g.cpitch * 2, (cuuint64_t)g.H * g.cpitch * 2};
         cuuint32_t bx[4] = {64, (cuuint32_t)pt.Wb, (cuuint32_t)pt.Hb, (cuuint32_t)pt.Nb};
+        if (halo) { bx[1] = HALO_PW; bx[2] = (cuuint32_t)halo_rows; bx[3] = 1; }   // the stem's row taps: 16 x (8 + 3) windows
         rc = encode(&ta, g.x, 4, gd, gs, bx, nullptr);
     } else if (halo) {
         rc = encode_act(&ta, g.x, g.C, g.cpitch, g.W, g.H, g.N, HALO_PW, halo_rows, 1, 1);
@@ -993,7 +999,8 @@ int run_fx(const FxGeom& g, cudaStream_t st, int* grid_out) {
         if (!g.b_mn) return LWC_EINVAL;
         rc = launch_fx<64, true, true, true, true>(ta, tb, tc_, tx, td, p, smem, grid, st);
     } else if (two) {
-        if (BN == 128) rc = g.b_mn ? LWC_FX2(128, true, false) : LWC_FX2(128, false, false);
+        if (BN == 128 && regsum) rc = g.b_mn ? LWC_EINVAL : LWC_FX2(128, false, true);
+        else if (BN == 128) rc = g.b_mn ? LWC_FX2(128, true, false) : LWC_FX2(128, false, false);
         else if (regsum) rc = g.b_mn ? LWC_FX2(64, true, true) : LWC_FX2(64, false, true);
         else rc = g.b_mn ? LWC_FX2(64, true, false) : LWC_FX2(64, false, false);
     } else if (g.addend) {

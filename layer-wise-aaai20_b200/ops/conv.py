@@ -62,11 +62,12 @@ def _halo_candidates(kdim: int, nout: int, k: int, stride: int):
 _TWO = {"on": os.environ.get("LWC_CONV_TWO", "1") != "0"}
 
 
-def _two_candidates(nout: int, sums: bool):
-    """Tile hints 2000 + width: the variant compiled for two resident CTAs per SM (64-wide tiles; 128-wide without sums)."""
+def _two_candidates(nout: int, aux: bool):
+    """Tile hints 2000 + width: the variant compiled for two resident CTAs per SM (64- and 128-wide tiles; 64 only for the
+    launches that stage a second tile per sub-tile: batch-norm backward sums, residual fork)."""
     if not _TWO["on"]:
         return []
-    return [2000 + b for b in ((64,) if sums else (64, 128)) if nout % b == 0]
+    return [2000 + b for b in ((64,) if aux else (64, 128)) if nout % b == 0]
 
 
 def _tuned(key: tuple, cout: int, run, cands=None) -> int:
@@ -178,7 +179,7 @@ def conv_forward(x: torch.Tensor, weight: torch.Tensor, bias: Optional[torch.Ten
 
     if bn_hint is None:
         bn_hint = _tuned(("f", n, h, w, cx, co, k, stride, pad, want_stats), co, run,
-                         _candidates(co) + _halo_candidates(cx, co, k, stride) + _two_candidates(co, want_stats))
+                         _candidates(co) + _halo_candidates(cx, co, k, stride) + _two_candidates(co, False))
     run(bn_hint)
     _native.counters.add(1)
     return y, (Stats(part, int(nparts.value), n * oh * ow) if want_stats else None)

@@ -97,7 +97,7 @@ def stem_forward_native_ok(xs: torch.Tensor, w7: torch.Tensor) -> bool:
             and xs.shape[1] == 16 and xs.is_contiguous(memory_format=torch.channels_last))
 
 
-def stem_forward(xs: torch.Tensor, w7: torch.Tensor, want_stats: bool = False) -> torch.Tensor:
+def stem_forward(xs: torch.Tensor, w7: torch.Tensor, want_stats: bool = False, bn_hint=None) -> torch.Tensor:
     """The stem convolution on the space-to-depth input: the tap-table tcgen05 kernel (four kernel-row taps over
     overlapping 128-byte windows, K = 256) or, off the GPU, the equivalent dense 4x4 convolution."""
     w = s2d_stem_weight(w7.detach())
@@ -117,9 +117,18 @@ def stem_forward(xs: torch.Tensor, w7: torch.Tensor, want_stats: bool = False) -
         part = torch.empty((int(lib.lwc_convx_max_partials()), 2, co), dtype=torch.float32, device=xs.device)
     nparts = C.c_int(0)
     st = torch.cuda.current_stream().cuda_stream
-    abi.check(lib.lwc_convx_stem_forward(xs.data_ptr(), w4.data_ptr(), y.data_ptr(), n, oh, ow, co,
-                                         0 if part is None else part.data_ptr(), C.byref(nparts), 0, C.c_void_p(st)),
-              "lwc_convx_stem_forward")
+
+    def run(hint):
+        abi.check(lib.lwc_convx_stem_forward(xs.data_ptr(), w4.data_ptr(), y.data_ptr(), n, oh, ow, co,
+                                             0 if part is None else part.data_ptr(), C.byref(nparts), hint, C.c_void_p(st)),
+                  "lwc_convx_stem_forward")
+
+    # per-tap boxes, or the halo variant: the four kernel-row taps read one 16 x 11-window box, weights resident
+    from . import conv as _conv
+    hint = bn_hint
+    if hint is None:
+        hint = _conv._tuned(("stem", n, oh, ow, co, want_stats), co, run, [64, 128, 1064, 1128, 3064] if co % 128 == 0 else [64, 1064, 3064])
+    run(hint)
     _native.counters.add(1)
     if want_stats:
         _LAST_STATS["v"] = Stats(part, int(nparts.value), n * oh * ow)

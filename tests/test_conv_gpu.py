@@ -467,9 +467,9 @@ def test_two_ctas_per_sm_variant(n, ci, co, h, w, k, bn):
     ref, _ = conv_forward(x, wt, bn_hint=bn)
     y, _ = conv_forward(x, wt, bn_hint=2000 + bn)
     assert torch.equal(y, ref)
-    if bn == 64:
-        y2, st = conv_forward(x, wt, want_stats=True, bn_hint=2064)
-        _, st_ref = conv_forward(x, wt, want_stats=True, bn_hint=64)
+    if True:
+        y2, st = conv_forward(x, wt, want_stats=True, bn_hint=2000 + bn)
+        _, st_ref = conv_forward(x, wt, want_stats=True, bn_hint=bn)
         assert torch.equal(y2, ref)
         a, b = st.partials[:st.nparts].sum(0), st_ref.partials[:st_ref.nparts].sum(0)
         assert (a - b).abs().max() <= 1e-3 * float(b.abs().max())
@@ -507,3 +507,22 @@ def test_two_ctas_per_sm_with_auxiliary_ring(n, ci, co, hw, k):
         finally:
             C_._FORK_NEW["on"] = was
         assert torch.equal(a, b)
+
+
+@pytest.mark.parametrize("n,hw", [(4, 64), (2, 224), (3, 100)])
+def test_stem_halo_variant_matches_the_per_tap_one(n, hw):
+    """Hint 1064 on the stem: the four kernel-row taps read one 16 x 11-window box, the weights stay resident."""
+    from layerwise_b200.ops import input as I
+    torch.manual_seed(0)
+    xu = torch.randint(0, 256, (n, 3, hw, hw), dtype=torch.uint8, device="cuda")
+    w7 = (torch.randn(64, 3, 7, 7, device="cuda") / 12).to(torch.bfloat16)
+    xs = I.normalize_u8(xu, s2d=True)
+    a = I.stem_forward(xs, w7, want_stats=True, bn_hint=64)
+    sa = I._LAST_STATS["v"]
+    ta = sa.partials[:sa.nparts].sum(0)
+    for hint in (1064, 3064):                      # halo; halo + two CTAs per SM
+        b = I.stem_forward(xs, w7, want_stats=True, bn_hint=hint)
+        sb = I._LAST_STATS["v"]
+        assert float((a != b).float().mean()) < 1e-3
+        tb = sb.partials[:sb.nparts].sum(0)
+        assert (ta - tb).abs().max() <= 1e-3 * float(ta.abs().max())
