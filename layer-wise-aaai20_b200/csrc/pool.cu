@@ -7,6 +7,7 @@
 #include <cuda_bf16.h>
 #include <cuda_fp16.h>
 #include <cuda_runtime.h>
+#include <type_traits>
 #include <string.h>
 
 #include "common.cuh"
@@ -201,25 +202,53 @@ __global__ void __launch_bounds__(256) k_maxpool_fwd_k3s2(Params p) {
             const int hh = ok[t] ? h : h0 + 1, ww = ok[t] ? w : w0 + 1;
             ldraw<T>(xb + (size_t)(hh * p.W + ww) * p.C, raw[t]);
         }
-        float best[8];
-        unsigned arg[8];
-#pragma unroll
-        for (int c = 0; c < 8; ++c) { best[c] = -INFINITY; arg[c] = 0; }
-#pragma unroll
-        for (int t = 0; t < 9; ++t) {
-            float v[8];
-            unpack(raw[t], v);
-#pragma unroll
-            for (int c = 0; c < 8; ++c)
-                if (ok[t] && v[c] > best[c]) { best[c] = v[c]; arg[c] = t; }
-        }
         const size_t o = (size_t)id * 8;                  // == ((n*OH + oh)*OW + ow)*C + cg*8
-        V8<T>::st(reinterpret_cast<T*>(p.y) + o, best);
-        if (p.idx) {
-            uint2 packed;
-            packed.x = arg[0] | (arg[1] << 8) | (arg[2] << 16) | (arg[3] << 24);
-            packed.y = arg[4] | (arg[5] << 8) | (arg[6] << 16) | (arg[7] << 24);
-            *reinterpret_cast<uint2*>(p.idx + o) = packed;
+        if constexpr (std::is_same<T, __nv_bfloat16>::value) {
+            // bf16: the running maximum and its tap index stay packed, two channels per 32-bit word (compare -> 16-bit
+            // lane masks -> bitwise selects); no unpacking, no conversion on the way out.  The kernel was issue-bound.
+            uint32_t best[4], arg[4];
+#pragma unroll
+            for (int w = 0; w < 4; ++w) { best[w] = 0xff80ff80u; arg[w] = 0u; }      // -inf, -inf
+#pragma unroll
+            for (int t = 0; t < 9; ++t) {
+                const uint32_t v[4] = {raw[t].v.x, raw[t].v.y, raw[t].v.z, raw[t].v.w};
+                const uint32_t okm = ok[t] ? 0xffffffffu : 0u;
+                const uint32_t tp = (uint32_t)t * 0x00010001u;
+#pragma unroll
+                for (int w = 0; w < 4; ++w) {
+                    const uint32_t m = __hgt2_mask(*reinterpret_cast<const __nv_bfloat162*>(&v[w]),
+                                                   *reinterpret_cast<const __nv_bfloat162*>(&best[w])) & okm;
+                    best[w] = (best[w] & ~m) | (v[w] & m);
+                    arg[w] = (arg[w] & ~m) | (tp & m);
+                }
+            }
+            *reinterpret_cast<uint4*>(reinterpret_cast<T*>(p.y) + o) = make_uint4(best[0], best[1], best[2], best[3]);
+            if (p.idx) {
+                uint2 packed;
+                packed.x = __byte_perm(arg[0], arg[1], 0x6420);
+                packed.y = __byte_perm(arg[2], arg[3], 0x6420);
+                *reinterpret_cast<uint2*>(p.idx + o) = packed;
+            }
+        } else {
+            float best[8];
+            unsigned arg[8];
+#pragma unroll
+            for (int c = 0; c < 8; ++c) { best[c] = -INFINITY; arg[c] = 0; }
+#pragma unroll
+            for (int t = 0; t < 9; ++t) {
+                float v[8];
+                unpack(raw[t], v);
+#pragma unroll
+                for (int c = 0; c < 8; ++c)
+                    if (ok[t] && v[c] > best[c]) { best[c] = v[c]; arg[c] = t; }
+            }
+            V8<T>::st(reinterpret_cast<T*>(p.y) + o, best);
+            if (p.idx) {
+                uint2 packed;
+                packed.x = arg[0] | (arg[1] << 8) | (arg[2] << 16) | (arg[3] << 24);
+                packed.y = arg[4] | (arg[5] << 8) | (arg[6] << 16) | (arg[7] << 24);
+                *reinterpret_cast<uint2*>(p.idx + o) = packed;
+            }
         }
     }
 }
