@@ -194,13 +194,21 @@ __global__ void __launch_bounds__(256) k_maxpool_fwd_k3s2(Params p) {
         const T* xb = reinterpret_cast<const T*>(p.x) + (size_t)n * p.H * p.W * p.C + cg * 8;
         Raw8<T> raw[9];
         bool ok[9];
+        // out-of-range rows / columns re-read the (always valid) centre row / column: no branch, and the tap is masked
+        // out of the maximum below.  Row and column are clamped separately: three row bases, three column offsets.
+        bool okh[3], okw[3];
+        int roff[3], coff[3];
+#pragma unroll
+        for (int r = 0; r < 3; ++r) {
+            okh[r] = h0 + r >= 0 && h0 + r < p.H;
+            okw[r] = w0 + r >= 0 && w0 + r < p.W;
+            roff[r] = (okh[r] ? h0 + r : h0 + 1) * p.W * p.C;
+            coff[r] = (okw[r] ? w0 + r : w0 + 1) * p.C;
+        }
 #pragma unroll
         for (int t = 0; t < 9; ++t) {
-            const int h = h0 + t / 3, w = w0 + t % 3;
-            ok[t] = h >= 0 && h < p.H && w >= 0 && w < p.W;
-            // out-of-range taps re-read the (always valid) centre tap: no branch, no effect on the maximum
-            const int hh = ok[t] ? h : h0 + 1, ww = ok[t] ? w : w0 + 1;
-            ldraw<T>(xb + (size_t)(hh * p.W + ww) * p.C, raw[t]);
+            ok[t] = okh[t / 3] && okw[t % 3];
+            ldraw<T>(xb + roff[t / 3] + coff[t % 3], raw[t]);
         }
         const size_t o = (size_t)id * 8;                  // == ((n*OH + oh)*OW + ow)*C + cg*8
         if constexpr (std::is_same<T, __nv_bfloat16>::value) {
