@@ -1,0 +1,36 @@
+"""Host-side logic of the convolution autotuner (no GPU): candidate lists and tolerance of variants that do not fit."""
+import pytest
+import torch
+
+import layerwise_b200  # noqa: F401
+from layerwise_b200.ops import conv as C_
+
+
+def test_candidate_lists():
+    assert C_._candidates(64) == [64]
+    assert C_._candidates(256) == [64, 128, 256]
+    assert C_._candidates(192) == [64]
+    # halo variant: one 64-channel chunk of K, stride 1, more than one tap that fits the tap table
+    assert C_._halo_candidates(64, 128, 3, 1) == [1064, 1128]
+    assert C_._halo_candidates(8, 64, 3, 1) == [1064]
+    assert C_._halo_candidates(128, 128, 3, 1) == []
+    assert C_._halo_candidates(64, 64, 1, 1) == []
+    assert C_._halo_candidates(64, 64, 3, 2) == []
+    assert C_._halo_candidates(64, 64, 5, 1) == []          # 25 taps > 16
+    # two CTAs per SM: 64 and 128 wide; 64 only when a second tile is staged per sub-tile
+    assert C_._two_candidates(256, False) == [2064, 2128]
+    assert C_._two_candidates(256, True) == [2064]
+    assert C_._two_candidates(64, False) == [2064]
+
+
+def test_switches_remove_candidates(monkeypatch):
+    monkeypatch.setitem(C_._HALO, "on", False)
+    monkeypatch.setitem(C_._TWO, "on", False)
+    assert C_._halo_candidates(64, 128, 3, 1) == [] and C_._two_candidates(256, False) == []
+
+
+@pytest.mark.skipif(torch.cuda.is_available(), reason="the timing path needs no device only when tuning is off")
+def test_tuner_is_inert_without_a_device(monkeypatch):
+    calls = []
+    monkeypatch.setitem(C_._TUNE_ON, "on", False)
+    assert C_._tuned(("x", 1), 64, calls.append, [64, 128]) == 0 and calls == []
