@@ -53,6 +53,13 @@ def build(what):
     elif what == "wx":
         x, dy = t(n, 128, 28, 28), t(n, 128, 28, 28)
         fn = lambda: C_.conv_wgrad(x, dy, (128, 128, 3, 3), 1, 1, out_dtype=torch.bfloat16)
+    elif what == "wx1x1":
+        # the 1x1 weight gradients of layer1: 256 -> 64 and 64 -> 256 @ 56 (k_wx<64> / k_wx<256>), fixed tile hints
+        x1, d1 = t(n, 256, 56, 56), t(n, 64, 56, 56)
+
+        def fn():
+            C_.conv_wgrad(x1, d1, (64, 256, 1, 1), 1, 0, out_dtype=torch.bfloat16, bn_hint=64)
+            C_.conv_wgrad(d1, x1, (256, 64, 1, 1), 1, 0, out_dtype=torch.bfloat16, bn_hint=256)
     elif what in ("bn_apply", "bn_bwd"):
         from layerwise_b200.ops.bn import batch_norm_act
         x = t(n, 256, 56, 56).requires_grad_(True)
