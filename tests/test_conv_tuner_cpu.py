@@ -34,3 +34,19 @@ def test_tuner_is_inert_without_a_device(monkeypatch):
     calls = []
     monkeypatch.setitem(C_._TUNE_ON, "on", False)
     assert C_._tuned(("x", 1), 64, calls.append, [64, 128]) == 0 and calls == []
+
+
+@pytest.mark.parametrize("span_w", [1, 2, 3, 4, 5])
+def test_halo_staging_rows_are_a_permutation(span_w):
+    """CPU restatement of the halo epilogue's row compaction (csrc/convx.cu, `dr`): accumulator row r = (r / 16, r % 16)
+    of the 16-pixel-pitch box goes to row (r / 16) * Wb + r % 16 of the Wb-pixel-pitch staging tile when the column is
+    an output pixel, and behind the patch otherwise -- every staging row is written exactly once."""
+    PW, HB = 16, 8
+    wb = PW - (span_w - 1)
+    dest = []
+    for r in range(128):
+        r_w, r_h = r % PW, r // PW
+        inside = r_w < wb and r_h < HB
+        dest.append(r_h * wb + r_w if inside else wb * HB + r_h * (PW - wb) + (r_w - wb))
+    assert sorted(dest) == list(range(128))
+    assert all(d < wb * HB for r, d in enumerate(dest) if r % PW < wb)          # valid pixels fill the patch exactly
