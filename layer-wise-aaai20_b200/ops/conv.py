@@ -101,6 +101,53 @@ def tuned_table() -> Dict[tuple, int]:
     return dict(_TUNE)
 
 
+def save_tuned(path: str) -> int:
+    """Write the tile choices made so far (layer shape -> hint) as JSON; returns the number of entries.  The choices are
+    the counterpart of cuDNN's benchmark cache, which the reference rebuilds on every start (``cudnn.benchmark = True``,
+    CIFAR10/dawn.py:120, IMAGENET/training/train_imagenet_nv.py:141): a job that restarts, or that wants every rank to
+    run the same variants, loads them instead of timing again."""
+    import json
+    rows = [[list(k), int(v)] for k, v in _TUNE.items()]
+    tmp = f"{path}.tmp{os.getpid()}"
+    with open(tmp, "w") as f:
+        json.dump({"version": 1, "entries": rows}, f)
+    os.replace(tmp, path)
+    return len(rows)
+
+
+def load_tuned(path: str) -> int:
+    """Merge tile choices saved by ``save_tuned`` (entries already present win); returns the number of entries added."""
+    import json
+    with open(path) as f:
+        doc = json.load(f)
+    if doc.get("version") != 1:
+        raise ValueError(f"{path}: unknown tuning-table version {doc.get('version')!r}")
+    n = 0
+    for k, v in doc["entries"]:
+        key = tuple(k)
+        if key not in _TUNE:
+            _TUNE[key] = int(v)
+            n += 1
+    return n
+
+
+def _tune_cache_from_env():
+    """``LWC_CONV_TUNE_CACHE=<file>``: load it now if it exists, write it back when the process exits."""
+    path = os.environ.get("LWC_CONV_TUNE_CACHE")
+    if not path:
+        return
+    if os.path.exists(path):
+        try:
+            load_tuned(path)
+        except (OSError, ValueError, KeyError, TypeError):
+            pass                                   # a stale or truncated file only costs the timing runs
+    import atexit
+    atexit.register(lambda: _TUNE and save_tuned(path))
+
+
+_tune_cache_from_env()
+
+
 # ---- operand preparation --------------------------------------------------------------------------------------
 def _prep_input(x: torch.Tensor) -> torch.Tensor:
     """Channels-last with a channel count the TMA unit can address (multiple of 8: 16-byte pixel pitch)."""

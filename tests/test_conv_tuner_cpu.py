@@ -50,3 +50,17 @@ def test_halo_staging_rows_are_a_permutation(span_w):
         dest.append(r_h * wb + r_w if inside else wb * HB + r_h * (PW - wb) + (r_w - wb))
     assert sorted(dest) == list(range(128))
     assert all(d < wb * HB for r, d in enumerate(dest) if r % PW < wb)          # valid pixels fill the patch exactly
+
+
+def test_tuning_table_round_trips_through_a_file(tmp_path, monkeypatch):
+    monkeypatch.setattr(C_, "_TUNE", {("f", 224, 56, 56, 64, 256, 1, 1, 0, True): 2128, ("stem", 224, 112, 112, 64, True): 3064})
+    path = str(tmp_path / "tune.json")
+    assert C_.save_tuned(path) == 2
+    monkeypatch.setattr(C_, "_TUNE", {("stem", 224, 112, 112, 64, True): 64})
+    assert C_.load_tuned(path) == 1                                   # the entry already present wins
+    assert C_._TUNE[("f", 224, 56, 56, 64, 256, 1, 1, 0, True)] == 2128 and C_._TUNE[("stem", 224, 112, 112, 64, True)] == 64
+    # a tuned key short-circuits the timing loop
+    assert C_._tuned(("f", 224, 56, 56, 64, 256, 1, 1, 0, True), 256, lambda h: (_ for _ in ()).throw(AssertionError("timed"))) == 2128
+    (tmp_path / "bad.json").write_text('{"version": 7, "entries": []}')
+    with pytest.raises(ValueError):
+        C_.load_tuned(str(tmp_path / "bad.json"))
