@@ -537,7 +537,9 @@ __device__ __forceinline__ void publish_when_last(const DevPlan& p) {
     if (p.direct_idx) return;
     // The CTA barrier orders every thread's payload stores before thread 0's fence; the fence is cumulative, so ONE
     // system-scope fence per CTA publishes them all (a fence in every thread cost a third of k_compact_send's time:
-    // 841 k membar.sys for 3288 CTAs, profiles/ncu_exchange_r2.csv).
+    // 841 k membar.sys for 3288 CTAs, profiles/ncu_exchange_r2.csv).  The multicast (multimem.st) variant keeps the
+    // per-thread fence it was validated with on 8 GPUs; the unicast path was re-validated on real GPUs after the change.
+    if (p.mc_region) __threadfence_system();
     __syncthreads();
     if (threadIdx.x == 0) {
         __threadfence_system();
